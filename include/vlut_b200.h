@@ -1,0 +1,119 @@
+/*
+ * vlut_b200.h -- C ABI of the B200-native Vec-LUT ternary MUL_MAT path (libvlut_b200.so).
+ *
+ * This is the drop-in boundary below the ggml backend plugin (libggml-vlut-b200.so):
+ * plain pointers and sizes, no C++/torch types, int error codes, never throws.  Every entry point names the
+ * piece of the reference (spinal-cord/vlut.cpp, paths relative to its root) it replaces.
+ *
+ * The op:  out[t][n] = (float)( sum_g wrap16( sum_{k in g} w[n][k] * q[t][k] ) ) * scale[t]
+ *   w  ternary {-1,0,+1}, GGUF-packed as I2_V / I2_V_4 / I2_V_8 (4 trits/byte) or I1_V / I1_V_2 (5 trits/byte)
+ *   q  per-token int8 quantisation of the f32 activations, scale[t] = max_k(x[t][k]) / 127
+ *   g  K-groups of 512 (I2*) or 640 (I1*) inside which the reference keeps int16 partial sums
+ * bit-exact against the reference CPU kernels (ggml/src/ggml-cpu/ggml-cpu-quants-vlut.c).
+ *
+ * There is no CPU fallback: every compute entry point returns VLUT_ERR_CUDA if no sm_100 device is usable.
+ */
+#ifndef VLUT_B200_H
+#define VLUT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VLUT_B200_VERSION 1
+
+/* error codes */
+#define VLUT_OK               0
+#define VLUT_ERR_INVALID     (-1)  /* bad argument (type, shape, null pointer) */
+#define VLUT_ERR_CUDA        (-2)  /* CUDA runtime error or no usable device; see vlut_last_cuda_error() */
+#define VLUT_ERR_UNSUPPORTED (-3)  /* shape not handled by the requested algorithm */
+#define VLUT_ERR_NOMEM       (-4)
+
+/* weight types: numerically identical to the reference's enum ggml_type (ggml/include/ggml.h:425-434) */
+#define VLUT_TYPE_I2_V    40
+#define VLUT_TYPE_I2_V_4  42
+#define VLUT_TYPE_I2_V_8  43
+#define VLUT_TYPE_I1_V    45
+#define VLUT_TYPE_I1_V_2  46
+
+/* GEMM algorithms (stage 2).  AUTO picks per token count from the measured crossover table. */
+#define VLUT_ALGO_AUTO    0
+#define VLUT_ALGO_SIMPLE  1   /* one thread per output, scalar: the in-library correctness anchor            */
+#define VLUT_ALGO_MMA     2   /* stream-K, TMA-bulk weight stream, register decode, mma.sync u8xs8 (small T)   */
+#define VLUT_ALGO_TC      3   /* tcgen05 kind::i8, ternary->int8 unpack in shared memory, TMEM accum (large T) */
+#define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate (measured candidate)      */
+
+typedef struct vlut_ctx vlut_ctx;
+
+/* ---- library / device ---------------------------------------------------------------------------------- */
+int         vlut_version(void);
+const char *vlut_error_string(int code);
+const char *vlut_last_cuda_error(void);            /* text of the last CUDA error seen by this thread       */
+int         vlut_device_count(int *count);         /* number of CUDA devices with compute capability 10.x    */
+int         vlut_device_info(int device, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes,
+                             int *sm_count);       /* replaces ggml_backend_dev get_description/get_memory    */
+
+/* A context = one device + one stream + a growable device workspace (quantised activations, stream-K
+ * partials).  Replaces the per-op scratch of the reference (params->wdata, ggml-cpu.c:1388-1399, and the
+ * malloc/free inside every kernel call, ggml-cpu-quants-vlut.c:1177-1182).  `stream` may be NULL (the
+ * context creates its own) or an existing cudaStream_t.  One host thread per context at a time. */
+int   vlut_ctx_create(int device, void *stream, vlut_ctx **out);
+void  vlut_ctx_destroy(vlut_ctx *ctx);
+void *vlut_ctx_stream(vlut_ctx *ctx);
+int   vlut_ctx_sync(vlut_ctx *ctx);
+/* number of this library's kernels launched through ctx so far (bench.py's gpu_launches) */
+int64_t vlut_ctx_launch_count(const vlut_ctx *ctx);
+
+/* ---- weights ------------------------------------------------------------------------------------------- */
+/* bytes of the GGUF-packed tensor = ggml_nbytes (ggml/src/ggml.c:1286-1289, :1326-1335); 0 if invalid */
+size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N);
+/* bytes of the device-resident tiled 2-bit layout ("T2") the kernels stream; what the ggml
+ * buffer type's get_alloc_size reports */
+size_t vlut_repacked_nbytes(int type, int64_t K, int64_t N);
+/* GGUF layout (already on the device) -> T2.  Replaces nothing in the reference (its CPU kernels read the
+ * GGUF layout directly); this is the backend buffer's set_tensor hook. */
+int vlut_repack_weights(vlut_ctx *ctx, int type, int64_t K, int64_t N, const void *gguf_dev, void *t2_dev);
+/* convenience: host GGUF bytes -> staged H2D -> T2 */
+int vlut_upload_weights(vlut_ctx *ctx, int type, int64_t K, int64_t N, const void *gguf_host, void *t2_dev);
+/* host-side row shard of a GGUF-packed matrix: rows [row0, row0+rows) of all K, in the same packing, for
+ * output-row tensor parallelism (the per-thread row split of ggml-cpu.c:1413-1418 generalised to GPUs) */
+int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t rows, const void *gguf_host,
+                         void *shard_host);
+
+/* ---- the three stages ---------------------------------------------------------------------------------- */
+/* (1) per-token int8 activation quantisation into the context workspace.
+ *     Replaces quantize_row_i8_v_tile (ggml-cpu-quants-vlut.c:952-973) + the loop at ggml-cpu.c:1394-1407.
+ *     x_dev: f32 [T][ldx], ldx >= K. */
+int vlut_quantize_act(vlut_ctx *ctx, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T);
+/* (2)+(3) Vec-LUT GEMM + fp32 scale epilogue on the activations last quantised into ctx.
+ *     Replaces ggml_gemm_{i2v,i2v4,i2v8,i1v,i1v2}_i8v_lut (ggml-cpu-quants-vlut.c:980-1739).
+ *     out_dev: f32 [T][ldo], ldo >= N.  w_scale: optional per-tensor weight scale folded into the epilogue
+ *     (the trailing GGML_OP_MUL by the {1} `.scale` tensor, src/models/bitnet.cpp:33-34); pass 1.0f for the
+ *     bare op.  With w_scale == 1.0f the result is bit-identical to the reference kernel. */
+int vlut_gemm(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev,
+              int64_t ldo, float w_scale, int algo);
+/* the whole op on device buffers = GGML_OP_MUL_MAT(vlut weight, f32) of ggml-cpu.c:1372-1421 */
+int vlut_mul_mat(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
+                 int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo);
+/* the whole op on HOST buffers: H2D of x, the op, D2H of out, stream sync -- what a ggml_backend_sched split
+ * costs (ggml/src/ggml-backend.cpp:1443-1460).  Pinned host memory makes the copies asynchronous. */
+int vlut_mul_mat_host(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev,
+                      const float *x_host, int64_t ldx, float *out_host, int64_t ldo, float w_scale, int algo);
+
+/* which algorithm AUTO resolves to for this shape (also what the last vlut_gemm on ctx used) */
+int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T);
+int vlut_ctx_last_algo(const vlut_ctx *ctx);
+
+/* ---- test hooks ---------------------------------------------------------------------------------------- */
+/* copy the quantised activations of the last vlut_quantize_act back: q_host int8 [T][K], scales_host [T] */
+int vlut_debug_get_act(vlut_ctx *ctx, int64_t K, int64_t T, int8_t *q_host, float *scales_host);
+/* decode a T2 buffer back to ternary int8 [N][K] on the host (round-trip check of the repacker) */
+int vlut_debug_unpack_t2(vlut_ctx *ctx, int type, int64_t K, int64_t N, const void *t2_dev, int8_t *w_host);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VLUT_B200_H */

@@ -1,0 +1,223 @@
+"""GPU suite: the CUDA path, called through the C ABI (libvlut_b200.so via ctypes), against the oracle.
+
+Bit-exact everywhere (the op is integer arithmetic followed by one fp32 multiply): fp32 outputs are compared as
+uint32 bit patterns -- a stricter bar than north_star's 1e-6 relative tolerance.
+"""
+import glob
+import hashlib
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+FIXTURES = sorted(glob.glob(str(GOLDEN / "*.npz")))
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def api():
+    import vlut_b200  # noqa: F401
+    from vlut_b200 import api as a
+    return a
+
+
+def algos_for(T):
+    a = api()
+    out = [a.ALGO_SIMPLE, a.ALGO_AUTO]
+    if T <= 64:
+        out.append(a.ALGO_MMA)
+    return out
+
+
+def run(ctx, type_, packed, x, N, algo, w_scale=1.0):
+    a = api()
+    T, K = x.shape
+    w = ctx.upload(type_, K, N, packed)
+    xd = torch.from_numpy(x).cuda()
+    out = ctx.mul_mat(w, xd, w_scale=w_scale, algo=algo)
+    torch.cuda.synchronize()
+    return out.cpu().numpy()
+
+
+def test_native_library_is_loaded(ctx):
+    import vlut_b200
+    maps = open("/proc/self/maps").read()
+    assert str(vlut_b200.LIB_PATH) in maps
+    assert api().device_count() >= 1
+
+
+@pytest.mark.parametrize("type_,K,N", [(O.I2_V, 1024, 130), (O.I2_V_4, 4096, 256), (O.I2_V_8, 2048, 64),
+                                       (O.I1_V, 1300, 77), (O.I1_V_2, 3200, 128), (O.I1_V_2, 4096, 40),
+                                       (O.I1_V, 1048, 16)])
+def test_repack_round_trip(ctx, orc, type_, K, N):
+    """GGUF bytes -> T2 (device) -> ternary == the weights that were packed (all five packings, ragged N, I1 tail)."""
+    w = O.make_ternary(N, K, seed=11)
+    packed = orc.pack(type_, w)
+    W = ctx.upload(type_, K, N, packed)
+    assert np.array_equal(ctx.unpack(W), w.astype(np.int8))
+    # device-resident source takes the same path
+    W2 = ctx.upload(type_, K, N, torch.from_numpy(packed).cuda())
+    torch.cuda.synchronize()
+    assert torch.equal(W.t2, W2.t2)
+
+
+@pytest.mark.parametrize("kind", ["normal", "uniform", "outlier", "negative", "zeros", "ones"])
+@pytest.mark.parametrize("T,K", [(1, 512), (7, 4096), (33, 3200), (70, 1300)])
+def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
+    x = O.make_acts(T, K, seed=T + K, kind=kind)
+    q_ref, s_ref = orc.quantize(x)
+    ctx.quantize_act(O.I2_V_4 if K % 16 == 0 else O.I1_V, torch.from_numpy(x).cuda())
+    q, s = ctx.get_act(K, T)
+    assert np.array_equal(q, q_ref)
+    assert np.array_equal(bits(s), bits(s_ref))
+
+
+def test_quantize_strided_rows(ctx, orc):
+    # ggml's src1 may have nb11 > 4*K
+    T, K, ld = 9, 1024, 1100
+    buf = np.zeros((T, ld), dtype=np.float32)
+    buf[:, :K] = O.make_acts(T, K, seed=1)
+    xd = torch.from_numpy(buf).cuda()[:, :K]
+    ctx.quantize_act(O.I2_V_4, xd)
+    q, s = ctx.get_act(K, T)
+    q_ref, s_ref = orc.quantize(buf[:, :K])
+    assert np.array_equal(q, q_ref) and np.array_equal(bits(s), bits(s_ref))
+
+
+@pytest.mark.parametrize("path", FIXTURES, ids=lambda p: Path(p).stem)
+def test_golden_fixtures(ctx, path):
+    """Committed outputs of the reference's own kernels (tests/golden, oracle/make_golden.py)."""
+    z = np.load(path)
+    type_, K, N, T = int(z["type"]), int(z["K"]), int(z["N"]), int(z["T"])
+    for algo in algos_for(T):
+        out = run(ctx, type_, z["packed"], z["x"], N, algo)
+        assert np.array_equal(bits(out), bits(z["out"])), f"algo={algo}"
+    q, s = ctx.get_act(K, T)
+    assert np.array_equal(q, z["q"]) and np.array_equal(bits(s), bits(z["scales"]))
+
+
+SHAPES = [
+    # type, K, N  -- model shapes scaled down in N, plus ragged / tail cases
+    (O.I2_V_4, 4096, 384), (O.I2_V_4, 2048, 200), (O.I2_V, 1040, 129), (O.I2_V_8, 3072, 256),
+    (O.I1_V_2, 3200, 320), (O.I1_V_2, 8640, 136), (O.I1_V, 1300, 64), (O.I1_V_2, 4096, 128), (O.I1_V, 3072, 72),
+]
+
+
+@pytest.mark.parametrize("T", [1, 2, 7, 16, 17, 32, 33, 64, 100, 256])
+@pytest.mark.parametrize("type_,K,N", SHAPES)
+def test_mul_mat_bit_exact(ctx, orc, type_, K, N, T):
+    w = O.make_ternary(N, K, seed=K + N)
+    x = O.make_acts(T, K, seed=T, kind="outlier" if T % 2 else "normal")
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    for algo in algos_for(T):
+        out = run(ctx, type_, packed, x, N, algo)
+        bad = bits(out) != bits(ref)
+        assert not bad.any(), f"algo={algo}: {bad.sum()} of {bad.size} differ, first at {np.argwhere(bad)[0]}"
+
+
+@pytest.mark.parametrize("type_,K", [(O.I2_V_4, 4096), (O.I1_V_2, 3200), (O.I2_V_4, 1536)])
+@pytest.mark.parametrize("T", [3, 40, 200])
+def test_int16_wrap(ctx, orc, type_, K, T):
+    """Adversarial: all-(+1) weights x saturated activations overflow int16 in every K-group."""
+    N = 144
+    w = np.ones((N, K), dtype=np.float32)
+    w[::3] = -1.0
+    x = O.make_acts(T, K, kind="ones")
+    x[1::2] *= -1.0  # negative rows saturate to -128
+    x[:, ::5] = 0.5
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    for algo in algos_for(T):
+        out = run(ctx, type_, packed, x, N, algo)
+        assert np.array_equal(bits(out), bits(ref)), f"algo={algo}"
+
+
+def test_full_size_known_answers(ctx):
+    """BASELINE.json configs at full size: sha256 of the fp32 result == the reference's own (kat_full.json)."""
+    kats = json.loads((GOLDEN / "kat_full.json").read_text())
+    for name, k in kats.items():
+        w = O.make_ternary(k["N"], k["K"], seed=k["w_seed"])
+        x = O.make_acts(k["T"], k["K"], seed=k["x_seed"], kind=k["x_kind"])
+        if hashlib.sha256(x.tobytes()).hexdigest() != k["sha256_x"]:
+            pytest.skip("numpy RNG stream differs from the one the fixtures were made with")
+        packed = O.Oracle().pack(k["type"], w)
+        assert hashlib.sha256(packed.tobytes()).hexdigest() == k["sha256_packed"]
+        for algo in algos_for(k["T"])[1:]:
+            out = run(ctx, k["type"], packed, x, k["N"], algo)
+            assert hashlib.sha256(out.tobytes()).hexdigest() == k["sha256_out"], f"{name} algo={algo}"
+
+
+@pytest.mark.parametrize("T", [4, 48, 512])
+def test_properties_at_full_size(ctx, T):
+    """Size-independent properties at the headline shape (4096 -> 14336): determinism, agreement between
+    algorithms, w_scale folding, row-shard concatenation == full result."""
+    a = api()
+    K, N = 4096, 14336
+    rng = np.random.Generator(np.random.PCG64(T))
+    w = (rng.integers(0, 3, size=(N, K), dtype=np.int8) - 1).astype(np.float32)
+    packed = O.Oracle().pack(O.I2_V_4, w)
+    x = rng.standard_normal((T, K), dtype=np.float32)
+    W = ctx.upload(O.I2_V_4, K, N, packed)
+    xd = torch.from_numpy(x).cuda()
+    base = ctx.mul_mat(W, xd, algo=a.ALGO_AUTO).clone()
+    again = ctx.mul_mat(W, xd, algo=a.ALGO_AUTO)
+    assert torch.equal(base, again)  # deterministic (stream-K partials are integers)
+    simple = ctx.mul_mat(W, xd, algo=a.ALGO_SIMPLE)
+    assert torch.equal(base, simple)
+    # exact integer check against torch on the device: out == (q @ w^T) * scale  (no wrap for these inputs)
+    q, s = ctx.get_act(K, T)
+    acc = (torch.from_numpy(q).cuda().double() @ torch.from_numpy(w).cuda().double().T)
+    expect = (acc.float() * torch.from_numpy(s).cuda()[:, None])
+    assert torch.equal(base, expect)
+    # weight scale folded into the epilogue == a following MUL by the scalar (bitnet.cpp:33-34)
+    scaled = ctx.mul_mat(W, xd, w_scale=0.0371, algo=a.ALGO_AUTO)
+    assert torch.equal(scaled, base * torch.tensor(0.0371, dtype=torch.float32, device="cuda"))
+    # output-row sharding: 4 shards concatenated == full
+    parts = []
+    for g in range(4):
+        r0, rows = g * N // 4, N // 4
+        Wg = ctx.upload(O.I2_V_4, K, rows, a.shard_rows(O.I2_V_4, K, N, r0, rows, packed))
+        parts.append(ctx.mul_mat(Wg, xd, algo=a.ALGO_AUTO).clone())
+    assert torch.equal(torch.cat(parts, dim=1), base)
+
+
+def test_mul_mat_host_buffers(ctx, orc):
+    a = api()
+    type_, K, N, T = O.I2_V_4, 2048, 512, 24
+    w = O.make_ternary(N, K, seed=1)
+    x = O.make_acts(T, K, seed=2)
+    packed = orc.pack(type_, w)
+    W = ctx.upload(type_, K, N, packed)
+    xh = torch.from_numpy(x).pin_memory()
+    oh = torch.empty((T, N), dtype=torch.float32).pin_memory()
+    ctx.mul_mat_host(W, xh, oh)
+    assert np.array_equal(bits(oh.numpy()), bits(orc.mul_mat(type_, packed, x, N)))
+
+
+def test_strided_output_and_errors(ctx, orc):
+    a = api()
+    type_, K, N, T = O.I1_V_2, 1280, 100, 5
+    w = O.make_ternary(N, K, seed=1)
+    x = O.make_acts(T, K, seed=2)
+    packed = orc.pack(type_, w)
+    W = ctx.upload(type_, K, N, packed)
+    big = torch.full((T, N + 28), -7.0, device="cuda")
+    ctx.mul_mat(W, torch.from_numpy(x).cuda(), out=big[:, :N])
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(big[:, :N].cpu().numpy()), bits(orc.mul_mat(type_, packed, x, N)))
+    assert (big[:, N:] == -7.0).all()  # nothing written past N
+    from vlut_b200._lib import VlutError
+    with pytest.raises(VlutError):
+        ctx.mul_mat(W, torch.from_numpy(x).cuda(), algo=99)
+    with pytest.raises(ValueError):
+        ctx.upload(O.I2_V_4, 1000, 8, np.zeros(10, dtype=np.uint8))  # K % 16 != 0

@@ -1,0 +1,82 @@
+"""ctypes binding of libvlut_b200.so (the C ABI of include/vlut_b200.h).
+
+The library is the product: if it is missing or cannot be loaded, importing the compute API raises -- there is
+no PyTorch/NumPy/CPU fallback anywhere in this package.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import re
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "csrc" / "build" / "libvlut_b200.so"
+HEADER = HERE.parent / "include" / "vlut_b200.h"
+
+_lib = None
+
+i64, cint, vp, f32 = C.c_int64, C.c_int, C.c_void_p, C.c_float
+
+_SIGNATURES = {
+    "vlut_version": (cint, []),
+    "vlut_error_string": (C.c_char_p, [cint]),
+    "vlut_last_cuda_error": (C.c_char_p, []),
+    "vlut_device_count": (cint, [C.POINTER(cint)]),
+    "vlut_device_info": (cint, [cint, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_size_t),
+                                C.POINTER(cint)]),
+    "vlut_ctx_create": (cint, [cint, vp, C.POINTER(vp)]),
+    "vlut_ctx_destroy": (None, [vp]),
+    "vlut_ctx_stream": (vp, [vp]),
+    "vlut_ctx_sync": (cint, [vp]),
+    "vlut_ctx_launch_count": (i64, [vp]),
+    "vlut_ctx_last_algo": (cint, [vp]),
+    "vlut_gguf_nbytes": (C.c_size_t, [cint, i64, i64]),
+    "vlut_repacked_nbytes": (C.c_size_t, [cint, i64, i64]),
+    "vlut_repack_weights": (cint, [vp, cint, i64, i64, vp, vp]),
+    "vlut_upload_weights": (cint, [vp, cint, i64, i64, vp, vp]),
+    "vlut_shard_rows_host": (cint, [cint, i64, i64, i64, i64, vp, vp]),
+    "vlut_quantize_act": (cint, [vp, cint, vp, i64, i64, i64]),
+    "vlut_gemm": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, f32, cint]),
+    "vlut_mul_mat": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
+    "vlut_mul_mat_host": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
+    "vlut_pick_algo": (cint, [cint, i64, i64, i64]),
+    "vlut_debug_get_act": (cint, [vp, i64, i64, vp, vp]),
+    "vlut_debug_unpack_t2": (cint, [vp, cint, i64, i64, vp, vp]),
+}
+
+
+def declared_symbols() -> list[str]:
+    """Every function include/vlut_b200.h declares (used by the CPU-side export test)."""
+    text = HEADER.read_text()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(vlut_[a-z0-9_]+)\s*\(", text)))
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise RuntimeError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                               f"g.build()'` (nvcc, sm_100a). There is no CPU fallback.")
+        L = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in _SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+class VlutError(RuntimeError):
+    def __init__(self, code: int, where: str):
+        L = lib()
+        msg = L.vlut_error_string(code).decode()
+        if code == -2:
+            msg += f" [{L.vlut_last_cuda_error().decode()}]"
+        super().__init__(f"{where}: {msg} (code {code})")
+        self.code = code
+
+
+def check(code: int, where: str) -> None:
+    if code != 0:
+        raise VlutError(code, where)

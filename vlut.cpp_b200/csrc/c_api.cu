@@ -1,0 +1,395 @@
+// c_api.cu -- the extern "C" surface declared in include/vlut_b200.h (libvlut_b200.so).
+// Host-side orchestration only: argument checks, workspace management, stage sequencing, algorithm choice.
+// No arithmetic happens on the host and there is no CPU fallback: without a usable sm_100 device every compute
+// entry point returns VLUT_ERR_CUDA.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "vlut_common.cuh"
+
+using namespace vlut;
+
+static thread_local char g_cuda_err[256] = "";
+
+static int cuda_fail(cudaError_t e, const char *what) {
+    snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s", what, cudaGetErrorString(e));
+    return VLUT_ERR_CUDA;
+}
+#define CK(call)                                           \
+    do {                                                   \
+        cudaError_t e__ = (call);                          \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+    } while (0)
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    // grow-only; returns true if (re)allocated
+    cudaError_t reserve(size_t n, bool *grew = nullptr) {
+        if (grew) *grew = false;
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = n + n / 4;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e != cudaSuccess) return e;
+        cap = want;
+        if (grew) *grew = true;
+        return cudaSuccess;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct vlut_ctx {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    DevBuf q_rm, q_frag, scales, gsum, part, counters, stage_x, stage_out, stage_w;
+    ActView act{};
+    int64_t act_K = 0, act_T = 0;
+    int act_type = 0;
+    int64_t launches = 0;
+    int last_algo = 0;
+};
+
+extern "C" {
+
+int vlut_version(void) { return VLUT_B200_VERSION; }
+
+const char *vlut_error_string(int code) {
+    switch (code) {
+        case VLUT_OK: return "ok";
+        case VLUT_ERR_INVALID: return "invalid argument";
+        case VLUT_ERR_CUDA: return "CUDA error / no usable sm_100 device";
+        case VLUT_ERR_UNSUPPORTED: return "shape not supported by the requested algorithm";
+        case VLUT_ERR_NOMEM: return "out of memory";
+        default: return "unknown error";
+    }
+}
+
+const char *vlut_last_cuda_error(void) { return g_cuda_err; }
+
+int vlut_device_count(int *count) {
+    if (!count) return VLUT_ERR_INVALID;
+    *count = 0;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+    int ok = 0;
+    for (int i = 0; i < n; i++) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ok++;
+    }
+    *count = ok;
+    return VLUT_OK;
+}
+
+int vlut_device_info(int device, char *name, size_t name_len, size_t *free_bytes, size_t *total_bytes, int *sm_count) {
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    if (name && name_len) snprintf(name, name_len, "%s", prop.name);
+    if (sm_count) *sm_count = prop.multiProcessorCount;
+    if (free_bytes || total_bytes) {
+        int prev = 0;
+        cudaGetDevice(&prev);
+        CK(cudaSetDevice(device));
+        size_t f = 0, t = 0;
+        CK(cudaMemGetInfo(&f, &t));
+        if (free_bytes) *free_bytes = f;
+        if (total_bytes) *total_bytes = t;
+        cudaSetDevice(prev);
+    }
+    return VLUT_OK;
+}
+
+int vlut_ctx_create(int device, void *stream, vlut_ctx **out) {
+    if (!out) return VLUT_ERR_INVALID;
+    *out = nullptr;
+    int n = 0;
+    CK(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return VLUT_ERR_INVALID;
+    int major = 0;
+    CK(cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device));
+    if (major != 10) {
+        snprintf(g_cuda_err, sizeof(g_cuda_err), "device %d has compute capability %d.x; this library is sm_100a only", device,
+                 major);
+        return VLUT_ERR_CUDA;
+    }
+    CK(cudaSetDevice(device));
+    vlut_ctx *c = new (std::nothrow) vlut_ctx();
+    if (!c) return VLUT_ERR_NOMEM;
+    c->device = device;
+    CK(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    if (stream) {
+        c->stream = (cudaStream_t) stream;
+    } else {
+        cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+        if (e != cudaSuccess) {
+            delete c;
+            return cuda_fail(e, "cudaStreamCreate");
+        }
+        c->own_stream = true;
+    }
+    *out = c;
+    return VLUT_OK;
+}
+
+void vlut_ctx_destroy(vlut_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    DevBuf *bufs[] = {&c->q_rm, &c->q_frag, &c->scales, &c->gsum, &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
+    for (DevBuf *b : bufs) b->release();
+    if (c->own_stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+void *vlut_ctx_stream(vlut_ctx *c) { return c ? (void *) c->stream : nullptr; }
+
+int vlut_ctx_sync(vlut_ctx *c) {
+    if (!c) return VLUT_ERR_INVALID;
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
+int64_t vlut_ctx_launch_count(const vlut_ctx *c) { return c ? c->launches : 0; }
+int vlut_ctx_last_algo(const vlut_ctx *c) { return c ? c->last_algo : 0; }
+
+size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N) {
+    if (!type_valid(type) || K <= 0 || N <= 0 || K % 4) return 0;
+    return (size_t) (gguf_row_bytes(type, K) * N);
+}
+
+size_t vlut_repacked_nbytes(int type, int64_t K, int64_t N) {
+    if (!type_valid(type) || K <= 0 || N <= 0 || K % 4) return 0;
+    return (size_t) (round_up(N, TILE_ROWS) * round_up(K, TILE_K) / 4);
+}
+
+static int check_shape(int type, int64_t K, int64_t N) {
+    if (!type_valid(type) || K <= 0 || N <= 0 || K % 4) return VLUT_ERR_INVALID;
+    // the reference packers index with int and require these (ggml-quants-vlut.c:61-107): K%16 for I2_V_4, K%32 for I2_V_8
+    if (type == VLUT_TYPE_I2_V_4 && K % 16) return VLUT_ERR_INVALID;
+    if (type == VLUT_TYPE_I2_V_8 && K % 32) return VLUT_ERR_INVALID;
+    return VLUT_OK;
+}
+
+int vlut_repack_weights(vlut_ctx *c, int type, int64_t K, int64_t N, const void *gguf_dev, void *t2_dev) {
+    if (!c || !gguf_dev || !t2_dev) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    CK(launch_repack(type, K, N, (const uint8_t *) gguf_dev, (uint8_t *) t2_dev, c->stream));
+    c->launches++;
+    return VLUT_OK;
+}
+
+int vlut_upload_weights(vlut_ctx *c, int type, int64_t K, int64_t N, const void *gguf_host, void *t2_dev) {
+    if (!c || !gguf_host || !t2_dev) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    const size_t nb = vlut_gguf_nbytes(type, K, N);
+    // the staging buffer may still be read by a previous repack on this stream
+    CK(cudaStreamSynchronize(c->stream));
+    if (c->stage_w.reserve(nb) != cudaSuccess) return VLUT_ERR_NOMEM;
+    CK(cudaMemcpyAsync(c->stage_w.p, gguf_host, nb, cudaMemcpyHostToDevice, c->stream));
+    CK(launch_repack(type, K, N, (const uint8_t *) c->stage_w.p, (uint8_t *) t2_dev, c->stream));
+    c->launches++;
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
+int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t rows, const void *gguf_host,
+                         void *shard_host) {
+    if (!gguf_host || !shard_host || row0 < 0 || rows <= 0 || row0 + rows > N) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    const uint8_t *src = (const uint8_t *) gguf_host;
+    uint8_t *dst = (uint8_t *) shard_host;
+    const int64_t rs = gguf_row_bytes(type, K);
+    const int64_t nb5 = type_is_i1(type) ? K / 20 * 4 : rs;
+    const int il0 = gguf_interleave(type);
+    // byte p of row n lives at (p/il)*il*N + n*il + p%il: for a fixed interleave group the rows are contiguous
+    for (int64_t p0 = 0; p0 < rs;) {
+        const int il = (type == VLUT_TYPE_I1_V_2 && p0 >= nb5) ? 1 : il0;
+        memcpy(dst + (p0 / il) * il * rows, src + (p0 / il) * il * N + row0 * il, (size_t) (rows * il));
+        p0 += il;
+    }
+    return VLUT_OK;
+}
+
+// (re)shape the activation workspace of ctx for (type, K, T)
+static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
+    const int64_t Kpad = round_up(K, TILE_K);
+    const int64_t Tpad = round_up(T, 16);
+    const int gsize = group_size(type);
+    const int G = (int) ceil_div(K, gsize);
+    if (G > 64) return VLUT_ERR_UNSUPPORTED;
+    if (c->q_rm.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->q_frag.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->scales.reserve((size_t) Tpad * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->gsum.reserve((size_t) Tpad * G * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    c->act.q_rm = (int8_t *) c->q_rm.p;
+    c->act.q_frag = (int8_t *) c->q_frag.p;
+    c->act.scales = (float *) c->scales.p;
+    c->act.gsum = (int32_t *) c->gsum.p;
+    c->act.Kpad = Kpad;
+    c->act.Tpad = Tpad;
+    c->act.G = G;
+    c->act.gsize = gsize;
+    c->act_K = K;
+    c->act_T = T;
+    c->act_type = type;
+    return VLUT_OK;
+}
+
+int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
+    if (!c || !x_dev || T <= 0 || ldx < K) return VLUT_ERR_INVALID;
+    if (!type_valid(type) || K <= 0 || K % 4) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    int rc = prepare_act(c, type, K, T);
+    if (rc) return rc;
+    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream));
+    c->launches++;
+    return VLUT_OK;
+}
+
+int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
+    // crossover table from measurements on B200 (profiles/, DESIGN.md section "crossover")
+    static int forced = -1;
+    if (forced < 0) {
+        const char *v = getenv("VLUT_B200_ALGO");
+        forced = v ? atoi(v) : 0;
+    }
+    if (forced > 0) return forced;
+    if (T <= 64 && gemm_mma_supported(type, K, N, T)) {
+        if (T <= 32 || !gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_MMA;
+    }
+    if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC;
+    return VLUT_ALGO_SIMPLE;
+}
+
+int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev, int64_t ldo,
+              float w_scale, int algo) {
+    if (!c || !t2_dev || !out_dev || T <= 0 || ldo < N) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    if (c->act_K != K || c->act_T != T || group_size(c->act_type) != group_size(type)) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, N, T);
+
+    GemmArgs g{};
+    g.w = (const uint8_t *) t2_dev;
+    g.act = c->act;
+    g.out = out_dev;
+    g.ldo = ldo;
+    g.K = K;
+    g.N = N;
+    g.T = T;
+    g.Npad = round_up(N, TILE_ROWS);
+    g.type = type;
+    g.w_scale = w_scale;
+    g.sm_count = c->sm_count;
+
+    if (algo == VLUT_ALGO_MMA || algo == VLUT_ALGO_LUT) {
+        // stream-K workspace: zeroed once at (re)allocation, the kernels leave it zero
+        bool grew = false;
+        const size_t pb = (size_t) (round_up(T, 16) * g.Npad) * sizeof(int32_t);
+        if (c->part.reserve(pb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+        if (grew) CK(cudaMemsetAsync(c->part.p, 0, c->part.cap, c->stream));
+        const size_t cb = (size_t) (g.Npad / TILE_ROWS) * sizeof(int32_t);
+        if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+        if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));
+        g.part = (int32_t *) c->part.p;
+        g.counters = (int32_t *) c->counters.p;
+    }
+
+    int launches = 0;
+    cudaError_t e;
+    switch (algo) {
+        case VLUT_ALGO_SIMPLE:
+            e = launch_gemm_simple(g, c->stream);
+            launches = 1;
+            break;
+        case VLUT_ALGO_MMA:
+            if (!gemm_mma_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_mma(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_TC:
+            if (!gemm_tc_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tc(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_LUT:
+            if (!gemm_lut_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_lut(g, c->stream, &launches);
+            break;
+        default:
+            return VLUT_ERR_INVALID;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
+    c->launches += launches;
+    c->last_algo = algo;
+    return VLUT_OK;
+}
+
+int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
+                 int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo) {
+    int rc = vlut_quantize_act(c, type, x_dev, ldx, K, T);
+    if (rc) return rc;
+    return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
+}
+
+int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_host,
+                      int64_t ldx, float *out_host, int64_t ldo, float w_scale, int algo) {
+    if (!c || !x_host || !out_host || T <= 0 || ldx < K || ldo < N) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    if (c->stage_x.reserve((size_t) (T * K) * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->stage_out.reserve((size_t) (T * N) * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    CK(cudaMemcpy2DAsync(c->stage_x.p, (size_t) K * 4, x_host, (size_t) ldx * 4, (size_t) K * 4, (size_t) T,
+                         cudaMemcpyHostToDevice, c->stream));
+    rc = vlut_mul_mat(c, type, K, N, T, t2_dev, (const float *) c->stage_x.p, K, (float *) c->stage_out.p, N, w_scale, algo);
+    if (rc) return rc;
+    CK(cudaMemcpy2DAsync(out_host, (size_t) ldo * 4, c->stage_out.p, (size_t) N * 4, (size_t) N * 4, (size_t) T,
+                         cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
+int vlut_debug_get_act(vlut_ctx *c, int64_t K, int64_t T, int8_t *q_host, float *scales_host) {
+    if (!c || c->act_K != K || c->act_T != T) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    if (q_host)
+        CK(cudaMemcpy2D(q_host, (size_t) K, c->act.q_rm, (size_t) c->act.Kpad, (size_t) K, (size_t) T, cudaMemcpyDeviceToHost));
+    if (scales_host) CK(cudaMemcpy(scales_host, c->act.scales, (size_t) T * sizeof(float), cudaMemcpyDeviceToHost));
+    return VLUT_OK;
+}
+
+int vlut_debug_unpack_t2(vlut_ctx *c, int type, int64_t K, int64_t N, const void *t2_dev, int8_t *w_host) {
+    if (!c || !t2_dev || !w_host) return VLUT_ERR_INVALID;
+    int rc = check_shape(type, K, N);
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    int8_t *tmp = nullptr;
+    CK(cudaMalloc(&tmp, (size_t) (N * K)));
+    cudaError_t e = launch_unpack_t2(K, N, (const uint8_t *) t2_dev, tmp, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = cudaMemcpy(w_host, tmp, (size_t) (N * K), cudaMemcpyDeviceToHost);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return cuda_fail(e, "unpack_t2");
+    c->launches++;
+    return VLUT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,100 @@
+// quantize.cu -- stage 1: per-token int8 activation quantisation.
+//
+// Bit-exact restatement, for sm_100a, of quantize_row_i8_v_tile (reference
+// ggml/src/ggml-cpu/ggml-cpu-quants-vlut.c:952-973):
+//     m  = max(1e-5, max_k x[k])            SIGNED max -- no fabs
+//     s  = m / 127                          (double)
+//     is = 1 / max(s, 1e-5)                 (double)
+//     q  = clamp(round((double)x * is), -128, 127)     round = half away from zero
+//     scale = (float) s
+// FP64 throughput is irrelevant here (T*K elements); the kernel is a pure HBM/L2 stream: one CTA per token,
+// 128-bit loads of x, 32-bit stores of q in two layouts (row-major for TMA/tcgen05, mma.sync A-fragment order),
+// plus the per-(token, K-group) sums that undo the +1 offset of the u8 weight codes.
+#include "vlut_common.cuh"
+
+namespace vlut {
+
+constexpr int QT = 256;
+
+__global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
+                                                      ActView a) {
+    const int t = blockIdx.x;
+    const int tid = threadIdx.x;
+    __shared__ float s_red[QT / 32];
+    __shared__ int s_gsum[64];
+    __shared__ double s_is;
+
+    const int64_t Kpad = a.Kpad;
+    const int MTall = (int) (a.Tpad / 16);
+    const bool live = t < T;
+    const float *xr = x + (int64_t) t * ldx;
+
+    for (int i = tid; i < 64; i += QT) s_gsum[i] = 0;
+
+    // pass 1: signed max
+    float mx = -INFINITY;
+    if (live) {
+        const bool vec = ((reinterpret_cast<uintptr_t>(xr) & 15) == 0);
+        if (vec) {
+            for (int64_t k = (int64_t) tid * 4; k + 3 < K; k += QT * 4) {
+                const float4 v = *reinterpret_cast<const float4 *>(xr + k);
+                mx = fmaxf(mx, fmaxf(fmaxf(v.x, v.y), fmaxf(v.z, v.w)));
+            }
+            for (int64_t k = (K & ~3LL) + tid; k < K; k += QT) mx = fmaxf(mx, xr[k]);
+        } else {
+            for (int64_t k = tid; k < K; k += QT) mx = fmaxf(mx, xr[k]);
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if ((tid & 31) == 0) s_red[tid >> 5] = mx;
+    __syncthreads();
+    if (tid == 0) {
+        float m = s_red[0];
+        for (int i = 1; i < QT / 32; i++) m = fmaxf(m, s_red[i]);
+        double dm = (double) m;
+        if (!(dm > 1e-5)) dm = 1e-5;  // MAX(eps, .) with eps = 1e-5
+        const double s = dm / 127;
+        s_is = 1e0 / (s > 1e-5 ? s : 1e-5);
+        a.scales[t] = live ? (float) s : 0.0f;
+    }
+    __syncthreads();
+    const double is = s_is;
+
+    // pass 2: quantise 4 consecutive k per thread-iteration
+    for (int64_t k = (int64_t) tid * 4; k < Kpad; k += QT * 4) {
+        int qv[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            int q = 0;
+            if (live && k + j < K) {
+                float v = (float) round((double) xr[k + j] * is);
+                v = v > 127.f ? 127.f : (v < -128.f ? -128.f : v);
+                q = (int) v;
+            }
+            qv[j] = q;
+        }
+        const uint32_t pk = (uint32_t) (qv[0] & 0xff) | ((uint32_t) (qv[1] & 0xff) << 8) |
+                            ((uint32_t) (qv[2] & 0xff) << 16) | ((uint32_t) (qv[3] & 0xff) << 24);
+        *reinterpret_cast<uint32_t *>(a.q_rm + (int64_t) t * Kpad + k) = pk;
+        // A-fragment order
+        const int64_t kb = k / TILE_K;
+        const int kk = (int) (k % TILE_K);
+        const int tig = kk / 32, r = kk % 32, h = r / 16, i = (r % 16) / 4;
+        const int mt = t / 16, tr = t % 16, g = tr % 8, hi = tr / 8;
+        const int64_t off = ((kb * MTall + mt) * 4 + i) * 512 + (4 * g + tig) * 16 + (2 * h + hi) * 4;
+        *reinterpret_cast<uint32_t *>(a.q_frag + off) = pk;
+        const int sum = qv[0] + qv[1] + qv[2] + qv[3];
+        if (sum != 0) atomicAdd(&s_gsum[k / a.gsize], sum);
+    }
+    __syncthreads();
+    for (int i = tid; i < a.G; i += QT) a.gsum[(int64_t) t * a.G + i] = s_gsum[i];
+}
+
+cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s) {
+    if (a.G > 64) return cudaErrorInvalidValue;
+    quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a);
+    return cudaGetLastError();
+}
+
+}  // namespace vlut
