@@ -42,8 +42,7 @@ extern "C" {
 /* GEMM algorithms (stage 2).  AUTO picks per token count from the measured crossover table. */
 #define VLUT_ALGO_AUTO    0
 #define VLUT_ALGO_SIMPLE  1   /* one thread per output, scalar: the in-library correctness anchor            */
-#define VLUT_ALGO_MMA     2   /* stream-K, TMA-bulk weight stream, register decode, mma.sync u8xs8 (small T)   */
-#define VLUT_ALGO_TC      3   /* tcgen05 kind::i8, ternary->int8 unpack in shared memory, TMEM accum (large T) */
+#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8: TMA weight stream, register unpack into TMEM/smem, TMEM acc */
 #define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate (measured candidate)      */
 
 typedef struct vlut_ctx vlut_ctx;
@@ -59,7 +58,8 @@ int         vlut_device_info(int device, char *name, size_t name_len, size_t *fr
 /* A context = one device + one stream + a growable device workspace (quantised activations, stream-K
  * partials).  Replaces the per-op scratch of the reference (params->wdata, ggml-cpu.c:1388-1399, and the
  * malloc/free inside every kernel call, ggml-cpu-quants-vlut.c:1177-1182).  `stream` may be NULL (the
- * context creates its own) or an existing cudaStream_t.  One host thread per context at a time. */
+ * context creates its own non-blocking stream) or an existing cudaStream_t; name the legacy default stream by
+ * CUDA's alias cudaStreamLegacy ((cudaStream_t)0x1).  One host thread per context at a time. */
 int   vlut_ctx_create(int device, void *stream, vlut_ctx **out);
 void  vlut_ctx_destroy(vlut_ctx *ctx);
 void *vlut_ctx_stream(vlut_ctx *ctx);

@@ -23,8 +23,8 @@ I2_V, I2_V_4, I2_V_8, I1_V, I1_V_2 = 40, 42, 43, 45, 46
 TYPE_NAMES = {I2_V: "I2_V", I2_V_4: "I2_V_4", I2_V_8: "I2_V_8", I1_V: "I1_V", I1_V_2: "I1_V_2"}
 TYPE_BY_NAME = {v: k for k, v in TYPE_NAMES.items()}
 
-ALGO_AUTO, ALGO_SIMPLE, ALGO_MMA, ALGO_TC, ALGO_LUT = 0, 1, 2, 3, 4
-ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_MMA: "mma", ALGO_TC: "tc", ALGO_LUT: "lut"}
+ALGO_AUTO, ALGO_SIMPLE, ALGO_TC, ALGO_LUT = 0, 1, 3, 4
+ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_TC: "tc", ALGO_LUT: "lut"}
 
 
 def nbytes(type_: int, K: int, N: int) -> int:
@@ -83,8 +83,10 @@ class Context:
         with torch.cuda.device(self.device):
             self.stream = stream or torch.cuda.current_stream()
         h = C.c_void_p()
-        check(_lib.lib().vlut_ctx_create(self.device.index, C.c_void_p(self.stream.cuda_stream), C.byref(h)),
-              "vlut_ctx_create")
+        # torch's default stream has handle 0; the C ABI reserves NULL for "create a private stream", so the legacy
+        # default stream is named by CUDA's own alias cudaStreamLegacy (0x1)
+        handle = self.stream.cuda_stream or 1
+        check(_lib.lib().vlut_ctx_create(self.device.index, C.c_void_p(handle), C.byref(h)), "vlut_ctx_create")
         self._h = h
 
     def close(self) -> None:

@@ -53,7 +53,7 @@ struct vlut_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    DevBuf q_rm, q_frag, scales, gsum, part, counters, stage_x, stage_out, stage_w;
+    DevBuf q_rm, q_sw, scales, gsum, gsum_all, nowrap, part, counters, stage_x, stage_out, stage_w;
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
@@ -147,7 +147,8 @@ void vlut_ctx_destroy(vlut_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf *bufs[] = {&c->q_rm, &c->q_frag, &c->scales, &c->gsum, &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
+    DevBuf *bufs[] = {&c->q_rm,  &c->q_sw,     &c->scales,  &c->gsum,      &c->gsum_all, &c->nowrap,
+                      &c->part,  &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
     for (DevBuf *b : bufs) b->release();
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -164,14 +165,16 @@ int vlut_ctx_sync(vlut_ctx *c) {
 int64_t vlut_ctx_launch_count(const vlut_ctx *c) { return c ? c->launches : 0; }
 int vlut_ctx_last_algo(const vlut_ctx *c) { return c ? c->last_algo : 0; }
 
+static int check_shape(int type, int64_t K, int64_t N);
+
 size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N) {
-    if (!type_valid(type) || K <= 0 || N <= 0 || K % 4) return 0;
+    if (check_shape(type, K, N) != VLUT_OK) return 0;
     return (size_t) (gguf_row_bytes(type, K) * N);
 }
 
 size_t vlut_repacked_nbytes(int type, int64_t K, int64_t N) {
-    if (!type_valid(type) || K <= 0 || N <= 0 || K % 4) return 0;
-    return (size_t) (round_up(N, TILE_ROWS) * round_up(K, TILE_K) / 4);
+    if (check_shape(type, K, N) != VLUT_OK) return 0;
+    return (size_t) (round_up(N, TILE_ROWS) * round_up(K, BLOCK_K) / 4);
 }
 
 static int check_shape(int type, int64_t K, int64_t N) {
@@ -229,23 +232,29 @@ int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t r
 
 // (re)shape the activation workspace of ctx for (type, K, T)
 static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
-    const int64_t Kpad = round_up(K, TILE_K);
-    const int64_t Tpad = round_up(T, 16);
+    const int64_t Kpad = round_up(K, BLOCK_K);
+    const int NT = token_tile(T);
+    const int64_t Tpad = round_up(T, NT);
     const int gsize = group_size(type);
     const int G = (int) ceil_div(K, gsize);
     if (G > 64) return VLUT_ERR_UNSUPPORTED;
     if (c->q_rm.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
-    if (c->q_frag.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->q_sw.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->scales.reserve((size_t) Tpad * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->gsum.reserve((size_t) Tpad * G * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->gsum_all.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->nowrap.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     c->act.q_rm = (int8_t *) c->q_rm.p;
-    c->act.q_frag = (int8_t *) c->q_frag.p;
+    c->act.q_sw = (int8_t *) c->q_sw.p;
     c->act.scales = (float *) c->scales.p;
     c->act.gsum = (int32_t *) c->gsum.p;
+    c->act.gsum_all = (int32_t *) c->gsum_all.p;
+    c->act.nowrap = (int32_t *) c->nowrap.p;
     c->act.Kpad = Kpad;
     c->act.Tpad = Tpad;
     c->act.G = G;
     c->act.gsize = gsize;
+    c->act.NT = NT;
     c->act_K = K;
     c->act_T = T;
     c->act_type = type;
@@ -265,15 +274,9 @@ int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, in
 
 int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     // crossover table from measurements on B200 (profiles/, DESIGN.md section "crossover")
-    static int forced = -1;
-    if (forced < 0) {
-        const char *v = getenv("VLUT_B200_ALGO");
-        forced = v ? atoi(v) : 0;
-    }
+    const char *v = getenv("VLUT_B200_ALGO");
+    const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
-    if (T <= 64 && gemm_mma_supported(type, K, N, T)) {
-        if (T <= 32 || !gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_MMA;
-    }
     if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC;
     return VLUT_ALGO_SIMPLE;
 }
@@ -300,13 +303,13 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
     g.w_scale = w_scale;
     g.sm_count = c->sm_count;
 
-    if (algo == VLUT_ALGO_MMA || algo == VLUT_ALGO_LUT) {
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_LUT) {
         // stream-K workspace: zeroed once at (re)allocation, the kernels leave it zero
         bool grew = false;
-        const size_t pb = (size_t) (round_up(T, 16) * g.Npad) * sizeof(int32_t);
+        const size_t pb = (size_t) (c->act.Tpad * g.Npad) * sizeof(int32_t);
         if (c->part.reserve(pb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->part.p, 0, c->part.cap, c->stream));
-        const size_t cb = (size_t) (g.Npad / TILE_ROWS) * sizeof(int32_t);
+        const size_t cb = (size_t) ((g.Npad / TILE_ROWS) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));
         g.part = (int32_t *) c->part.p;
@@ -319,10 +322,6 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
         case VLUT_ALGO_SIMPLE:
             e = launch_gemm_simple(g, c->stream);
             launches = 1;
-            break;
-        case VLUT_ALGO_MMA:
-            if (!gemm_mma_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
-            e = launch_gemm_mma(g, c->stream, &launches);
             break;
         case VLUT_ALGO_TC:
             if (!gemm_tc_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;

@@ -8,8 +8,9 @@
 //     q  = clamp(round((double)x * is), -128, 127)     round = half away from zero
 //     scale = (float) s
 // FP64 throughput is irrelevant here (T*K elements); the kernel is a pure HBM/L2 stream: one CTA per token,
-// 128-bit loads of x, 32-bit stores of q in two layouts (row-major for TMA/tcgen05, mma.sync A-fragment order),
-// plus the per-(token, K-group) sums that undo the +1 offset of the u8 weight codes.
+// 128-bit loads of x, 32-bit stores of q in two layouts (row-major, and pre-swizzled K-major UMMA operand tiles
+// that a TMA bulk copy drops into shared memory ready for tcgen05.mma), plus per (token, K-group): the sum of q
+// that undoes the +1 offset of the u8 weight codes, and whether sum|q| rules out any int16 wrap.
 #include "vlut_common.cuh"
 
 namespace vlut {
@@ -22,14 +23,14 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
     const int tid = threadIdx.x;
     __shared__ float s_red[QT / 32];
     __shared__ int s_gsum[64];
+    __shared__ int s_gabs[64];
     __shared__ double s_is;
 
     const int64_t Kpad = a.Kpad;
-    const int MTall = (int) (a.Tpad / 16);
     const bool live = t < T;
     const float *xr = x + (int64_t) t * ldx;
 
-    for (int i = tid; i < 64; i += QT) s_gsum[i] = 0;
+    for (int i = tid; i < 64; i += QT) { s_gsum[i] = 0; s_gabs[i] = 0; }
 
     // pass 1: signed max
     float mx = -INFINITY;
@@ -77,18 +78,30 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         const uint32_t pk = (uint32_t) (qv[0] & 0xff) | ((uint32_t) (qv[1] & 0xff) << 8) |
                             ((uint32_t) (qv[2] & 0xff) << 16) | ((uint32_t) (qv[3] & 0xff) << 24);
         *reinterpret_cast<uint32_t *>(a.q_rm + (int64_t) t * Kpad + k) = pk;
-        // A-fragment order
-        const int64_t kb = k / TILE_K;
-        const int kk = (int) (k % TILE_K);
-        const int tig = kk / 32, r = kk % 32, h = r / 16, i = (r % 16) / 4;
-        const int mt = t / 16, tr = t % 16, g = tr % 8, hi = tr / 8;
-        const int64_t off = ((kb * MTall + mt) * 4 + i) * 512 + (4 * g + tig) * 16 + (2 * h + hi) * 4;
-        *reinterpret_cast<uint32_t *>(a.q_frag + off) = pk;
+        // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
+        const int64_t kb = k / BLOCK_K;
+        const int kk = (int) (k % BLOCK_K);
+        const int c = kk / 16;
+        const int64_t off = (kb * a.Tpad + t) * 128 + ((c ^ (t & 7)) << 4) + (kk & 15);
+        *reinterpret_cast<uint32_t *>(a.q_sw + off) = pk;
         const int sum = qv[0] + qv[1] + qv[2] + qv[3];
-        if (sum != 0) atomicAdd(&s_gsum[k / a.gsize], sum);
+        const int asum = abs(qv[0]) + abs(qv[1]) + abs(qv[2]) + abs(qv[3]);
+        if (asum != 0) {
+            atomicAdd(&s_gsum[k / a.gsize], sum);
+            atomicAdd(&s_gabs[k / a.gsize], asum);
+        }
     }
     __syncthreads();
     for (int i = tid; i < a.G; i += QT) a.gsum[(int64_t) t * a.G + i] = s_gsum[i];
+    if (tid == 0) {
+        int all = 0, safe = 1;
+        for (int i = 0; i < a.G; i++) {
+            all += s_gsum[i];
+            if (s_gabs[i] > 32767) safe = 0;
+        }
+        a.gsum_all[t] = all;
+        a.nowrap[t] = safe;
+    }
 }
 
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s) {

@@ -3,17 +3,15 @@
 // Device weight layout "T2" (what vlut_repack_weights produces and every GEMM kernel streams):
 //   * 2-bit codes c = w + 1 in {0,1,2}  (same 2 bits/weight as GGUF I2_*; I1_* grows from 1.6 to 2 bits)
 //   * matrix padded to Npad = ceil128(N) rows, Kpad = ceil128(K) columns, pad code = 1 (weight 0)
-//   * tile  (rt, kb) = 128 rows x 128 k = 4096 B, tiles ordered [rt][kb]  -> one 128-row strip is contiguous
-//   * tile  = 8 chunks of 16 rows, 512 B each
-//   * chunk = 32 "lanes" x 16 B; lane = 4*g + tig (g = 0..7, tig = 0..3), 4 words of 32 bits per lane
-//   * word  (rg, h) = 2*rg + h holds 16 consecutive k of ONE row:
-//         row_in_chunk = 8*rg + g,   k_in_block = 32*tig + 16*h + 4*i + j
-//     stored at byte j (0..3), bit pair i (0..3) of the word:  bits [8j+2i, 8j+2i+2)
-//     so  (word >> 2i) & 0x03030303  is 4 consecutive k of that row as 4 u8 -- one mma.sync B register, or
-//     one 32-bit quarter of a 16-byte run of the K-major tcgen05 A operand.
-// A warp reading a chunk with one 128-bit load per lane gets, for mma.sync.m16n8k32 with the weight rows as
-// the N dimension (B fragment: n = g, k-slot = 16*h + 4*tig + j), both B registers of k-step i for two
-// 8-row groups.  The k-slot <-> k permutation inside a 128-block is matched by the activation fragments.
+//   * strip rt = 128 consecutive rows; inside a strip the K axis is cut into 64-wide chunks kc; one
+//     (strip, chunk) tile is 128 rows x 16 bytes = 2048 B, row-major:   tile[row][16 B]
+//     tiles ordered [rt][kc]  ->  a strip (and any K-group of it) is one contiguous run of bytes (TMA bulk)
+//   * the 16 bytes of a row are 4 little-endian 32-bit words; word j holds 16 consecutive k of that row,
+//         k_in_chunk = 16*j + 4*i + b     stored at byte b (0..3), bit pair i (0..3):  bits [8b+2i, 8b+2i+2)
+//     so  (word >> 2i) & 0x03030303  is 4 consecutive k of the row as 4 u8 codes: one 32-bit column of the
+//     K-major tcgen05 A operand in TMEM (lane = row, column = k/4), or a quarter of a 16-byte swizzle chunk of
+//     the shared-memory A operand.  Thread m of a 128-thread decode group owns row m: its 128-bit shared-memory
+//     load is conflict-free and yields two K=32 MMA steps.
 #pragma once
 
 #include <cuda_runtime.h>
@@ -24,10 +22,10 @@
 namespace vlut {
 
 constexpr int TILE_ROWS = 128;
-constexpr int TILE_K = 128;
-constexpr int TILE_BYTES = TILE_ROWS * TILE_K / 4;  // 4096
-constexpr int CHUNK_ROWS = 16;
-constexpr int CHUNK_BYTES = 512;
+constexpr int CHUNK_K = 64;                       // k per tile
+constexpr int TILE_BYTES = TILE_ROWS * 16;        // 2048
+constexpr int BLOCK_K = 128;                      // k per pipeline stage (2 tiles)
+constexpr int BLOCK_BYTES = 2 * TILE_BYTES;       // 4096
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 __host__ __device__ inline int64_t round_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
@@ -47,34 +45,39 @@ __host__ __device__ inline int64_t gguf_row_bytes(int type, int64_t K) {
     return type_is_i1(type) ? (K / 20 * 4 + K % 20 / 4) : K / 4;
 }
 
-// byte offset of the word holding (row n, k) in a T2 buffer, plus byte j / bit-pair i inside it
+// byte offset of the word holding (row n, k) in a T2 buffer, and the bit position of k's code inside it
 __host__ __device__ inline int64_t t2_word_offset(int64_t n, int64_t k, int64_t Kpad) {
-    const int64_t rt = n / TILE_ROWS, kb = k / TILE_K;
-    const int r = (int) (n % TILE_ROWS), kk = (int) (k % TILE_K);
-    const int chunk = r / CHUNK_ROWS, rc = r % CHUNK_ROWS;
-    const int rg = rc / 8, g = rc % 8;
-    const int tig = kk / 32, h = (kk % 32) / 16;
-    return (rt * (Kpad / TILE_K) + kb) * TILE_BYTES + chunk * CHUNK_BYTES + (4 * g + tig) * 16 + (2 * rg + h) * 4;
+    const int64_t rt = n / TILE_ROWS, kc = k / CHUNK_K;
+    const int r = (int) (n % TILE_ROWS), j = (int) (k % CHUNK_K) / 16;
+    return (rt * (Kpad / CHUNK_K) + kc) * TILE_BYTES + r * 16 + j * 4;
 }
-__host__ __device__ inline int t2_shift(int64_t k) {  // bit position of the code of k inside its word
+__host__ __device__ inline int t2_shift(int64_t k) {
     const int kk = (int) (k % 16);
     return 8 * (kk % 4) + 2 * (kk / 4);
 }
 
+// token tile (UMMA N) used for a token count
+__host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : 128; }
+
 // ---- activation workspace -------------------------------------------------------------------------------
-// q_rm   int8  [Tpad][Kpad]      row-major (tcgen05 B operand via TMA, SIMPLE kernel), zero padded
-// q_frag int8  [Kpad/128][Tpad/16][4 k-steps][32 lanes][16 B]   mma.sync A fragments, per lane
-//              {a0,a1,a2,a3} = q[16mt+g][kq], q[16mt+g+8][kq], q[16mt+g][kq+16], q[16mt+g+8][kq+16],
-//              kq = 128*kb + 32*tig + 4*i + (0..3)
+// q_rm   int8  [Tpad][Kpad]   row-major, zero padded (SIMPLE kernel, test read-back)
+// q_sw   int8  [Kpad/128][Tpad][128 B]   K-major UMMA operand tiles, already 128B-swizzled: the 16-byte chunk c
+//              of token row t sits at chunk position c ^ (t % 8).  A bulk copy of NT consecutive rows lands in
+//              shared memory exactly as a SWIZZLE_128B K-major [NT x 128] s8 operand (8-row atoms of 1024 B).
 // scales f32   [Tpad]
-// gsum   int32 [Tpad][G]         sum_{k in group} q[t][k]   (the u8-code offset correction)
+// gsum   int32 [Tpad][G]      sum_{k in group} q[t][k]   (undoes the +1 offset of the u8 weight codes)
+// gsum_all int32 [Tpad]       sum over all groups
+// nowrap int32 [Tpad/NT]      1 if for every token of the tile and every group sum_k |q| <= 32767, i.e. no int16
+//                             wrap is possible whatever the weights are (full-K accumulation is then exact)
 struct ActView {
     int8_t *q_rm;
-    int8_t *q_frag;
+    int8_t *q_sw;
     float *scales;
     int32_t *gsum;
+    int32_t *gsum_all;
+    int32_t *nowrap;
     int64_t Kpad, Tpad;
-    int G, gsize;
+    int G, gsize, NT;
 };
 
 struct GemmArgs {
@@ -85,8 +88,8 @@ struct GemmArgs {
     int64_t K, N, T, Npad;
     int type;
     float w_scale;
-    int32_t *part;      // int32 [Tpad_ws][Npad] stream-K partial sums (self-cleaning, zero between calls)
-    int32_t *counters;  // per row-tile arrival counters (self-cleaning)
+    int32_t *part;      // int32 [Tpad][Npad] stream-K partial sums (self-cleaning: zero between calls)
+    int32_t *counters;  // per output-tile arrival counters (self-cleaning)
     int sm_count;
 };
 
@@ -97,8 +100,6 @@ cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, u
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s);
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
-cudaError_t launch_gemm_mma(const GemmArgs &g, cudaStream_t s, int *launches);
-bool gemm_mma_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);
 bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_lut(const GemmArgs &g, cudaStream_t s, int *launches);
