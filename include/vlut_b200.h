@@ -113,6 +113,10 @@ int vlut_debug_get_act(vlut_ctx *ctx, int64_t K, int64_t T, int8_t *q_host, floa
 /* decode a T2 buffer back to ternary int8 [N][K] on the host (round-trip check of the repacker) */
 int vlut_debug_unpack_t2(vlut_ctx *ctx, int type, int64_t K, int64_t N, const void *t2_dev, int8_t *w_host);
 
+/* cycle counters of the last tcgen05 GEMM launched with env VLUT_TC_DEBUG=1: [256 CTAs][4 roles][8] int64
+ * (roles: TMA producer, MMA issuer, decode warp 0, epilogue warp 0; slot 7 = role lifetime) */
+int vlut_debug_tc_counters(long long *out_host, int n_words);
+
 #ifdef __cplusplus
 }
 #endif

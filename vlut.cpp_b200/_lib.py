@@ -42,6 +42,7 @@ _SIGNATURES = {
     "vlut_pick_algo": (cint, [cint, i64, i64, i64]),
     "vlut_debug_get_act": (cint, [vp, i64, i64, vp, vp]),
     "vlut_debug_unpack_t2": (cint, [vp, cint, i64, i64, vp, vp]),
+    "vlut_debug_tc_counters": (cint, [vp, cint]),
 }
 
 

@@ -53,7 +53,7 @@ struct vlut_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    DevBuf q_rm, q_sw, scales, gsum, gsum_all, nowrap, part, counters, stage_x, stage_out, stage_w;
+    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_fast, tile_cnt, part, counters, stage_x, stage_out, stage_w;
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
@@ -147,8 +147,8 @@ void vlut_ctx_destroy(vlut_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf *bufs[] = {&c->q_rm,  &c->q_sw,     &c->scales,  &c->gsum,      &c->gsum_all, &c->nowrap,
-                      &c->part,  &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
+    DevBuf *bufs[] = {&c->q_rm,     &c->q_sw, &c->scales,   &c->gpre,    &c->nowrap,    &c->tile_fast,
+                      &c->tile_cnt, &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
     for (DevBuf *b : bufs) b->release();
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -241,15 +241,19 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
     if (c->q_rm.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->q_sw.reserve((size_t) (Tpad * Kpad)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->scales.reserve((size_t) Tpad * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
-    if (c->gsum.reserve((size_t) Tpad * G * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
-    if (c->gsum_all.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->gpre.reserve((size_t) Tpad * (G + 1) * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->nowrap.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->tile_fast.reserve((size_t) (Tpad / 16) * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
+    bool grew = false;
+    if (c->tile_cnt.reserve((size_t) (Tpad / 16) * sizeof(int32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (grew && cudaMemsetAsync(c->tile_cnt.p, 0, c->tile_cnt.cap, c->stream) != cudaSuccess) return VLUT_ERR_CUDA;
     c->act.q_rm = (int8_t *) c->q_rm.p;
     c->act.q_sw = (int8_t *) c->q_sw.p;
     c->act.scales = (float *) c->scales.p;
-    c->act.gsum = (int32_t *) c->gsum.p;
-    c->act.gsum_all = (int32_t *) c->gsum_all.p;
+    c->act.gpre = (int32_t *) c->gpre.p;
     c->act.nowrap = (int32_t *) c->nowrap.p;
+    c->act.tile_fast = (int32_t *) c->tile_fast.p;
+    c->act.tile_cnt = (int32_t *) c->tile_cnt.p;
     c->act.Kpad = Kpad;
     c->act.Tpad = Tpad;
     c->act.G = G;
@@ -304,11 +308,11 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
     g.sm_count = c->sm_count;
 
     if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_LUT) {
-        // stream-K workspace: zeroed once at (re)allocation, the kernels leave it zero
+        // stream-K workspace: two private partial-tile slots per persistent CTA (no initialisation needed) and
+        // self-resetting per-tile arrival counters (zeroed once at (re)allocation)
         bool grew = false;
-        const size_t pb = (size_t) (c->act.Tpad * g.Npad) * sizeof(int32_t);
-        if (c->part.reserve(pb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
-        if (grew) CK(cudaMemsetAsync(c->part.p, 0, c->part.cap, c->stream));
+        const size_t pb = (size_t) c->sm_count * 2 * 128 * 128 * sizeof(int32_t);
+        if (c->part.reserve(pb) != cudaSuccess) return VLUT_ERR_NOMEM;
         const size_t cb = (size_t) ((g.Npad / TILE_ROWS) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));

@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         const int64_t kb = k / BLOCK_K;
         const int kk = (int) (k % BLOCK_K);
         const int c = kk / 16;
-        const int64_t off = (kb * a.Tpad + t) * 128 + ((c ^ (t & 7)) << 4) + (kk & 15);
+        const int64_t off = (((int64_t) (t / a.NT) * (Kpad / BLOCK_K) + kb) * a.NT + (t % a.NT)) * 128 + ((c ^ (t & 7)) << 4) + (kk & 15);
         *reinterpret_cast<uint32_t *>(a.q_sw + off) = pk;
         const int sum = qv[0] + qv[1] + qv[2] + qv[3];
         const int asum = abs(qv[0]) + abs(qv[1]) + abs(qv[2]) + abs(qv[3]);
@@ -92,15 +92,32 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         }
     }
     __syncthreads();
-    for (int i = tid; i < a.G; i += QT) a.gsum[(int64_t) t * a.G + i] = s_gsum[i];
+    __shared__ int s_islast;
     if (tid == 0) {
-        int all = 0, safe = 1;
+        int run = 0, safe = 1;
+        int32_t *pre = a.gpre + (int64_t) t * (a.G + 1);
         for (int i = 0; i < a.G; i++) {
-            all += s_gsum[i];
+            pre[i] = run;
+            run += s_gsum[i];
             if (s_gabs[i] > 32767) safe = 0;
         }
-        a.gsum_all[t] = all;
+        pre[a.G] = run;
         a.nowrap[t] = safe;
+        // last CTA of the token tile reduces the per-token flags to one flag per tile
+        __threadfence();
+        const int old = atomicAdd(a.tile_cnt + t / a.NT, 1);
+        s_islast = (old == a.NT - 1);
+    }
+    __syncthreads();
+    if (s_islast) {
+        __threadfence();
+        const int tile = t / a.NT;
+        int ok = (tid < a.NT) ? __ldcg(a.nowrap + tile * a.NT + tid) : 1;
+        ok = __syncthreads_and(ok);
+        if (tid == 0) {
+            a.tile_fast[tile] = ok;
+            a.tile_cnt[tile] = 0;
+        }
     }
 }
 

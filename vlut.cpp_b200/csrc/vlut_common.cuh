@@ -61,21 +61,25 @@ __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <
 
 // ---- activation workspace -------------------------------------------------------------------------------
 // q_rm   int8  [Tpad][Kpad]   row-major, zero padded (SIMPLE kernel, test read-back)
-// q_sw   int8  [Kpad/128][Tpad][128 B]   K-major UMMA operand tiles, already 128B-swizzled: the 16-byte chunk c
-//              of token row t sits at chunk position c ^ (t % 8).  A bulk copy of NT consecutive rows lands in
-//              shared memory exactly as a SWIZZLE_128B K-major [NT x 128] s8 operand (8-row atoms of 1024 B).
+// q_sw   int8  [Tpad/NT][Kpad/128][NT][128 B]   K-major UMMA operand tiles, already 128B-swizzled: the 16-byte
+//              chunk c of token row t sits at chunk position c ^ (t % 8).  One [NT][128 B] tile dropped into shared
+//              memory by a bulk copy IS a SWIZZLE_128B K-major [NT x 128] s8 operand (8-row atoms of 1024 B); the
+//              tiles of consecutive 128-k sub-blocks of one token tile are contiguous (one copy per stage).
 // scales f32   [Tpad]
-// gsum   int32 [Tpad][G]      sum_{k in group} q[t][k]   (undoes the +1 offset of the u8 weight codes)
-// gsum_all int32 [Tpad]       sum over all groups
-// nowrap int32 [Tpad/NT]      1 if for every token of the tile and every group sum_k |q| <= 32767, i.e. no int16
-//                             wrap is possible whatever the weights are (full-K accumulation is then exact)
+// gpre   int32 [Tpad][G+1]    exclusive prefix sums over the K-groups of sum_{k in group} q[t][k]: the code-offset
+//                             correction of groups [a, b] is gpre[b+1] - gpre[a]  (undoes the +1 of the u8 codes)
+// nowrap int32 [Tpad]         1 if for every group of token t sum_k |q| <= 32767, i.e. no int16 wrap is possible
+//                             whatever the weights are (full-K accumulation is then exact)
+// tile_fast int32 [Tpad/NT]   AND of nowrap over the token tile (written by the last quantise CTA of the tile)
+// tile_cnt  int32 [Tpad/NT]   arrival counters for that reduction (self-resetting)
 struct ActView {
     int8_t *q_rm;
     int8_t *q_sw;
     float *scales;
-    int32_t *gsum;
-    int32_t *gsum_all;
+    int32_t *gpre;
     int32_t *nowrap;
+    int32_t *tile_fast;
+    int32_t *tile_cnt;
     int64_t Kpad, Tpad;
     int G, gsize, NT;
 };
@@ -88,7 +92,7 @@ struct GemmArgs {
     int64_t K, N, T, Npad;
     int type;
     float w_scale;
-    int32_t *part;      // int32 [Tpad][Npad] stream-K partial sums (self-cleaning: zero between calls)
+    int32_t *part;      // int32 [CTAs][2 slots][NT][128] stream-K partial tiles (no initialisation needed)
     int32_t *counters;  // per output-tile arrival counters (self-cleaning)
     int sm_count;
 };
