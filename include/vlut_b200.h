@@ -67,6 +67,15 @@ int   vlut_ctx_sync(vlut_ctx *ctx);
 /* number of this library's kernels launched through ctx so far (bench.py's gpu_launches) */
 int64_t vlut_ctx_launch_count(const vlut_ctx *ctx);
 
+/* ---- device memory (so that hosts of this ABI -- the ggml backend plugin, FFI bindings -- need no CUDA headers) --
+ * Back ggml_backend_buffer_type_i.alloc_buffer / ggml_backend_buffer_i.{free_buffer,set_tensor,get_tensor,
+ * memset_tensor,clear} (ggml/src/ggml-backend-impl.h:17-58).  Copies are synchronous on return. */
+int vlut_dev_malloc(int device, size_t nbytes, void **out_dev);
+int vlut_dev_free(int device, void *dev_ptr);
+int vlut_dev_memcpy_h2d(vlut_ctx *ctx, void *dst_dev, const void *src_host, size_t nbytes);
+int vlut_dev_memcpy_d2h(vlut_ctx *ctx, void *dst_host, const void *src_dev, size_t nbytes);
+int vlut_dev_memset(vlut_ctx *ctx, void *dst_dev, int value, size_t nbytes);
+
 /* ---- weights ------------------------------------------------------------------------------------------- */
 /* bytes of the GGUF-packed tensor = ggml_nbytes (ggml/src/ggml.c:1286-1289, :1326-1335); 0 if invalid */
 size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N);

@@ -1,0 +1,99 @@
+"""The ggml backend plugin (libggml-vlut-b200.so) exercised through the reference's own ggml API.
+
+oracle/_ref/{libggml-base,libggml,libggml-cpu}.so are the reference's UNMODIFIED ggml sources compiled in place by
+oracle/Makefile; tests/harness/ggml_harness.cpp (-> oracle/_ref/vlut_ggml_harness) is a small driver that loads the
+plugin with ggml_backend_load() and runs GGML_OP_MUL_MAT graphs the way the reference's tools do.
+"""
+import ctypes
+import os
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+ROOT = Path(__file__).resolve().parent.parent
+REFDIR = ROOT / "oracle" / "_ref"
+HARNESS = REFDIR / "vlut_ggml_harness"
+PLUGIN = ROOT / "vlut.cpp_b200" / "csrc" / "build" / "libggml-vlut-b200.so"
+CPU_BACKEND = REFDIR / "libggml-cpu.so"
+
+
+def need_artifacts():
+    missing = [p for p in (HARNESS, PLUGIN, CPU_BACKEND) if not p.exists()]
+    if missing:
+        pytest.skip(f"not built (needs /root/reference at build time): {missing}")
+
+
+def bits(a):
+    return np.ascontiguousarray(a).view(np.uint32)
+
+
+def run_harness(tmp_path, mode, type_, K, N, T, packed, x):
+    (tmp_path / "w.bin").write_bytes(packed.tobytes())
+    (tmp_path / "x.bin").write_bytes(np.ascontiguousarray(x, dtype=np.float32).tobytes())
+    cmd = [str(HARNESS), str(PLUGIN), mode, str(type_), str(K), str(N), str(T), str(tmp_path / "w.bin"), str(tmp_path / "x.bin"),
+           str(tmp_path / "out.bin")]
+    if mode == "sched":
+        cmd.append(str(CPU_BACKEND))
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    return r
+
+
+def test_plugin_exports_ggml_entry_points():
+    need_artifacts()
+    # resolve against libggml-base like the host process would
+    ctypes.CDLL(str(REFDIR / "libggml-base.so"), mode=ctypes.RTLD_GLOBAL)
+    lib = ctypes.CDLL(str(PLUGIN))
+    assert hasattr(lib, "ggml_backend_init") and hasattr(lib, "ggml_backend_score")
+    lib.ggml_backend_score.restype = ctypes.c_int
+    import torch
+    score = lib.ggml_backend_score()
+    assert (score > 0) == torch.cuda.is_available()
+
+
+def test_plugin_is_refused_without_gpu(tmp_path, orc):
+    """ggml_backend_load() asks ggml_backend_score(): 0 on a box without an sm_100 GPU -> not loaded, no CPU fallback."""
+    need_artifacts()
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    w = O.make_ternary(16, 512, seed=1)
+    r = run_harness(tmp_path, "direct", O.I2_V_4, 512, 16, 2, orc.pack(O.I2_V_4, w), O.make_acts(2, 512))
+    assert r.returncode == 3, r.stdout
+    assert "failed" in r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("type_,K,N,T", [(O.I2_V_4, 4096, 512, 8), (O.I2_V_4, 2048, 300, 70), (O.I1_V_2, 3200, 384, 33),
+                                         (O.I2_V, 1024, 128, 1), (O.I2_V_8, 2048, 256, 130), (O.I1_V, 1300, 64, 17),
+                                         (O.I1_V_2, 4096, 128, 5)])
+def test_mul_mat_through_ggml_direct(tmp_path, orc, type_, K, N, T):
+    need_artifacts()
+    w = O.make_ternary(N, K, seed=K + T)
+    x = O.make_acts(T, K, seed=N, kind="outlier")
+    packed = orc.pack(type_, w)
+    r = run_harness(tmp_path, "direct", type_, K, N, T, packed, x)
+    assert r.returncode == 0, r.stdout
+    assert "VLUT_B200" in r.stdout
+    out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(T, N)
+    assert np.array_equal(bits(out), bits(orc.mul_mat(type_, packed, x, N)))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("type_,K,N,T", [(O.I2_V_4, 4096, 512, 16), (O.I1_V_2, 3200, 256, 40), (O.I2_V_4, 2048, 1024, 512)])
+def test_mul_mat_through_ggml_sched(tmp_path, orc, type_, K, N, T):
+    """Weight in the plugin's buffer, everything else on the CPU backend: ggml_backend_sched must route the MUL_MAT to
+    the plugin (supports_op / supports_buft) and copy activations in and results out around the split."""
+    need_artifacts()
+    w = O.make_ternary(N, K, seed=K + T)
+    x = O.make_acts(T, K, seed=N)
+    packed = orc.pack(type_, w)
+    r = run_harness(tmp_path, "sched", type_, K, N, T, packed, x)
+    assert r.returncode == 0, r.stdout
+    assert "mul_mat ran on 'VLUT_B200_0'" in r.stdout, r.stdout
+    out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(T, N)
+    expect = orc.mul_mat(type_, packed, x, N) + np.float32(1.0)
+    assert np.array_equal(bits(out), bits(expect))

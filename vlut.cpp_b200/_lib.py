@@ -30,6 +30,11 @@ _SIGNATURES = {
     "vlut_ctx_sync": (cint, [vp]),
     "vlut_ctx_launch_count": (i64, [vp]),
     "vlut_ctx_last_algo": (cint, [vp]),
+    "vlut_dev_malloc": (cint, [cint, C.c_size_t, C.POINTER(vp)]),
+    "vlut_dev_free": (cint, [cint, vp]),
+    "vlut_dev_memcpy_h2d": (cint, [vp, vp, vp, C.c_size_t]),
+    "vlut_dev_memcpy_d2h": (cint, [vp, vp, vp, C.c_size_t]),
+    "vlut_dev_memset": (cint, [vp, vp, cint, C.c_size_t]),
     "vlut_gguf_nbytes": (C.c_size_t, [cint, i64, i64]),
     "vlut_repacked_nbytes": (C.c_size_t, [cint, i64, i64]),
     "vlut_repack_weights": (cint, [vp, cint, i64, i64, vp, vp]),

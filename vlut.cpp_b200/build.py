@@ -66,10 +66,13 @@ def build_lib(force: bool = False, verbose: bool = False) -> Path:
 def build_all(force: bool = False, verbose: bool = False) -> dict:
     built = {"lib": str(build_lib(force=force, verbose=verbose))}
     try:
-        from . import build_ggml  # noqa: WPS433  (optional: needs the ggml headers of the reference tree)
-        built.update(build_ggml.build(force=force))
-    except ImportError:
-        pass
+        from . import build_ggml  # package import (vlut_b200.build)
+    except ImportError:  # run as a script
+        import importlib.util
+        spec = importlib.util.spec_from_file_location("build_ggml", HERE / "build_ggml.py")
+        build_ggml = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(build_ggml)
+    built.update(build_ggml.build(force=force))
     return built
 
 

@@ -165,6 +165,50 @@ int vlut_ctx_sync(vlut_ctx *c) {
 int64_t vlut_ctx_launch_count(const vlut_ctx *c) { return c ? c->launches : 0; }
 int vlut_ctx_last_algo(const vlut_ctx *c) { return c ? c->last_algo : 0; }
 
+int vlut_dev_malloc(int device, size_t nbytes, void **out_dev) {
+    if (!out_dev) return VLUT_ERR_INVALID;
+    *out_dev = nullptr;
+    CK(cudaSetDevice(device));
+    cudaError_t e = cudaMalloc(out_dev, nbytes ? nbytes : 1);
+    if (e == cudaErrorMemoryAllocation) {
+        cudaGetLastError();
+        return VLUT_ERR_NOMEM;
+    }
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc");
+    return VLUT_OK;
+}
+
+int vlut_dev_free(int device, void *dev_ptr) {
+    if (!dev_ptr) return VLUT_OK;
+    CK(cudaSetDevice(device));
+    CK(cudaFree(dev_ptr));
+    return VLUT_OK;
+}
+
+int vlut_dev_memcpy_h2d(vlut_ctx *c, void *dst_dev, const void *src_host, size_t nbytes) {
+    if (!c || (nbytes && (!dst_dev || !src_host))) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst_dev, src_host, nbytes, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
+int vlut_dev_memcpy_d2h(vlut_ctx *c, void *dst_host, const void *src_dev, size_t nbytes) {
+    if (!c || (nbytes && (!dst_host || !src_dev))) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemcpyAsync(dst_host, src_dev, nbytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
+int vlut_dev_memset(vlut_ctx *c, void *dst_dev, int value, size_t nbytes) {
+    if (!c || (nbytes && !dst_dev)) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    CK(cudaMemsetAsync(dst_dev, value, nbytes, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    return VLUT_OK;
+}
+
 static int check_shape(int type, int64_t K, int64_t N);
 
 size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N) {

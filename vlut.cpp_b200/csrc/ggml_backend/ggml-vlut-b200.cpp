@@ -1,0 +1,432 @@
+// ggml-vlut-b200.cpp -- out-of-tree ggml backend for the Vec-LUT ternary MUL_MAT path on NVIDIA B200 (sm_100a).
+//
+// Built against the UNMODIFIED ggml headers of spinal-cord/vlut.cpp (ggml/include, ggml/src/ggml-backend-impl.h,
+// GGML_BACKEND_API_VERSION 2) into libggml-vlut-b200.so, which exports ggml_backend_init / ggml_backend_score and is
+// picked up by ggml_backend_load(), i.e. by every tool of the reference when GGML_BACKEND_PATH points at it
+// (ggml/src/ggml-backend-reg.cpp:627-631; llama-bench.cpp:2020; common/arg.cpp:874; tests/test-vlut-gemm.cpp:853).
+//
+// Scope: supports_op is limited to GGML_OP_MUL_MAT whose src0 is a 2-D tensor of a vlut type
+// (I2_V, I2_V_4, I2_V_8, I1_V, I1_V_2) living in this backend's buffer type, with f32 src1 and f32 dst -- the op the
+// CPU backend runs in ggml_compute_forward_mul_mat's Vec-LUT branch (ggml/src/ggml-cpu/ggml-cpu.c:1372-1421).
+// The buffer type repacks GGUF weights into the HBM-coalesced tiled 2-bit layout at load (set_tensor hook).  All
+// arithmetic happens in libvlut_b200.so (include/vlut_b200.h); this file contains no CUDA.
+//
+// The device reports GGML_BACKEND_DEVICE_TYPE_ACCEL so that libllama offers its buffer type to every weight through
+// the CPU buffer-type list (src/llama-model.cpp:329-339) and adds the backend to the scheduler
+// (src/llama-context.cpp:198-208) while KV cache and all other ops stay on the CPU backend.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "ggml-backend-impl.h"
+#include "ggml-backend.h"
+#include "ggml-impl.h"
+#include "ggml.h"
+
+#include "../../../include/vlut_b200.h"
+
+namespace {
+
+bool is_vlut_type(enum ggml_type t) {
+    return t == GGML_TYPE_I2_V || t == GGML_TYPE_I2_V_4 || t == GGML_TYPE_I2_V_8 || t == GGML_TYPE_I1_V ||
+           t == GGML_TYPE_I1_V_2;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// device / registry state (static, never freed: the registry leaks handles on purpose, ggml-backend-reg.cpp:229-236)
+// ---------------------------------------------------------------------------------------------------------------
+struct device_ctx {
+    int device = 0;
+    std::string name;
+    std::string description;
+    vlut_ctx *io_ctx = nullptr;  // context used by buffer uploads / downloads
+    std::mutex io_mutex;
+    ggml_backend_buffer_type buft{};
+};
+
+struct buffer_ctx {
+    device_ctx *dev = nullptr;
+    void *base = nullptr;
+};
+
+struct backend_ctx {
+    device_ctx *dev = nullptr;
+    vlut_ctx *ctx = nullptr;
+    std::string name;
+};
+
+vlut_ctx *io_ctx(device_ctx *d) {
+    if (!d->io_ctx) {
+        if (vlut_ctx_create(d->device, nullptr, &d->io_ctx) != VLUT_OK) {
+            GGML_LOG_ERROR("%s: vlut_ctx_create failed: %s\n", __func__, vlut_last_cuda_error());
+            return nullptr;
+        }
+    }
+    return d->io_ctx;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// buffer
+// ---------------------------------------------------------------------------------------------------------------
+void buffer_free(ggml_backend_buffer_t buffer) {
+    buffer_ctx *b = (buffer_ctx *) buffer->context;
+    vlut_dev_free(b->dev->device, b->base);
+    delete b;
+}
+
+void *buffer_get_base(ggml_backend_buffer_t buffer) { return ((buffer_ctx *) buffer->context)->base; }
+
+void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor *tensor, uint8_t value, size_t offset, size_t size) {
+    buffer_ctx *b = (buffer_ctx *) buffer->context;
+    std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    vlut_dev_memset(io_ctx(b->dev), (char *) tensor->data + offset, value, size);
+}
+
+// The repack hook.  libllama uploads a weight with ONE whole-tensor set_tensor when the device reports no
+// async/host_buffer/events caps (src/llama-model-loader.cpp:1003-1007), so the full GGUF-layout tensor is seen here.
+void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor *tensor, const void *data, size_t offset, size_t size) {
+    buffer_ctx *b = (buffer_ctx *) buffer->context;
+    std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    vlut_ctx *c = io_ctx(b->dev);
+    if (is_vlut_type(tensor->type)) {
+        GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "vlut weights must be uploaded whole (they are repacked)");
+        GGML_ASSERT(ggml_n_dims(tensor) <= 2);
+        const int rc = vlut_upload_weights(c, (int) tensor->type, tensor->ne[0], tensor->ne[1], data, tensor->data);
+        if (rc != VLUT_OK) GGML_ABORT("vlut_upload_weights failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
+        return;
+    }
+    const int rc = vlut_dev_memcpy_h2d(c, (char *) tensor->data + offset, data, size);
+    if (rc != VLUT_OK) GGML_ABORT("H2D copy failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
+}
+
+void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor *tensor, void *data, size_t offset, size_t size) {
+    buffer_ctx *b = (buffer_ctx *) buffer->context;
+    std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    GGML_ASSERT(!is_vlut_type(tensor->type) && "vlut weights are stored repacked and cannot be read back in GGUF layout");
+    const int rc = vlut_dev_memcpy_d2h(io_ctx(b->dev), data, (const char *) tensor->data + offset, size);
+    if (rc != VLUT_OK) GGML_ABORT("D2H copy failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
+}
+
+void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
+    buffer_ctx *b = (buffer_ctx *) buffer->context;
+    std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    vlut_dev_memset(io_ctx(b->dev), b->base, value, buffer->size);
+}
+
+const ggml_backend_buffer_i buffer_iface = {
+    /* .free_buffer   = */ buffer_free,
+    /* .get_base      = */ buffer_get_base,
+    /* .init_tensor   = */ nullptr,
+    /* .memset_tensor = */ buffer_memset_tensor,
+    /* .set_tensor    = */ buffer_set_tensor,
+    /* .get_tensor    = */ buffer_get_tensor,
+    /* .cpy_tensor    = */ nullptr,
+    /* .clear         = */ buffer_clear,
+    /* .reset         = */ nullptr,
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// buffer type
+// ---------------------------------------------------------------------------------------------------------------
+const char *buft_get_name(ggml_backend_buffer_type_t buft) { return ((device_ctx *) buft->context)->name.c_str(); }
+
+ggml_backend_buffer_t buft_alloc_buffer(ggml_backend_buffer_type_t buft, size_t size) {
+    device_ctx *d = (device_ctx *) buft->context;
+    void *p = nullptr;
+    const int rc = vlut_dev_malloc(d->device, size, &p);
+    if (rc != VLUT_OK) {
+        GGML_LOG_ERROR("%s: allocating %.2f MiB on %s failed: %s\n", __func__, size / 1024.0 / 1024.0, d->name.c_str(),
+                       vlut_error_string(rc));
+        return nullptr;  // contract: NULL on OOM
+    }
+    buffer_ctx *b = new buffer_ctx{d, p};
+    return ggml_backend_buffer_init(buft, buffer_iface, b, size);
+}
+
+size_t buft_get_alignment(ggml_backend_buffer_type_t) { return 1024; }
+
+// vlut weights are stored in the tiled 2-bit layout: padded to 128x128 tiles, and 2 bits/weight for the 1.6-bit I1 types
+size_t buft_get_alloc_size(ggml_backend_buffer_type_t, const ggml_tensor *tensor) {
+    const size_t nb = ggml_nbytes(tensor);
+    if (is_vlut_type(tensor->type) && ggml_n_dims(tensor) <= 2) {
+        const size_t rp = vlut_repacked_nbytes((int) tensor->type, tensor->ne[0], tensor->ne[1]);
+        return rp > nb ? rp : nb;
+    }
+    return nb;
+}
+
+bool buft_is_host(ggml_backend_buffer_type_t) { return false; }
+
+const ggml_backend_buffer_type_i buft_iface = {
+    /* .get_name       = */ buft_get_name,
+    /* .alloc_buffer   = */ buft_alloc_buffer,
+    /* .get_alignment  = */ buft_get_alignment,
+    /* .get_max_size   = */ nullptr,
+    /* .get_alloc_size = */ buft_get_alloc_size,
+    /* .is_host        = */ buft_is_host,
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// backend (stream)
+// ---------------------------------------------------------------------------------------------------------------
+const char *backend_get_name(ggml_backend_t backend) { return ((backend_ctx *) backend->context)->name.c_str(); }
+
+void backend_free(ggml_backend_t backend) {
+    backend_ctx *b = (backend_ctx *) backend->context;
+    vlut_ctx_destroy(b->ctx);
+    delete b;
+    delete backend;
+}
+
+void backend_synchronize(ggml_backend_t backend) { vlut_ctx_sync(((backend_ctx *) backend->context)->ctx); }
+
+// GGML_OP_MUL_MAT(vlut weight [K,N], f32 [K,T,...]) -> f32 [N,T,...]: the Vec-LUT branch of
+// ggml_compute_forward_mul_mat (ggml-cpu.c:1372-1421): quantise activations per token, Vec-LUT GEMM, fp32 epilogue.
+ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst) {
+    const ggml_tensor *src0 = dst->src[0];
+    const ggml_tensor *src1 = dst->src[1];
+    const int64_t K = src0->ne[0], N = src0->ne[1], T = src1->ne[1];
+    GGML_ASSERT(src1->ne[0] == K && dst->ne[0] == N && dst->ne[1] == T);
+    GGML_ASSERT(src1->nb[0] == sizeof(float) && dst->nb[0] == sizeof(float));
+    for (int64_t i3 = 0; i3 < src1->ne[3]; i3++) {
+        for (int64_t i2 = 0; i2 < src1->ne[2]; i2++) {
+            const float *x = (const float *) ((const char *) src1->data + i2 * src1->nb[2] + i3 * src1->nb[3]);
+            float *out = (float *) ((char *) dst->data + i2 * dst->nb[2] + i3 * dst->nb[3]);
+            const int rc = vlut_mul_mat(b->ctx, (int) src0->type, K, N, T, src0->data, x, (int64_t) (src1->nb[1] / sizeof(float)),
+                                        out, (int64_t) (dst->nb[1] / sizeof(float)), 1.0f, VLUT_ALGO_AUTO);
+            if (rc != VLUT_OK) {
+                GGML_LOG_ERROR("%s: vlut_mul_mat(%s) failed: %s (%s)\n", __func__, dst->name, vlut_error_string(rc),
+                               vlut_last_cuda_error());
+                return rc == VLUT_ERR_NOMEM ? GGML_STATUS_ALLOC_FAILED : GGML_STATUS_FAILED;
+            }
+        }
+    }
+    return GGML_STATUS_SUCCESS;
+}
+
+ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
+    backend_ctx *b = (backend_ctx *) backend->context;
+    for (int i = 0; i < cgraph->n_nodes; i++) {
+        ggml_tensor *node = cgraph->nodes[i];
+        switch (node->op) {
+            case GGML_OP_MUL_MAT: {
+                const ggml_status st = compute_mul_mat(b, node);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_NONE:
+            case GGML_OP_RESHAPE:
+            case GGML_OP_VIEW:
+            case GGML_OP_PERMUTE:
+            case GGML_OP_TRANSPOSE:
+                break;
+            default:
+                GGML_LOG_ERROR("%s: unsupported op %s\n", __func__, ggml_op_desc(node));
+                return GGML_STATUS_FAILED;
+        }
+    }
+    // results are read back through get_tensor (which synchronises its own stream): make them visible first
+    if (vlut_ctx_sync(b->ctx) != VLUT_OK) return GGML_STATUS_FAILED;
+    return GGML_STATUS_SUCCESS;
+}
+
+const ggml_backend_i backend_iface = {
+    /* .get_name           = */ backend_get_name,
+    /* .free               = */ backend_free,
+    /* .set_tensor_async   = */ nullptr,
+    /* .get_tensor_async   = */ nullptr,
+    /* .cpy_tensor_async   = */ nullptr,
+    /* .synchronize        = */ backend_synchronize,
+    /* .graph_plan_create  = */ nullptr,
+    /* .graph_plan_free    = */ nullptr,
+    /* .graph_plan_update  = */ nullptr,
+    /* .graph_plan_compute = */ nullptr,
+    /* .graph_compute      = */ backend_graph_compute,
+    /* .event_record       = */ nullptr,
+    /* .event_wait         = */ nullptr,
+    /* .graph_optimize     = */ nullptr,
+};
+
+ggml_guid_t backend_guid() {
+    static ggml_guid guid = {0x76, 0x6c, 0x75, 0x74, 0x2d, 0x62, 0x32, 0x30, 0x30, 0x2d, 0x73, 0x6d, 0x31, 0x30, 0x30, 0x61};
+    return &guid;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// device
+// ---------------------------------------------------------------------------------------------------------------
+const char *dev_get_name(ggml_backend_dev_t dev) { return ((device_ctx *) dev->context)->name.c_str(); }
+const char *dev_get_description(ggml_backend_dev_t dev) { return ((device_ctx *) dev->context)->description.c_str(); }
+
+void dev_get_memory(ggml_backend_dev_t dev, size_t *free, size_t *total) {
+    device_ctx *d = (device_ctx *) dev->context;
+    *free = *total = 0;
+    vlut_device_info(d->device, nullptr, 0, free, total, nullptr);
+}
+
+enum ggml_backend_dev_type dev_get_type(ggml_backend_dev_t) { return GGML_BACKEND_DEVICE_TYPE_ACCEL; }
+
+void dev_get_props(ggml_backend_dev_t dev, ggml_backend_dev_props *props) {
+    props->name = dev_get_name(dev);
+    props->description = dev_get_description(dev);
+    props->type = dev_get_type(dev);
+    props->device_id = nullptr;
+    dev_get_memory(dev, &props->memory_free, &props->memory_total);
+    // no async / host buffer / events: makes libllama upload every weight with one whole-tensor set_tensor (repack hook)
+    props->caps = {/* .async = */ false, /* .host_buffer = */ false, /* .buffer_from_host_ptr = */ false, /* .events = */ false};
+}
+
+ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char * /*params*/) {
+    device_ctx *d = (device_ctx *) dev->context;
+    backend_ctx *b = new backend_ctx;
+    b->dev = d;
+    b->name = d->name;
+    const int rc = vlut_ctx_create(d->device, nullptr, &b->ctx);
+    if (rc != VLUT_OK) {
+        GGML_LOG_ERROR("%s: vlut_ctx_create(%d) failed: %s (%s)\n", __func__, d->device, vlut_error_string(rc), vlut_last_cuda_error());
+        delete b;
+        return nullptr;
+    }
+    return new ggml_backend{
+        /* .guid    = */ backend_guid(),
+        /* .iface   = */ backend_iface,
+        /* .device  = */ dev,
+        /* .context = */ b,
+    };
+}
+
+ggml_backend_buffer_type_t dev_get_buffer_type(ggml_backend_dev_t dev) { return &((device_ctx *) dev->context)->buft; }
+
+// libllama probes with a dummy MUL_MAT(w, f32[K,512]) whose w->buffer is a 0-byte buffer of the candidate buft
+// (src/llama-model.cpp:172-306): decide from the op's types and from where src0 lives.
+bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor *op) {
+    device_ctx *d = (device_ctx *) dev->context;
+    switch (op->op) {
+        case GGML_OP_NONE:
+        case GGML_OP_RESHAPE:
+        case GGML_OP_VIEW:
+        case GGML_OP_PERMUTE:
+        case GGML_OP_TRANSPOSE:
+            return true;
+        case GGML_OP_MUL_MAT: {
+            const ggml_tensor *src0 = op->src[0];
+            const ggml_tensor *src1 = op->src[1];
+            if (!src0 || !src1) return false;
+            if (!is_vlut_type(src0->type)) return false;
+            if (src0->ne[2] != 1 || src0->ne[3] != 1) return false;
+            if (src1->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
+            if (src1->nb[0] != sizeof(float) || src1->nb[1] % sizeof(float) != 0) return false;
+            if (vlut_gguf_nbytes((int) src0->type, src0->ne[0], src0->ne[1]) == 0) return false;
+            // the weight must live (or be about to live) in our buffer type: it is stored repacked there
+            if (src0->buffer && src0->buffer->buft != &d->buft) return false;
+            return true;
+        }
+        default:
+            return false;
+    }
+}
+
+bool dev_supports_buft(ggml_backend_dev_t dev, ggml_backend_buffer_type_t buft) {
+    return buft == &((device_ctx *) dev->context)->buft;
+}
+
+const ggml_backend_device_i device_iface = {
+    /* .get_name             = */ dev_get_name,
+    /* .get_description      = */ dev_get_description,
+    /* .get_memory           = */ dev_get_memory,
+    /* .get_type             = */ dev_get_type,
+    /* .get_props            = */ dev_get_props,
+    /* .init_backend         = */ dev_init_backend,
+    /* .get_buffer_type      = */ dev_get_buffer_type,
+    /* .get_host_buffer_type = */ nullptr,
+    /* .buffer_from_host_ptr = */ nullptr,
+    /* .supports_op          = */ dev_supports_op,
+    /* .supports_buft        = */ dev_supports_buft,
+    /* .offload_op           = */ nullptr,
+    /* .event_new            = */ nullptr,
+    /* .event_free           = */ nullptr,
+    /* .event_synchronize    = */ nullptr,
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// registry
+// ---------------------------------------------------------------------------------------------------------------
+struct reg_ctx {
+    std::vector<device_ctx *> devices;
+    std::vector<ggml_backend_device> handles;
+};
+
+const char *reg_get_name(ggml_backend_reg_t) { return "VLUT_B200"; }
+size_t reg_get_device_count(ggml_backend_reg_t reg) { return ((reg_ctx *) reg->context)->handles.size(); }
+ggml_backend_dev_t reg_get_device(ggml_backend_reg_t reg, size_t index) {
+    reg_ctx *r = (reg_ctx *) reg->context;
+    GGML_ASSERT(index < r->handles.size());
+    return &r->handles[index];
+}
+void *reg_get_proc_address(ggml_backend_reg_t, const char *) { return nullptr; }
+
+const ggml_backend_reg_i reg_iface = {
+    /* .get_name         = */ reg_get_name,
+    /* .get_device_count = */ reg_get_device_count,
+    /* .get_device       = */ reg_get_device,
+    /* .get_proc_address = */ reg_get_proc_address,
+};
+
+ggml_backend_reg_t vlut_b200_reg() {
+    static ggml_backend_reg reg;
+    static bool initialized = false;
+    static std::mutex mutex;
+    std::lock_guard<std::mutex> lock(mutex);
+    if (!initialized) {
+        reg_ctx *r = new reg_ctx;
+        int n = 0;
+        if (vlut_device_count(&n) != VLUT_OK) n = 0;
+        // env VLUT_B200_DEVICES limits how many GPUs are exposed as ggml devices
+        if (const char *lim = getenv("VLUT_B200_DEVICES")) {
+            const int l = atoi(lim);
+            if (l >= 0 && l < n) n = l;
+        }
+        reg = ggml_backend_reg{
+            /* .api_version = */ GGML_BACKEND_API_VERSION,
+            /* .iface       = */ reg_iface,
+            /* .context     = */ r,
+        };
+        r->handles.reserve(n);
+        for (int i = 0; i < n; i++) {
+            device_ctx *d = new device_ctx;
+            d->device = i;
+            d->name = "VLUT_B200_" + std::to_string(i);
+            char gpu[128] = "";
+            vlut_device_info(i, gpu, sizeof(gpu), nullptr, nullptr, nullptr);
+            d->description = std::string(gpu) + " (Vec-LUT ternary MUL_MAT, sm_100a)";
+            d->buft = ggml_backend_buffer_type{
+                /* .iface   = */ buft_iface,
+                /* .device  = */ nullptr,  // fixed up below
+                /* .context = */ d,
+            };
+            r->devices.push_back(d);
+            r->handles.push_back(ggml_backend_device{
+                /* .iface   = */ device_iface,
+                /* .reg     = */ &reg,
+                /* .context = */ d,
+            });
+        }
+        for (int i = 0; i < n; i++) r->devices[i]->buft.device = &r->handles[i];
+        initialized = true;
+    }
+    return &reg;
+}
+
+// 0 = not usable on this system (ggml_backend_load skips it, ggml-backend-reg.cpp:271-300)
+int vlut_b200_score() {
+    int n = 0;
+    if (vlut_device_count(&n) != VLUT_OK) return 0;
+    return n > 0 ? 100 : 0;
+}
+
+}  // namespace
+
+GGML_BACKEND_DL_IMPL(vlut_b200_reg)
+GGML_BACKEND_DL_SCORE_IMPL(vlut_b200_score)
