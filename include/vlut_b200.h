@@ -107,6 +107,15 @@ int vlut_gemm(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const vo
 /* the whole op on device buffers = GGML_OP_MUL_MAT(vlut weight, f32) of ggml-cpu.c:1372-1421 */
 int vlut_mul_mat(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                  int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo);
+/* Multi-GPU, row-sharded weights (output-row tensor parallelism: the thread split of ggml-cpu.c:1413-1418 across
+ * GPUs): this rank's [K x N] shard produces columns [col0, col0+N) of the [T][N_total] result.  The GEMM epilogue
+ * itself performs the all-gather: it stores every element into each rank's result buffer, either through n_out peer
+ * pointers (CUDA P2P / symmetric memory over NVLink 5) or, with multicast != 0 and n_out == 1, through ONE NVSwitch
+ * multicast address (multimem.st).  outs_dev[i] must already point at column col0 of rank i's buffer; ldo = N_total.
+ * The caller follows with a cross-rank barrier (e.g. a symmetric-memory barrier) before reading. */
+int vlut_mul_mat_scatter(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
+                         int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
+                         int algo);
 /* the whole op on HOST buffers: H2D of x, the op, D2H of out, stream sync -- what a ggml_backend_sched split
  * costs (ggml/src/ggml-backend.cpp:1443-1460).  Pinned host memory makes the copies asynchronous. */
 int vlut_mul_mat_host(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev,

@@ -242,3 +242,24 @@ def test_streamk_split_tiles_and_ring_wrap(ctx, orc, monkeypatch, grid, stages, 
         for rep in range(2):  # second run sees the workspace the first one left behind
             out = run(ctx, type_, packed, x, N, a.ALGO_TC)
             assert np.array_equal(bits(out), bits(ref)), f"rep={rep}"
+
+
+def test_fused_scatter_epilogue_single_gpu_emulation(ctx, orc):
+    """The fused all-gather epilogue (vlut_mul_mat_scatter, peer-pointer flavour), with the 'ranks' emulated as two
+    shards and two result buffers on ONE GPU: each shard's GEMM writes its column slice into both [T][N] buffers."""
+    a = api()
+    type_, K, N, T = O.I2_V_4, 2048, 640, 40
+    w = O.make_ternary(N, K, seed=3)
+    x = O.make_acts(T, K, seed=4)
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    xd = torch.from_numpy(x).cuda()
+    bufs = [torch.zeros((T, N), device="cuda") for _ in range(2)]
+    bounds = [0, 384, 640]
+    for g in range(2):
+        r0, rows = bounds[g], bounds[g + 1] - bounds[g]
+        Wg = ctx.upload(type_, K, rows, a.shard_rows(type_, K, N, r0, rows, packed))
+        ctx.mul_mat_scatter(Wg, xd, peers=[b.data_ptr() for b in bufs], multicast_ptr=0, ldo=N, col0=r0)
+    torch.cuda.synchronize()
+    for b in bufs:
+        assert np.array_equal(bits(b.cpu().numpy()), bits(ref))

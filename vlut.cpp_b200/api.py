@@ -158,6 +158,22 @@ class Context:
                                       out.data_ptr(), out.stride(0), w_scale, algo), "vlut_mul_mat")
         return out
 
+    def mul_mat_scatter(self, w: Weight, x: torch.Tensor, peers: list[int], multicast_ptr: int, ldo: int, col0: int,
+                        w_scale: float = 1.0, algo: int = ALGO_AUTO) -> None:
+        """Row-sharded op with the all-gather fused into the epilogue: this rank's [T][w.N] slice is stored at column
+        ``col0`` of the [T][ldo] result buffer of EVERY rank (``peers`` = base addresses of those buffers, or the
+        NVSwitch multicast address of the symmetric allocation)."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] == w.K
+        T = x.shape[0]
+        if multicast_ptr:
+            ptrs = [multicast_ptr + 4 * col0]
+        else:
+            ptrs = [p + 4 * col0 for p in peers]
+        arr = (C.c_void_p * len(ptrs))(*ptrs)
+        check(_lib.lib().vlut_mul_mat_scatter(self._h, w.type, w.K, w.N, T, w.t2.data_ptr(), x.data_ptr(), x.stride(0), arr,
+                                              len(ptrs), 1 if multicast_ptr else 0, ldo, w_scale, algo),
+              "vlut_mul_mat_scatter")
+
     def mul_mat_host(self, w: Weight, x_host: torch.Tensor, out_host: torch.Tensor, w_scale: float = 1.0,
                      algo: int = ALGO_AUTO) -> torch.Tensor:
         """The op on HOST buffers (pinned for asynchronous copies): H2D(x) + op + D2H(out) + sync."""

@@ -329,9 +329,9 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     return VLUT_ALGO_SIMPLE;
 }
 
-int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev, int64_t ldo,
-              float w_scale, int algo) {
-    if (!c || !t2_dev || !out_dev || T <= 0 || ldo < N) return VLUT_ERR_INVALID;
+static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev,
+                     float *const *outs, int n_out, int multicast, int64_t ldo, float w_scale, int algo) {
+    if (!c || !t2_dev || (!out_dev && n_out <= 0) || T <= 0 || ldo < N || n_out > 8) return VLUT_ERR_INVALID;
     int rc = check_shape(type, K, N);
     if (rc) return rc;
     if (c->act_K != K || c->act_T != T || group_size(c->act_type) != group_size(type)) return VLUT_ERR_INVALID;
@@ -342,6 +342,9 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
     g.w = (const uint8_t *) t2_dev;
     g.act = c->act;
     g.out = out_dev;
+    g.n_out = n_out > 0 ? n_out : 0;
+    g.multicast = multicast;
+    for (int i = 0; i < g.n_out; i++) g.outs[i] = outs[i];
     g.ldo = ldo;
     g.K = K;
     g.N = N;
@@ -368,6 +371,7 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
     cudaError_t e;
     switch (algo) {
         case VLUT_ALGO_SIMPLE:
+            if (g.n_out) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_simple(g, c->stream);
             launches = 1;
             break;
@@ -386,6 +390,20 @@ int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void
     c->launches += launches;
     c->last_algo = algo;
     return VLUT_OK;
+}
+
+int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev, int64_t ldo,
+              float w_scale, int algo) {
+    return gemm_impl(c, type, K, N, T, t2_dev, out_dev, nullptr, 0, 0, ldo, w_scale, algo);
+}
+
+int vlut_mul_mat_scatter(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
+                         int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
+                         int algo) {
+    if (!outs_dev || n_out < 1 || n_out > 8 || (multicast && n_out != 1)) return VLUT_ERR_INVALID;
+    int rc = vlut_quantize_act(c, type, x_dev, ldx, K, T);
+    if (rc) return rc;
+    return gemm_impl(c, type, K, N, T, t2_dev, nullptr, outs_dev, n_out, multicast, ldo, w_scale, algo);
 }
 
 int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,

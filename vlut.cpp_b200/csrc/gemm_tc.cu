@@ -413,7 +413,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                         if (t0 + i < p.g.T) {
                             float v = (float) tot[i] * s_sc[i];
                             if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                            p.g.out[(t0 + i) * p.g.ldo + n] = v;
+                            store_out(p.g, (t0 + i) * p.g.ldo + n, v);
                         }
                     }
                 }
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                             if (t0 + i < p.g.T) {
                                 float v = (float) tot[i] * s_sc[i];
                                 if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                                p.g.out[(t0 + i) * p.g.ldo + n] = v;
+                                store_out(p.g, (t0 + i) * p.g.ldo + n, v);
                             }
                         }
                     }

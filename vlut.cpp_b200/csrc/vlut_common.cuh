@@ -87,7 +87,14 @@ struct ActView {
 struct GemmArgs {
     const uint8_t *w;  // T2
     ActView act;
-    float *out;
+    float *out;         // single-GPU destination, f32 [T][ldo]
+    // multi-GPU fused all-gather (row-sharded weights): the epilogue writes its column slice of the [T][N_total]
+    // result into EVERY rank's buffer -- either n_out peer pointers (CUDA P2P over NVLink), or one NVSwitch multicast
+    // address (multimem.st: the switch replicates the store to all ranks).  Pointers are already offset to this
+    // rank's first column.  n_out == 0: plain single-destination store through `out`.
+    float *outs[8];
+    int n_out;
+    int multicast;
     int64_t ldo;
     int64_t K, N, T, Npad;
     int type;
@@ -96,6 +103,17 @@ struct GemmArgs {
     int32_t *counters;  // per output-tile arrival counters (self-cleaning)
     int sm_count;
 };
+
+// epilogue store: local, peer-scatter (NVLink P2P) or NVSwitch multicast
+inline __device__ void store_out(const GemmArgs &g, int64_t idx, float v) {
+    if (g.n_out == 0) {
+        g.out[idx] = v;
+    } else if (g.multicast) {
+        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(g.outs[0] + idx), "f"(v) : "memory");
+    } else {
+        for (int i = 0; i < g.n_out; i++) g.outs[i][idx] = v;
+    }
+}
 
 inline __device__ int32_t wrap16(int32_t v) { return (int32_t) (int16_t) (uint16_t) ((uint32_t) v & 0xffffu); }
 
