@@ -210,20 +210,46 @@ def main() -> None:
 
     xs = make_x(T)
     n_total = N * world
-    outs = [torch.empty((T, n_total), dtype=torch.float32, device=dev) for _ in range(n_x)]
-    gather_buf = torch.empty((world, T, N), dtype=torch.float32, device=dev) if world > 1 else None
-    local_out = [torch.empty((T, N), dtype=torch.float32, device=dev) for _ in range(n_x)] if world > 1 else None
+    gather_mode = "none"
+    if world == 1:
+        outs = [torch.empty((T, n_total), dtype=torch.float32, device=dev) for _ in range(n_x)]
+    else:
+        # fused all-gather: the GEMM epilogue stores into every rank's [T][N_total] symmetric-memory buffer (NVSwitch
+        # multicast when available, peer pointers otherwise); NCCL all-gather + permute as the fallback / comparison
+        outs, hdls = [], []
+        try:
+            if os.environ.get("VLUT_BENCH_GATHER", "fused") != "fused":
+                raise RuntimeError("nccl gather requested")
+            import torch.distributed._symmetric_memory as symm_mem
+            for _ in range(n_x):
+                buf = symm_mem.empty((T, n_total), dtype=torch.float32, device=dev)
+                hdls.append(symm_mem.rendezvous(buf, dist.group.WORLD))
+                outs.append(buf)
+            gather_mode = "fused-multimem" if int(getattr(hdls[0], "multicast_ptr", 0) or 0) else "fused-p2p"
+        except Exception as e:  # noqa: BLE001
+            if rank == 0:
+                print(f"[bench] symmetric memory unavailable ({e}); using the NCCL all-gather", file=sys.stderr)
+            outs = [torch.empty((T, n_total), dtype=torch.float32, device=dev) for _ in range(n_x)]
+            hdls = []
+            gather_mode = "nccl"
+        gather_buf = torch.empty((world * T, N), dtype=torch.float32, device=dev)
+        local_out = [torch.empty((T, N), dtype=torch.float32, device=dev) for _ in range(n_x)]
 
     def step(i: int):
         w = weights[i % n_w]
         x = xs[i % n_x]
         if world == 1:
             ctx.mul_mat(w, x, out=outs[i % n_x])
+        elif hdls:
+            h = hdls[i % n_x]
+            ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs], multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0),
+                                ldo=n_total, col0=rank * N)
+            h.barrier()
         else:
             lo = local_out[i % n_x]
             ctx.mul_mat(w, x, out=lo)
             dist.all_gather_into_tensor(gather_buf, lo)
-            outs[i % n_x].view(T, world, N).copy_(gather_buf.permute(1, 0, 2))
+            outs[i % n_x].view(T, world, N).copy_(gather_buf.view(world, T, N).permute(1, 0, 2))
 
     def barrier():
         if world > 1:
@@ -231,6 +257,7 @@ def main() -> None:
         torch.cuda.synchronize()
 
     # quick in-run sanity: AUTO agrees with the scalar anchor kernel at the bench size (both on the GPU)
+    torch.cuda.synchronize()
     chk_a = ctx.mul_mat(weights[0], xs[0]).clone()
     chk_b = ctx.mul_mat(weights[0], xs[0], algo=api.ALGO_SIMPLE)
     auto_equals_simple = bool(torch.equal(chk_a, chk_b))
@@ -377,11 +404,11 @@ def main() -> None:
             "scaling": "weak", "vs_baseline": None, "dtype": "int8xternary->int32->f32", "data": "synthetic",
             "config": {"workload": f"vlut MUL_MAT {args.type} K={K} N={n_total} T={T} "
                                    f"(quantise + Vec-LUT GEMM + fp32 epilogue"
-                                   f"{', row-sharded + NCCL all-gather' if world > 1 else ''})",
+                                   f"{', row-sharded + all-gather of output slices' if world > 1 else ''})",
                        "K": K, "N": n_total, "T": T, "type": args.type, "algo": algo_used,
                        "l2": f"rotating {n_w} weight buffers + {n_x} activation/output buffers, working set "
                              f"{ws_mb:.0f} MB > 126 MB L2",
-                       "parallelism": f"row-shard x{world}" if world > 1 else "single GPU"},
+                       "parallelism": f"row-shard x{world}, gather={gather_mode}" if world > 1 else "single GPU"},
             "median_ms_per_step": statistics.median(per_step),
             "gpu_launches": int(launches),
             "roofline": roofline,
