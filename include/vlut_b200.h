@@ -42,7 +42,8 @@ extern "C" {
 /* GEMM algorithms (stage 2).  AUTO picks per token count from the measured crossover table. */
 #define VLUT_ALGO_AUTO    0
 #define VLUT_ALGO_SIMPLE  1   /* one thread per output, scalar: the in-library correctness anchor            */
-#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8: TMA weight stream, register unpack into TMEM/smem, TMEM acc */
+#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8, two decode+issue pipelines, A operand unpacked into TMEM    */
+#define VLUT_ALGO_TC1     5   /* same algorithm, single pipeline; A operand in TMEM or (VLUT_TC_TS=0) shared memory     */
 #define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate (measured candidate)      */
 
 typedef struct vlut_ctx vlut_ctx;

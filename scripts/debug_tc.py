@@ -18,7 +18,7 @@ for ts in modes:
         xd = torch.from_numpy(x).cuda()
         e = ctx.mul_mat(W, xd, algo=api.ALGO_SIMPLE).clone()
         torch.cuda.synchronize()
-        r = ctx.mul_mat(W, xd, algo=api.ALGO_TC).clone()
+        r = ctx.mul_mat(W, xd, algo=int(os.environ.get('DBG_ALGO', api.ALGO_TC))).clone()
         torch.cuda.synchronize()
         bad = (r != e)
         msg = ""

@@ -325,7 +325,9 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     const char *v = getenv("VLUT_B200_ALGO");
     const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
-    if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC;
+    // measured (profiles/): the two-pipeline kernel wins up to 16 tokens, the single-pipeline one above
+    if (T <= 16 && gemm_tc2_supported(type, K, N, T)) return VLUT_ALGO_TC;
+    if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
     return VLUT_ALGO_SIMPLE;
 }
 
@@ -354,11 +356,11 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     g.w_scale = w_scale;
     g.sm_count = c->sm_count;
 
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_LUT) {
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_LUT) {
         // stream-K workspace: two private partial-tile slots per persistent CTA (no initialisation needed) and
         // self-resetting per-tile arrival counters (zeroed once at (re)allocation)
         bool grew = false;
-        const size_t pb = (size_t) c->sm_count * 2 * 128 * 128 * sizeof(int32_t);
+        const size_t pb = (size_t) c->sm_count * 3 * 128 * 128 * sizeof(int32_t);  // 2 partial-tile slots + 1 scratch per CTA
         if (c->part.reserve(pb) != cudaSuccess) return VLUT_ERR_NOMEM;
         const size_t cb = (size_t) ((g.Npad / TILE_ROWS) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
@@ -376,6 +378,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
             launches = 1;
             break;
         case VLUT_ALGO_TC:
+            if (!gemm_tc2_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tc2(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_TC1:
             if (!gemm_tc_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tc(g, c->stream, &launches);
             break;

@@ -122,8 +122,10 @@ cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, u
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s);
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
-cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);
+cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);   // single pipeline (TS or SS)
 bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
+cudaError_t launch_gemm_tc2(const GemmArgs &g, cudaStream_t s, int *launches);  // two pipelines (TS)
+bool gemm_tc2_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_lut(const GemmArgs &g, cudaStream_t s, int *launches);
 bool gemm_lut_supported(int type, int64_t K, int64_t N, int64_t T);
 
