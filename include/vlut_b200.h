@@ -42,8 +42,9 @@ extern "C" {
 /* GEMM algorithms (stage 2).  AUTO picks per token count from the measured crossover table. */
 #define VLUT_ALGO_AUTO    0
 #define VLUT_ALGO_SIMPLE  1   /* one thread per output, scalar: the in-library correctness anchor            */
-#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8, two decode+issue pipelines, A operand unpacked into TMEM    */
-#define VLUT_ALGO_TC1     5   /* same algorithm, single pipeline; A operand in TMEM or (VLUT_TC_TS=0) shared memory     */
+#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8: TMA weight stream, 8-warp register unpack into TMEM, PDL     */
+#define VLUT_ALGO_TC1     5   /* first generation: 4 decode warps; A operand in TMEM or (VLUT_TC_TS=0) shared memory    */
+#define VLUT_ALGO_TC2     6   /* 256 weight rows per CTA, two pipelines sharing every activation stage                  */
 #define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate (measured candidate)      */
 
 typedef struct vlut_ctx vlut_ctx;

@@ -1,6 +1,7 @@
 """Per-role wait-cycle breakdown of the tcgen05 GEMM (VLUT_TC_DEBUG=1)."""
 import sys, os; sys.path.insert(0, '.')
 os.environ["VLUT_TC_DEBUG"] = "1"
+
 import numpy as np, torch
 import vlut_b200
 from vlut_b200 import api, _lib
@@ -15,9 +16,10 @@ for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "16,128,512").s
     for i in range(3):
         ctx.mul_mat(W, x, out=out)
     torch.cuda.synchronize()
-    buf = np.zeros(256 * 4 * 8, dtype=np.int64)
+    buf = np.zeros(256 * 4 * 8 + 4 * 24 * 2, dtype=np.int64)
     rc = _lib.lib().vlut_debug_tc_counters(buf.ctypes.data, buf.size)
-    c = buf.reshape(256, 4, 8)
+    c = buf[:8192].reshape(256, 4, 8)
+    ev = buf[8192:].reshape(4, 24, 2)
     used = c[:, 1, 7] > 0
     n = int(used.sum())
     m = c[used].mean(axis=0)
@@ -26,3 +28,9 @@ for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "16,128,512").s
     print(f"  mma     : life {m[1,7]:.0f}  wait_full {m[1,0]:.0f}  wait_afull {m[1,1]:.0f}  wait_accempty {m[1,2]:.0f}")
     print(f"  decode  : life {m[2,7]:.0f}  wait_full {m[2,0]:.0f}  wait_aempty {m[2,1]:.0f}  wait_st {m[2,2]:.0f}")
     print(f"  epilogue: life {m[3,7]:.0f}  wait_accfull {m[3,0]:.0f}")
+
+    if os.environ.get("TIMELINE"):
+        names = ["producer", "mma", "decode0", "epilogue"]
+        kinds = {0: "w0", 1: "w1", 2: "accempty/st", 7: "drained", 8: "mma-issued", 9: "A-ready"}
+        for r in range(4):
+            print("  timeline", names[r], " ".join(f"{int(t)}:{kinds.get(int(k), k)}" for t, k in ev[r] if t > 0))

@@ -325,8 +325,12 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     const char *v = getenv("VLUT_B200_ALGO");
     const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
-    // measured (profiles/): the two-pipeline kernel wins up to 16 tokens, the single-pipeline one above
-    if (T <= 16 && gemm_tc2_supported(type, K, N, T)) return VLUT_ALGO_TC;
+    // crossover table from B200 measurements (profiles/r1_crossover.txt):
+    //   T <= 128        TC   (8-warp unpack, PDL): lowest latency, one token tile
+    //   128 < T <= 256  TC2  (256 rows per CTA, shared activation stages): least shared-memory fill per MAC
+    //   T  > 256        TC1  (first generation, 4-warp unpack, register-resident epilogue totals)
+    if (T <= 128 && gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
+    if (T <= 256 && gemm_tc3_supported(type, K, N, T)) return VLUT_ALGO_TC2;
     if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
     return VLUT_ALGO_SIMPLE;
 }
@@ -338,7 +342,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     if (rc) return rc;
     if (c->act_K != K || c->act_T != T || group_size(c->act_type) != group_size(type)) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
-    if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, N, T);
+    if (algo == VLUT_ALGO_AUTO) {
+        algo = vlut_pick_algo(type, K, N, T);
+        if (n_out > 0 && algo == VLUT_ALGO_TC1) algo = VLUT_ALGO_TC;  // the scatter epilogue lives in TC / TC2
+    }
 
     GemmArgs g{};
     g.w = (const uint8_t *) t2_dev;
@@ -356,11 +363,11 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     g.w_scale = w_scale;
     g.sm_count = c->sm_count;
 
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_LUT) {
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_LUT) {
         // stream-K workspace: two private partial-tile slots per persistent CTA (no initialisation needed) and
         // self-resetting per-tile arrival counters (zeroed once at (re)allocation)
         bool grew = false;
-        const size_t pb = (size_t) c->sm_count * 3 * 128 * 128 * sizeof(int32_t);  // 2 partial-tile slots + 1 scratch per CTA
+        const size_t pb = (size_t) c->sm_count * 6 * 128 * 128 * sizeof(int32_t);  // 4 partial-tile slots + 2 scratch per CTA
         if (c->part.reserve(pb) != cudaSuccess) return VLUT_ERR_NOMEM;
         const size_t cb = (size_t) ((g.Npad / TILE_ROWS) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
@@ -378,11 +385,15 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
             launches = 1;
             break;
         case VLUT_ALGO_TC:
-            if (!gemm_tc2_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
-            e = launch_gemm_tc2(g, c->stream, &launches);
+            if (!gemm_tc4_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tc4(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_TC2:
+            if (!gemm_tc3_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tc3(g, c->stream, &launches);
             break;
         case VLUT_ALGO_TC1:
-            if (!gemm_tc_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            if (!gemm_tc_supported(type, K, N, T) || g.n_out) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tc(g, c->stream, &launches);
             break;
         case VLUT_ALGO_LUT:

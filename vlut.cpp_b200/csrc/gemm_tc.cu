@@ -157,16 +157,27 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     // optional instrumentation: cycles spent in each kind of wait, per role (lane 0 reports)
     long long dbgc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const bool dbg_on = p.dbg != nullptr;
+    const long long t_start = dbg_on ? clock64() : 0;
+    int n_ev = 0;
+    int ev_role = 0;
+    // timeline (CTA 0 only): time at which each wait of a role returned, 24 events per role
+    auto mark = [&](int kind) {
+        if (dbg_on && blockIdx.x == 0 && lane == 0 && n_ev < 24) {
+            p.dbg[8192 + (ev_role * 24 + n_ev) * 2] = clock64() - t_start;
+            p.dbg[8192 + (ev_role * 24 + n_ev) * 2 + 1] = kind;
+            ++n_ev;
+        }
+    };
     auto twait = [&](uint32_t bar, uint32_t parity, int slot) {
         if (dbg_on) {
             const long long t0 = clock64();
             ptx::mbar_wait(bar, parity);
             dbgc[slot] += clock64() - t0;
+            mark(slot);
         } else {
             ptx::mbar_wait(bar, parity);
         }
     };
-    const long long t_start = dbg_on ? clock64() : 0;
     auto dbg_report = [&](int role) {
         if (dbg_on && lane == 0) {
             dbgc[7] = clock64() - t_start;
@@ -175,6 +186,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     };
 
     if (warp == 8) {
+        ev_role = 0;
         // ===================== TMA producer (whole warp walks, one elected lane issues) =====================
         const uint64_t pol_w = ptx::policy_evict_first();
         const uint64_t pol_a = ptx::policy_evict_last();
@@ -203,6 +215,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
         }
         dbg_report(0);
     } else if (warp == 9) {
+        ev_role = 1;
         // ===================== MMA issuer (whole warp walks, one elected lane issues) =====================
         constexpr uint32_t idesc = make_idesc(NT);
         UnitWalk w;
@@ -256,6 +269,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                     ptx::umma_commit(ptx::smem_u32(&s_aempty[ar.i]));  // A stage is free again
                 }
                 __syncwarp();
+                mark(8);
                 for (int s0 = 0; s0 < na; s0 += SPS) st.advance();
                 ar.advance();
             }
@@ -273,6 +287,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     } else if (warp >= 4 && warp < 8) {
         // ===================== decode: packed 2-bit codes -> u8 A operand =====================
         const int dw = warp - 4;
+        ev_role = 2;
         const int m = dw * 32 + lane;  // weight row inside the strip == TMEM lane
         UnitWalk w;
         w.init(p, u0, u1);
@@ -346,6 +361,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                 }
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ar.i]));
+                mark(9);
                 ar.advance();
             }
         }
@@ -353,6 +369,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     } else if (warp < 4) {
         // ===================== epilogue =====================
         const int ew = warp;
+        ev_role = 3;
         const int m = ew * 32 + lane;
         const int et = threadIdx.x;  // 0..127
         int32_t tot[NT];
@@ -413,7 +430,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                         if (t0 + i < p.g.T) {
                             float v = (float) tot[i] * s_sc[i];
                             if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                            store_out(p.g, (t0 + i) * p.g.ldo + n, v);
+                            p.g.out[(t0 + i) * p.g.ldo + n] = v;
                         }
                     }
                 }
@@ -460,7 +477,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
                             if (t0 + i < p.g.T) {
                                 float v = (float) tot[i] * s_sc[i];
                                 if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                                store_out(p.g, (t0 + i) * p.g.ldo + n, v);
+                                p.g.out[(t0 + i) * p.g.ldo + n] = v;
                             }
                         }
                     }
@@ -488,8 +505,17 @@ bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T) {
     return type_valid(type) && T >= 1 && K >= 4 && N >= 1 && ceil_div(K, group_size(type)) <= 64;
 }
 
-constexpr int DBG_WORDS = 256 * 4 * 8;
+constexpr int DBG_WORDS = 256 * 4 * 8 + 4 * 24 * 2;
 static long long *g_dbg_buf = nullptr;
+
+// zeroed debug buffer shared by the kernels' optional instrumentation; word 0 = number of timeline events to skip
+long long *debug_buffer(cudaStream_t s, int skip) {
+    if (!g_dbg_buf) cudaMalloc(&g_dbg_buf, DBG_WORDS * sizeof(long long));
+    cudaMemsetAsync(g_dbg_buf, 0, DBG_WORDS * sizeof(long long), s);
+    const long long sk = skip;
+    cudaMemcpyAsync(g_dbg_buf, &sk, sizeof(sk), cudaMemcpyHostToDevice, s);
+    return g_dbg_buf;
+}
 
 static int env_int(const char *name, int dflt) {
     const char *v = getenv(name);

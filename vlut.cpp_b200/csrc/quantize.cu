@@ -21,6 +21,9 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
                                                       ActView a) {
     const int t = blockIdx.x;
     const int tid = threadIdx.x;
+    // programmatic dependent launch: let the GEMM that follows start its prologue and its weight prefetch now; it
+    // orders itself against this kernel's results with griddepcontrol.wait
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
     __shared__ float s_red[QT / 32];
     __shared__ int s_gsum[64];
     __shared__ int s_gabs[64];

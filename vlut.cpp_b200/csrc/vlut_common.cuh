@@ -99,19 +99,20 @@ struct GemmArgs {
     int64_t K, N, T, Npad;
     int type;
     float w_scale;
-    int32_t *part;      // int32 [CTAs][2 slots][NT][128] stream-K partial tiles (no initialisation needed)
+    int32_t *part;      // int32 [CTAs][4 slots + 2 scratch][NT][128] stream-K partial tiles (no initialisation needed)
     int32_t *counters;  // per output-tile arrival counters (self-cleaning)
     int sm_count;
 };
 
-// epilogue store: local, peer-scatter (NVLink P2P) or NVSwitch multicast
-inline __device__ void store_out(const GemmArgs &g, int64_t idx, float v) {
-    if (g.n_out == 0) {
-        g.out[idx] = v;
-    } else if (g.multicast) {
-        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(g.outs[0] + idx), "f"(v) : "memory");
+// epilogue store, selected at compile time: 0 local, 1 peer scatter (NVLink P2P), 2 NVSwitch multicast (multimem.st)
+template <int MODE>
+__device__ __forceinline__ void store_out(float *const out, float *const *outs, int n_out, int64_t idx, float v) {
+    if (MODE == 0) {
+        out[idx] = v;
+    } else if (MODE == 2) {
+        asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(out + idx), "f"(v) : "memory");
     } else {
-        for (int i = 0; i < g.n_out; i++) g.outs[i][idx] = v;
+        for (int i = 0; i < n_out; i++) outs[i][idx] = v;
     }
 }
 
@@ -124,8 +125,10 @@ cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, c
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
 cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);   // single pipeline (TS or SS)
 bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
-cudaError_t launch_gemm_tc2(const GemmArgs &g, cudaStream_t s, int *launches);  // two pipelines (TS)
-bool gemm_tc2_supported(int type, int64_t K, int64_t N, int64_t T);
+cudaError_t launch_gemm_tc3(const GemmArgs &g, cudaStream_t s, int *launches);  // 256 rows / CTA, shared act stages
+bool gemm_tc3_supported(int type, int64_t K, int64_t N, int64_t T);
+cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches);  // production: 8 decode warps, PDL
+bool gemm_tc4_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_lut(const GemmArgs &g, cudaStream_t s, int *launches);
 bool gemm_lut_supported(int type, int64_t K, int64_t N, int64_t T);
 
