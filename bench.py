@@ -117,7 +117,8 @@ def run_reference(args) -> None:
     ref = O.RefLib()
     type_ = O.__dict__[args.type]
     T, K, N = args.tokens, K_DIM, N_DIM * args.gpus
-    nth = ref.max_threads()
+    # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
+    nth = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     rng = np.random.Generator(np.random.PCG64(1234))
     packed = rng.integers(0, 81 if type_ in (O.I2_V, O.I2_V_4, O.I2_V_8) else 243, size=O.row_size(type_, K) * N,
                           dtype=np.uint8)
@@ -241,17 +242,25 @@ def main() -> None:
         if world == 1:
             ctx.mul_mat(w, x, out=outs[i % n_x])
         elif hdls:
+            # the result buffers rotate: the cross-rank barrier that publishes step i-1 is issued after step i's GEMM
+            # has been launched, so the NVLink transfer of one step overlaps the compute of the next
             h = hdls[i % n_x]
             ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs], multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0),
                                 ldo=n_total, col0=rank * N)
-            h.barrier()
+            if pending:
+                pending.pop().barrier()
+            pending.append(h)
         else:
             lo = local_out[i % n_x]
             ctx.mul_mat(w, x, out=lo)
             dist.all_gather_into_tensor(gather_buf, lo)
             outs[i % n_x].view(T, world, N).copy_(gather_buf.view(world, T, N).permute(1, 0, 2))
 
+    pending = []  # symmetric-memory handles whose publishing barrier is still owed
+
     def barrier():
+        while pending:
+            pending.pop().barrier()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
@@ -330,7 +339,13 @@ def main() -> None:
     else:
         roofline = {"bound": "tensor", "achieved": gemm_tops, "peak": int8_peak_tops, "unit": "TOP/s",
                     "frac": frac_tensor}
-    roofline.update({"traffic": None, "kernel": f"vlut gemm ({gemm_algo}) T={T}", "kernel_us": gemm_us,
+    traffic = None
+    try:
+        tj = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text())
+        traffic = tj.get(f"{gemm_algo}_T{T}_{args.type}")
+    except Exception:  # noqa: BLE001
+        pass
+    roofline.update({"traffic": traffic, "kernel": f"vlut gemm ({gemm_algo}) T={T}", "kernel_us": gemm_us,
                      "peak_source": f"{peaks['source']} (MEASURED_PEAKS.json); int8 tensor peak taken as 2 x measured "
                                     f"bf16 burst (no int8 figure is measured)",
                      "algorithmic_bytes": alg_bytes(T), "algorithmic_ops": 2 * K * N * T})
@@ -378,7 +393,8 @@ def main() -> None:
         from oracle import oracle as O
         try:
             ref = O.RefLib()
-            kind, nth = "reference", ref.max_threads()
+            kind = "reference"
+            nth = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
             pk = weights[0]  # regenerate the same distribution on the host: timing is data independent
             rng = np.random.Generator(np.random.PCG64(1234))
             packed = rng.integers(0, 81 if is_i2 else 243, size=nb_gguf, dtype=np.uint8)

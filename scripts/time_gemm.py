@@ -18,7 +18,7 @@ xw = torch.randn((256, K), device="cuda", generator=g); ow = torch.empty((256, N
 ctx.quantize_act(42, xw)
 t_end = time.time() + 2.0
 while time.time() < t_end:
-    for i in range(50): ctx.gemm(ws[i % 11], 256, out=ow, algo=algo)
+    for i in range(50): ctx.gemm(ws[i % 11], 256, out=ow)
     torch.cuda.synchronize()
 for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "1,16,128,512").split(",")]:
     x = torch.randn((T, K), device="cuda", generator=g)

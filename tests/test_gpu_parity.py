@@ -32,7 +32,7 @@ def api():
 
 def algos_for(T):
     a = api()
-    return [a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2]
+    return [a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_LUT] if T <= 16 else [])
 
 
 def run(ctx, type_, packed, x, N, algo, w_scale=1.0):

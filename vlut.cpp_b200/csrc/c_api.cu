@@ -398,6 +398,9 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
             break;
         case VLUT_ALGO_LUT:
             if (!gemm_lut_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            // the LUT candidate accumulates with atomics into the (shared) workspace: hand it a zeroed region
+            if ((size_t) (16 * g.Npad) * sizeof(int32_t) > c->part.cap) return VLUT_ERR_UNSUPPORTED;
+            CK(cudaMemsetAsync(c->part.p, 0, (size_t) (16 * g.Npad) * sizeof(int32_t), c->stream));
             e = launch_gemm_lut(g, c->stream, &launches);
             break;
         default:
