@@ -87,9 +87,16 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         const int c = kk / 16;
         const int64_t off = (((int64_t) (t / a.NT) * (Kpad / BLOCK_K) + kb) * a.NT + (t % a.NT)) * 128 + ((c ^ (t & 7)) << 4) + (kk & 15);
         *reinterpret_cast<uint32_t *>(a.q_sw + off) = pk;
-        const int sum = qv[0] + qv[1] + qv[2] + qv[3];
-        const int asum = abs(qv[0]) + abs(qv[1]) + abs(qv[2]) + abs(qv[3]);
-        if (asum != 0) {
+        // the 32 lanes of a warp cover 128 consecutive, 128-aligned k here: one K-group (512 and 640 are multiples of
+        // 128), so reduce with shuffles and touch shared memory once per warp (Kpad % 128 == 0: the loop is warp-uniform)
+        int sum = qv[0] + qv[1] + qv[2] + qv[3];
+        int asum = abs(qv[0]) + abs(qv[1]) + abs(qv[2]) + abs(qv[3]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            asum += __shfl_xor_sync(0xffffffffu, asum, o);
+        }
+        if ((tid & 31) == 0 && asum != 0) {
             atomicAdd(&s_gsum[k / a.gsize], sum);
             atomicAdd(&s_gabs[k / a.gsize], asum);
         }
