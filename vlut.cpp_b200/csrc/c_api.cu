@@ -53,12 +53,13 @@ struct vlut_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_fast, tile_cnt, part, counters, stage_x, stage_out, stage_w;
+    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_unsafe, part, counters, stage_x, stage_out, stage_w;
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
     int64_t launches = 0;
     int last_algo = 0;
+    uint32_t epoch = 0;  // quantisation call counter (ActView.epoch)
 };
 
 extern "C" {
@@ -147,8 +148,8 @@ void vlut_ctx_destroy(vlut_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
-    DevBuf *bufs[] = {&c->q_rm,     &c->q_sw, &c->scales,   &c->gpre,    &c->nowrap,    &c->tile_fast,
-                      &c->tile_cnt, &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
+    DevBuf *bufs[] = {&c->q_rm, &c->q_sw,     &c->scales,  &c->gpre,      &c->nowrap, &c->tile_unsafe,
+                      &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
     for (DevBuf *b : bufs) b->release();
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -287,17 +288,17 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
     if (c->scales.reserve((size_t) Tpad * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->gpre.reserve((size_t) Tpad * (G + 1) * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->nowrap.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
-    if (c->tile_fast.reserve((size_t) (Tpad / 16) * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     bool grew = false;
-    if (c->tile_cnt.reserve((size_t) (Tpad / 16) * sizeof(int32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
-    if (grew && cudaMemsetAsync(c->tile_cnt.p, 0, c->tile_cnt.cap, c->stream) != cudaSuccess) return VLUT_ERR_CUDA;
+    if (c->tile_unsafe.reserve((size_t) (Tpad / 16) * sizeof(uint32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (grew && cudaMemsetAsync(c->tile_unsafe.p, 0, c->tile_unsafe.cap, c->stream) != cudaSuccess) return VLUT_ERR_CUDA;
     c->act.q_rm = (int8_t *) c->q_rm.p;
     c->act.q_sw = (int8_t *) c->q_sw.p;
     c->act.scales = (float *) c->scales.p;
     c->act.gpre = (int32_t *) c->gpre.p;
     c->act.nowrap = (int32_t *) c->nowrap.p;
-    c->act.tile_fast = (int32_t *) c->tile_fast.p;
-    c->act.tile_cnt = (int32_t *) c->tile_cnt.p;
+    c->act.tile_unsafe = (uint32_t *) c->tile_unsafe.p;
+    if (++c->epoch == 0) c->epoch = 1;
+    c->act.epoch = c->epoch;
     c->act.Kpad = Kpad;
     c->act.Tpad = Tpad;
     c->act.G = G;

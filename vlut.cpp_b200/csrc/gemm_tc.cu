@@ -153,7 +153,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) gemm_tc_kernel(const __grid_con
     const int u1 = (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
 
     // exact (per-group drain) or fast (single drain) path: uniform per token tile
-    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_fast + tt) != 0); };
+    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional instrumentation: cycles spent in each kind of wait, per role (lane 0 reports)
     long long dbgc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     const bool dbg_on = p.dbg != nullptr;

@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
 
     const int u0 = (int) (((int64_t) blockIdx.x * p.U) / gridDim.x);
     const int u1 = (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
-    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_fast + tt) != 0); };
+    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     auto pipe_valid = [&](int rp, int d) -> bool { return 2 * rp + d < p.RT; };
 
     if (warp == 12) {

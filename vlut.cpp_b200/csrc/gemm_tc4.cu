@@ -130,7 +130,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
 
     const int u0 = (int) (((int64_t) blockIdx.x * p.U) / gridDim.x);
     const int u1 = (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
-    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_fast + tt) != 0); };
+    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
     const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
     const long long t_start = dbg_on ? clock64() : 0;

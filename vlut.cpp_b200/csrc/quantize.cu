@@ -102,7 +102,6 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         }
     }
     __syncthreads();
-    __shared__ int s_islast;
     if (tid == 0) {
         int run = 0, safe = 1;
         int32_t *pre = a.gpre + (int64_t) t * (a.G + 1);
@@ -113,21 +112,8 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         }
         pre[a.G] = run;
         a.nowrap[t] = safe;
-        // last CTA of the token tile reduces the per-token flags to one flag per tile
-        __threadfence();
-        const int old = atomicAdd(a.tile_cnt + t / a.NT, 1);
-        s_islast = (old == a.NT - 1);
-    }
-    __syncthreads();
-    if (s_islast) {
-        __threadfence();
-        const int tile = t / a.NT;
-        int ok = (tid < a.NT) ? __ldcg(a.nowrap + tile * a.NT + tid) : 1;
-        ok = __syncthreads_and(ok);
-        if (tid == 0) {
-            a.tile_fast[tile] = ok;
-            a.tile_cnt[tile] = 0;
-        }
+        // a token tile takes the single-drain path unless one of its tokens stamps it with this call's epoch
+        if (!safe) a.tile_unsafe[t / a.NT] = a.epoch;
     }
 }
 

@@ -70,16 +70,16 @@ __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <
 //                             correction of groups [a, b] is gpre[b+1] - gpre[a]  (undoes the +1 of the u8 codes)
 // nowrap int32 [Tpad]         1 if for every group of token t sum_k |q| <= 32767, i.e. no int16 wrap is possible
 //                             whatever the weights are (full-K accumulation is then exact)
-// tile_fast int32 [Tpad/NT]   AND of nowrap over the token tile (written by the last quantise CTA of the tile)
-// tile_cnt  int32 [Tpad/NT]   arrival counters for that reduction (self-resetting)
+// tile_unsafe u32 [Tpad/NT]   = `epoch` of this quantisation iff some token of the tile can wrap (any unsafe token's CTA
+//                             stores the epoch: no reduction, no atomics); epoch = per-context call counter, never 0
 struct ActView {
     int8_t *q_rm;
     int8_t *q_sw;
     float *scales;
     int32_t *gpre;
     int32_t *nowrap;
-    int32_t *tile_fast;
-    int32_t *tile_cnt;
+    uint32_t *tile_unsafe;
+    uint32_t epoch;
     int64_t Kpad, Tpad;
     int G, gsize, NT;
 };
