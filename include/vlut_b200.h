@@ -45,6 +45,7 @@ extern "C" {
 #define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8: TMA weight stream, 8-warp register unpack into TMEM, PDL     */
 #define VLUT_ALGO_TC1     5   /* first generation: 4 decode warps; A operand in TMEM or (VLUT_TC_TS=0) shared memory    */
 #define VLUT_ALGO_TC2     6   /* 256 weight rows per CTA, two pipelines sharing every activation stage                  */
+#define VLUT_ALGO_TCP     7   /* CTA pairs (cluster of 2, cta_group::2, M = 256): each CTA stages half the token tile, T > 32 */
 #define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate, T <= 16 (measured candidate)     */
 
 typedef struct vlut_ctx vlut_ctx;

@@ -32,7 +32,8 @@ def api():
 
 def algos_for(T):
     a = api()
-    return [a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_LUT] if T <= 16 else [])
+    return ([a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_LUT] if T <= 16 else []) +
+            ([a.ALGO_TCP] if T > 32 else []))  # CTA-pair kernel: token tiles of 64 / 128
 
 
 def run(ctx, type_, packed, x, N, algo, w_scale=1.0):
@@ -239,7 +240,8 @@ def test_streamk_split_tiles_and_ring_wrap(ctx, orc, monkeypatch, grid, stages, 
         x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "normal")  # uniform: sum|q| often > 32767
         packed = orc.pack(type_, w)
         ref = orc.mul_mat(type_, packed, x, N)
-        for algo in ([a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] if ts else [a.ALGO_TC1]):  # shared-memory A path: TC1 only
+        algos = [a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_TCP] if T > 32 else [])
+        for algo in (algos if ts else [a.ALGO_TC1]):  # shared-memory A path: TC1 only
             for rep in range(2):  # second run sees the workspace the first one left behind
                 out = run(ctx, type_, packed, x, N, algo)
                 assert np.array_equal(bits(out), bits(ref)), f"algo={algo} rep={rep}"

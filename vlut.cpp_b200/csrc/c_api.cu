@@ -327,11 +327,11 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
     // crossover table from B200 measurements (profiles/r1_crossover.txt):
-    //   T <= 128        TC   (8-warp unpack, PDL): lowest latency, one token tile
-    //   128 < T <= 256  TC2  (256 rows per CTA, shared activation stages): least shared-memory fill per MAC
-    //   T  > 256        TC1  (first generation, 4-warp unpack, register-resident epilogue totals)
-    if (T <= 128 && gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
-    if (T <= 256 && gemm_tc3_supported(type, K, N, T)) return VLUT_ALGO_TC2;
+    //   T <= 256   TC   (one CTA per 128-row strip, 8-warp unpack, PDL): lowest latency
+    //   T  > 256   TCP  (CTA pairs, cta_group::2: each CTA stages half of the token tile -> less L2 -> shared-memory fill)
+    // TC1 / TC2 (earlier generations) stay selectable for comparison.
+    if (T > 256 && gemm_tc5_supported(type, K, N, T)) return VLUT_ALGO_TCP;
+    if (gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
     if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
     return VLUT_ALGO_SIMPLE;
 }
@@ -345,7 +345,7 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     CK(cudaSetDevice(c->device));
     if (algo == VLUT_ALGO_AUTO) {
         algo = vlut_pick_algo(type, K, N, T);
-        if (n_out > 0 && algo == VLUT_ALGO_TC1) algo = VLUT_ALGO_TC;  // the scatter epilogue lives in TC / TC2
+        if (n_out > 0 && algo == VLUT_ALGO_TC1) algo = VLUT_ALGO_TC;  // TC1 has no scatter epilogue
     }
 
     GemmArgs g{};
@@ -364,13 +364,14 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     g.w_scale = w_scale;
     g.sm_count = c->sm_count;
 
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_LUT) {
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP ||
+        algo == VLUT_ALGO_LUT) {
         // stream-K workspace: two private partial-tile slots per persistent CTA (no initialisation needed) and
         // self-resetting per-tile arrival counters (zeroed once at (re)allocation)
         bool grew = false;
         const size_t pb = (size_t) c->sm_count * 6 * 128 * 128 * sizeof(int32_t);  // 4 partial-tile slots + 2 scratch per CTA
         if (c->part.reserve(pb) != cudaSuccess) return VLUT_ERR_NOMEM;
-        const size_t cb = (size_t) ((g.Npad / TILE_ROWS) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
+        const size_t cb = (size_t) ((g.Npad / TILE_ROWS + 1) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));
         g.part = (int32_t *) c->part.p;
@@ -392,6 +393,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
         case VLUT_ALGO_TC2:
             if (!gemm_tc3_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tc3(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_TCP:
+            if (!gemm_tc5_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tc5(g, c->stream, &launches);
             break;
         case VLUT_ALGO_TC1:
             if (!gemm_tc_supported(type, K, N, T) || g.n_out) return VLUT_ERR_UNSUPPORTED;

@@ -1,0 +1,103 @@
+// epilogue.cuh -- accumulator drain shared by the tcgen05 kernels (gemm_tc4.cu, gemm_tc5.cu).
+//
+// The first version of the drain spent ~350 SASS instructions per 16 accumulator columns (per-value branches for the
+// exact path, per-store token predicates, 64-bit index arithmetic) and was issue-latency bound: one epilogue warp per
+// scheduler needed ~18,000 clk per 128-column tile, more than twice the tile's tensor-pipe time
+// (profiles/r1_ncu_tc5_T2048_source.txt).  The hot cases -- fast path (one drain per tile run), complete tile -> fp32
+// output, or split tile -> int32 partial slot -- are specialised here: branch-free per value, vector shared-memory reads
+// of the per-token corrections and scales, the next tcgen05.ld in flight while the current 16 columns are converted and
+// stored.  The exact (per-K-group int16 wrap) path keeps the generic code in the kernels.
+#pragma once
+#include "ptx.cuh"
+#include "vlut_common.cuh"
+
+namespace vlut {
+namespace epi {
+
+// tcgen05.wait::ld that also "produces" the loaded registers, so no consumer can be scheduled above it
+__device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&v)[16]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])::"memory");
+}
+
+// 16 final int32 sums of one weight row (tokens t .. t+15) -> fp32 outputs: out[(t+i) * ldo + n] = (float) x * s[t+i]
+// (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all).
+template <int OUT>
+__device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_smem, bool ws, float w_scale, float *out0,
+                                        float *const *outs, int n_out, int64_t idx0, int64_t ldo, int nv) {
+    float f[16];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const float4 s = *reinterpret_cast<const float4 *>(sc_smem + 4 * j);
+        f[4 * j + 0] = (float) x[4 * j + 0] * s.x;
+        f[4 * j + 1] = (float) x[4 * j + 1] * s.y;
+        f[4 * j + 2] = (float) x[4 * j + 2] * s.z;
+        f[4 * j + 3] = (float) x[4 * j + 3] * s.w;
+    }
+    if (ws) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) f[i] *= w_scale;
+    }
+    if (nv >= 16) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) store_out<OUT>(out0, outs, n_out, idx0 + i * ldo, f[i]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            if (i < nv) store_out<OUT>(out0, outs, n_out, idx0 + i * ldo, f[i]);
+    }
+}
+
+// One 16-column chunk of a fast-path drain: subtract the u8-code offset correction, then store (fp32 output or partial slot).
+template <int OUT, bool TO_SLOT>
+__device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, const int32_t *s_gs, const float *s_sc, bool ws,
+                                           float w_scale, float *out0, float *const *outs, int n_out, int64_t idx0,
+                                           int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m) {
+    int32_t x[16];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const int4 g = *reinterpret_cast<const int4 *>(s_gs + c0 + 4 * j);
+        x[4 * j + 0] = (int32_t) v[4 * j + 0] - g.x;
+        x[4 * j + 1] = (int32_t) v[4 * j + 1] - g.y;
+        x[4 * j + 2] = (int32_t) v[4 * j + 2] - g.z;
+        x[4 * j + 3] = (int32_t) v[4 * j + 3] - g.w;
+    }
+    if (TO_SLOT) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) __stcg(slot_m + (c0 + i) * 128, x[i]);
+    } else if (nvalid) {
+        store16<OUT>(x, s_sc + c0, ws, w_scale, out0, outs, n_out, idx0 + (int64_t) c0 * ldo, ldo, tvalid - c0);
+    }
+}
+
+// Fast-path drain of one accumulator (NT columns of this thread's TMEM lane).  `ta` = TMEM address of column 0 for this
+// warp's lane quadrant; s_gs / s_sc = per-token correction and scale (shared memory, 16-byte aligned); idx0 = t0 * ldo + n;
+// tvalid = T - t0; slot_m = partial slot + m (TO_SLOT).  Warp-collective: every lane must call it.
+template <int NT, int OUT, bool TO_SLOT>
+__device__ __forceinline__ void drain_fast(uint32_t ta, const int32_t *s_gs, const float *s_sc, float w_scale, float *out0,
+                                           float *const *outs, int n_out, int64_t idx0, int64_t ldo, int tvalid, bool nvalid,
+                                           int32_t *slot_m) {
+    const bool ws = (w_scale != 1.0f);
+    uint32_t va[16];
+    ptx::tmem_ld_32x32b_x16(ta, va);
+    if constexpr (NT == 16) {
+        tmem_ld_wait_dep(va);
+        fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m);
+    } else {
+        uint32_t vb[16];
+#pragma unroll 1
+        for (int c0 = 0; c0 < NT; c0 += 32) {
+            tmem_ld_wait_dep(va);
+            ptx::tmem_ld_32x32b_x16(ta + c0 + 16, vb);
+            fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m);
+            tmem_ld_wait_dep(vb);
+            if (c0 + 32 < NT) ptx::tmem_ld_32x32b_x16(ta + c0 + 32, va);
+            fast_chunk<OUT, TO_SLOT>(vb, c0 + 16, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid,
+                                     slot_m);
+        }
+    }
+}
+
+}  // namespace epi
+}  // namespace vlut

@@ -18,6 +18,7 @@
 //   warp 12     TMA producer        warp 13     MMA issuer          warp 14  TMEM allocator
 #include <stdlib.h>
 
+#include "epilogue.cuh"
 #include "ptx.cuh"
 #include "vlut_common.cuh"
 
@@ -95,8 +96,8 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     __shared__ __align__(8) uint64_t s_accfull[2], s_accempty[2];
     __shared__ uint32_t s_tmem_base;
     __shared__ int s_last;
-    __shared__ int32_t s_gs[NT];
-    __shared__ float s_sc[NT];
+    __shared__ __align__(16) int32_t s_gs[NT];
+    __shared__ __align__(16) float s_sc[NT];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int S = p.nstages;
@@ -408,22 +409,35 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 mark(0);
                 ptx::tc_fence_after();
                 const uint32_t ta = tmem_base + ((uint32_t) (ew * 32) << 16) + ab * NT;
+                if (fast) {
+                    // hot path: one drain per tile run, branch-free per value (epilogue.cuh)
+                    const int64_t idx0 = t0 * p.g.ldo + n;
+                    const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
+                    if (complete)
+                        epi::drain_fast<NT, OUT, false>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                                                        p.g.ldo, tvalid, n < p.g.N, nullptr);
+                    else
+                        epi::drain_fast<NT, OUT, true>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                                                       p.g.ldo, tvalid, n < p.g.N, slot + m);
+                } else {
+                    // exact path: int16 wrap per K-group, running totals in the scratch tile
 #pragma unroll 1
-                for (int c0 = 0; c0 < NT; c0 += 16) {
-                    uint32_t v[16];
-                    ptx::tmem_ld_32x32b_x16(ta + c0, v);
-                    ptx::tmem_ld_wait();
-                    int32_t vals[16];
+                    for (int c0 = 0; c0 < NT; c0 += 16) {
+                        uint32_t v[16];
+                        ptx::tmem_ld_32x32b_x16(ta + c0, v);
+                        ptx::tmem_ld_wait();
+                        int32_t vals[16];
 #pragma unroll
-                    for (int i = 0; i < 16; i++) {
-                        const int32_t x = (int32_t) v[i] - s_gs[c0 + i];
-                        vals[i] = fast ? x : ((u == ra) ? wrap16(x) : tots[(c0 + i) * 128 + et] + wrap16(x));
-                    }
-                    if (u == rb) {
-                        emit(c0, vals);
-                    } else {
+                        for (int i = 0; i < 16; i++) {
+                            const int32_t x = (int32_t) v[i] - s_gs[c0 + i];
+                            vals[i] = (u == ra) ? wrap16(x) : tots[(c0 + i) * 128 + et] + wrap16(x);
+                        }
+                        if (u == rb) {
+                            emit(c0, vals);
+                        } else {
 #pragma unroll
-                        for (int i = 0; i < 16; i++) tots[(c0 + i) * 128 + et] = vals[i];
+                            for (int i = 0; i < 16; i++) tots[(c0 + i) * 128 + et] = vals[i];
+                        }
                     }
                 }
                 ptx::tc_fence_before();
@@ -464,16 +478,9 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
 #pragma unroll
                             for (int i = 0; i < 16; i++) acc[i] += a[i];
                         }
-                        if (n < p.g.N) {
-#pragma unroll
-                            for (int i = 0; i < 16; i++) {
-                                if (t0 + c0 + i < p.g.T) {
-                                    float v = (float) acc[i] * s_sc[c0 + i];
-                                    if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                                    store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c0 + i) * p.g.ldo + n, v);
-                                }
-                            }
-                        }
+                        if (n < p.g.N)
+                            epi::store16<OUT>(acc, s_sc + c0, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs, p.g.n_out,
+                                              (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0));
                     }
                     if (et == 0) p.g.counters[tile] = 0;
                 }

@@ -1,0 +1,590 @@
+// gemm_tc5.cu -- VLUT_ALGO_TCP: the Vec-LUT GEMM on CTA PAIRS (cluster of 2, tcgen05 cta_group::2, M = 256).
+//
+// Why (profiles/r1_timeline_tc4_T512.txt): with 128 rows x 128 tokens per CTA every 512-k A block
+// needs 64 KB of int8 activations + 16 KB of weights from L2 for 1024 clk of tensor-pipe time = 80 B/clk/SM, twice what
+// the L2 fabric sustains per SM (~6300 B/clk chip-wide = 42.6 B/clk/SM), and the 40 KB stages leave room for only two A
+// blocks of look-ahead: the single-CTA kernels are shared-memory-fill bound from T = 256 up.  A CTA pair halves the
+// activation traffic: one tcgen05.mma.cta_group::2 multiplies 256 weight rows (128 per CTA, unpacked into each CTA's own
+// TMEM) with a 128-token activation tile of which each CTA loads and holds only HALF (64 tokens); the tensor cores read
+// the peer's half over the pair's shared-memory link.  Per CTA and A block: 32 KB + 16 KB = 48 KB (47 B/clk), stages of
+// 24 KB, eight stages = four A blocks of look-ahead.
+//
+// Roles per CTA (same warp layout as gemm_tc4.cu):
+//   warps 0-3 epilogue, 4-11 decode, 12 TMA producer, 13 MMA issuer (even CTA only), 14 TMEM allocator.
+// Cross-CTA protocol: every CTA has its own stage ring (full/empty), A ring (aempty) and accumulator barriers (accfull);
+// the even CTA ("leader") owns afull[] (16 arrivals: 8 decode warps of each CTA -- a decode warp has waited for its CTA's
+// stage, so A-ready implies that CTA's half of the activations has landed) and accempty[] (8 arrivals: 4 epilogue warps of
+// each CTA).  The leader's commits are multicast to both CTAs.
+#include <stdlib.h>
+
+#include "epilogue.cuh"
+#include "ptx.cuh"
+#include "vlut_common.cuh"
+
+namespace vlut {
+
+long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
+
+namespace tc5 {
+
+constexpr int THREADS = 480;
+constexpr int SPA = 4;             // 128-k sub-blocks per A stage / decode->MMA hand-off
+constexpr int A_COLS = SPA * 32;   // TMEM columns of one A stage
+constexpr int MAX_STAGES = 12;
+constexpr int SUB_W_BYTES = 4096;
+
+struct Params {
+    GemmArgs g;
+    int KB, G, gsub, RT, RP, TT, U;
+    int nstages, stage_bytes;
+    int allow_fast, pdl;
+    int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores, 16 no drain
+    long long *dbg;
+};
+
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t) ((smem_addr & 0x3FFFFu) >> 4);
+    d |= (uint64_t) 1 << 16;
+    d |= (uint64_t) (1024 >> 4) << 32;
+    d |= (uint64_t) 1 << 46;
+    d |= (uint64_t) 2 << 61;
+    return d;
+}
+// kind::i8, A = u8 (K-major, TMEM), B = s8 (K-major), D = s32, M = 256 across the pair, N = n
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+    return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (256 >> 4) << 24);
+}
+
+// units of this PAIR: unit = (row-pair tile rp, token tile tt, K-group g), ordered [rp][tt][g]
+struct Walk {
+    int u, u0, u1, G, TT, gsub, KB;
+    int tile, g, rp, tt, kb0, nsub;
+    __device__ __forceinline__ void init(const Params &p, int u0_, int u1_) {
+        u = u0 = u0_; u1 = u1_; G = p.G; TT = p.TT; gsub = p.gsub; KB = p.KB;
+        tile = u / G; g = u - tile * G;
+        rp = tile / TT; tt = tile - rp * TT;
+        refresh();
+    }
+    __device__ __forceinline__ void refresh() { kb0 = g * gsub; nsub = min(gsub, KB - kb0); }
+    __device__ __forceinline__ bool valid() const { return u < u1; }
+    __device__ __forceinline__ int run_last() const { return min(u1 - 1, u - g + G - 1); }
+    __device__ __forceinline__ void next() {
+        ++u;
+        if (++g == G) { g = 0; ++tile; if (++tt == TT) { tt = 0; ++rp; } }
+        refresh();
+    }
+};
+
+struct Ring {
+    int i, n;
+    uint32_t ph;
+    __device__ __forceinline__ void init(int n_) { i = 0; n = n_; ph = 0; }
+    __device__ __forceinline__ void advance() { if (++i == n) { i = 0; ph ^= 1; } }
+};
+
+// NT: tokens per tile (N of the pair MMA); every CTA stages NT/2 of them.  OUT: epilogue store flavour.
+template <int NT, int SPS, int OUT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
+    static_assert(SPA % SPS == 0, "an A stage is a whole number of shared-memory stages");
+    static_assert(NT % 32 == 0 && NT >= 32 && NT <= 256, "pair MMA with A in TMEM: N multiple of 32");
+    constexpr int NH = NT / 2;                       // tokens staged by this CTA
+    constexpr int ACT_BYTES = NH * 128;              // one 128-k sub-block of this CTA's half
+    constexpr int W_OFF = SPS * ACT_BYTES;           // stage: [activations][weights]
+    constexpr uint32_t A_COL0 = 2 * NT;              // two accumulators of NT columns, then two A stages
+    static_assert(A_COL0 + 2 * A_COLS <= 512, "TMEM budget");
+    extern __shared__ __align__(1024) uint8_t smem_raw[];
+    __shared__ __align__(8) uint64_t s_full[MAX_STAGES], s_empty[MAX_STAGES];
+    __shared__ __align__(8) uint64_t s_afull[2], s_aempty[2];
+    __shared__ __align__(8) uint64_t s_accfull[2], s_accempty[2];
+    __shared__ uint32_t s_tmem_base;
+    __shared__ int s_last;
+    __shared__ __align__(16) int32_t s_gs[NT];
+    __shared__ __align__(16) float s_sc[NT];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int S = p.nstages;
+    const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+    const uint32_t rank = ptx::cluster_ctarank();    // 0 = leader (issues the MMAs), 1 = peer
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+    if (p.pdl) ptx::pdl_launch_dependents();
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < S; s++) {
+            ptx::mbar_init(ptx::smem_u32(&s_full[s]), 1);
+            ptx::mbar_init(ptx::smem_u32(&s_empty[s]), 8 + 1);  // 8 local decode warps + the leader's multicast commit
+        }
+        for (int d = 0; d < 2; d++) {
+            ptx::mbar_init(ptx::smem_u32(&s_afull[d]), 16);     // used in the leader: decode warps of both CTAs
+            ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
+            ptx::mbar_init(ptx::smem_u32(&s_accfull[d]), 1);
+            ptx::mbar_init(ptx::smem_u32(&s_accempty[d]), 8);   // used in the leader: epilogue warps of both CTAs
+        }
+        ptx::fence_barrier_init();
+    }
+    if (warp == 14) {
+        ptx::tmem_alloc_pair(ptx::smem_u32(&s_tmem_base), 512);
+        ptx::tmem_relinquish_pair();
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();  // the peer's barriers are initialised before anybody arrives on them
+    ptx::tc_fence_after();
+    const uint32_t tmem_base = s_tmem_base;
+    float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
+
+    const int u0 = (int) (((int64_t) pair * p.U) / npairs);
+    const int u1 = (int) (((int64_t) (pair + 1) * p.U) / npairs);
+    auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
+    // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
+    const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
+    const long long t_start = dbg_on ? clock64() : 0;
+    int n_ev = 0, ev_role = 0;
+    auto mark = [&](int kind) {
+        if (dbg_on) {
+            const int k = n_ev - (int) p.dbg[0];
+            if (k >= 0 && k < 24) {
+                p.dbg[8192 + (ev_role * 24 + k) * 2] = clock64() - t_start;
+                p.dbg[8192 + (ev_role * 24 + k) * 2 + 1] = kind;
+            }
+            ++n_ev;
+        }
+    };
+
+    if (warp == 12) {
+        ev_role = 0;
+        // ===================== TMA producer: this CTA's weight rows and its half of the activation tile ==============
+        const uint64_t pol_w = ptx::policy_evict_first();
+        const uint64_t pol_a = ptx::policy_evict_last();
+        Walk w;
+        w.init(p, u0, u1);
+        Ring st;
+        st.init(S);
+        int early = p.pdl ? S : 0;  // stages whose WEIGHTS are requested before griddepcontrol.wait (static data)
+        bool waited = !p.pdl;
+        const Walk wa = w;
+        const Ring sta = st;
+        auto issue = [&](const Walk &ww, const Ring &rr, bool do_w, bool do_a, int ab0, int s0, int ns) {
+            const uint32_t full = ptx::smem_u32(&s_full[rr.i]);
+            const uint32_t dst = smem_base + rr.i * p.stage_bytes;
+            if (do_w) {
+                ptx::mbar_arrive_expect_tx(full, ns * (ACT_BYTES + SUB_W_BYTES));
+                const int rt = min(2 * ww.rp + (int) rank, p.RT - 1);  // odd strip count: the last peer re-reads a valid strip
+                const uint8_t *w0 = p.g.w + ((int64_t) rt * p.KB + ww.kb0 + ab0 + s0) * SUB_W_BYTES;
+                ptx::bulk_g2s_hint(dst + W_OFF, w0, ns * SUB_W_BYTES, full, pol_w);
+            }
+            if (do_a) {
+                const int8_t *a = p.g.act.q_sw + (((int64_t) ww.tt * p.KB + ww.kb0 + ab0 + s0) * NT + rank * NH) * 128;
+                for (int sb = 0; sb < ns; sb++)
+                    ptx::bulk_g2s_hint(dst + sb * ACT_BYTES, a + (int64_t) sb * NT * 128, ACT_BYTES, full, pol_a);
+            }
+        };
+        // activations of the first `n` stages (the ones whose weights went out early)
+        auto late_acts = [&](int n) {
+            Walk wb = wa;
+            Ring rb = sta;
+            for (int e = 0; e < n && wb.valid(); wb.next())
+                for (int b0 = 0; b0 < wb.nsub && e < n; b0 += SPA) {
+                    const int nb = min(SPA, wb.nsub - b0);
+                    for (int t0 = 0; t0 < nb && e < n; t0 += SPS, ++e) {
+                        if (ptx::elect_one()) issue(wb, rb, false, true, b0, t0, min(SPS, nb - t0));
+                        __syncwarp();
+                        rb.advance();
+                    }
+                }
+        };
+        for (; w.valid(); w.next()) {
+            for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
+                const int na = min(SPA, w.nsub - ab0);
+                for (int s0 = 0; s0 < na; s0 += SPS) {
+                    const int ns = min(SPS, na - s0);
+                    if (early > 0) {
+                        if (ptx::elect_one()) issue(w, st, true, false, ab0, s0, ns);  // fresh barrier: no empty wait
+                        __syncwarp();
+                        st.advance();
+                        --early;
+                        continue;
+                    }
+                    if (!waited) {
+                        ptx::pdl_wait();
+                        waited = true;
+                        late_acts(S);
+                    }
+                    ptx::mbar_wait(ptx::smem_u32(&s_empty[st.i]), st.ph ^ 1);
+                    mark(0);
+                    if (ptx::elect_one()) issue(w, st, true, true, ab0, s0, ns);
+                    __syncwarp();
+                    st.advance();
+                }
+            }
+        }
+        if (!waited) {
+            ptx::pdl_wait();  // fewer than S stages in total
+            late_acts(S);
+        }
+    } else if (warp == 13) {
+        ev_role = 1;
+        // ===================== MMA issuer (leader CTA only): one M=256 MMA feeds both CTAs' accumulators ============
+        if (rank == 0) {
+            constexpr uint32_t idesc = make_idesc(NT);
+            Walk w;
+            w.init(p, u0, u1);
+            Ring st, ar;
+            st.init(S);
+            ar.init(2);
+            uint32_t ndrain = 0;  // drains committed so far; accumulator buffer = ndrain % 2
+            if (p.pdl) ptx::pdl_wait();  // tile_fast below is written by the predecessor (quantise) kernel
+            int run_tile = -1;
+            bool fast = false, open = false;
+            for (; w.valid(); w.next()) {
+                if (w.tile != run_tile) {
+                    run_tile = w.tile;
+                    fast = tile_fast(w.tt);
+                }
+                const uint32_t ab = ndrain & 1;
+                if (!open) {
+                    ptx::mbar_wait_cluster(ptx::smem_u32(&s_accempty[ab]), ((ndrain >> 1) & 1) ^ 1);
+                    ptx::tc_fence_after();
+                }
+                const uint32_t d_tmem = tmem_base + ab * NT;
+                for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
+                    const int na = min(SPA, w.nsub - ab0);
+                    ptx::mbar_wait_cluster(ptx::smem_u32(&s_afull[ar.i]), ar.ph);
+                    mark(1);
+                    ptx::tc_fence_after();
+                    if (ptx::elect_one()) {
+                        const uint32_t a_tmem = tmem_base + A_COL0 + ar.i * A_COLS;
+                        Ring st2 = st;
+                        for (int s0 = 0; s0 < na; s0 += SPS) {
+                            const int ns = min(SPS, na - s0);
+                            const uint32_t stage = smem_base + st2.i * p.stage_bytes;
+                            for (int sb = 0; sb < ns; sb++) {
+                                const uint64_t b_desc = make_smem_desc(stage + sb * ACT_BYTES);
+#pragma unroll
+                                for (int ks = 0; ks < 4; ks++) {
+                                    const uint32_t accumulate = (open || ab0 > 0 || s0 > 0 || sb > 0 || ks > 0) ? 1u : 0u;
+                                    if (!(p.abl & 2))
+                                        ptx::umma_i8_ts_pair(d_tmem, a_tmem + (s0 + sb) * 32 + ks * 8,
+                                                             b_desc + (uint64_t) (ks * 2), idesc, accumulate);
+                                }
+                            }
+                            ptx::umma_commit_pair(ptx::smem_u32(&s_empty[st2.i]), 3);
+                            st2.advance();
+                        }
+                        ptx::umma_commit_pair(ptx::smem_u32(&s_aempty[ar.i]), 3);
+                    }
+                    __syncwarp();
+                    mark(8);
+                    for (int s0 = 0; s0 < na; s0 += SPS) st.advance();
+                    ar.advance();
+                }
+                // exact path: drain after every unit; fast path: drain after the last unit of the tile run
+                if (!fast || w.u == w.run_last()) {
+                    if (ptx::elect_one()) ptx::umma_commit_pair(ptx::smem_u32(&s_accfull[ab]), 3);
+                    __syncwarp();
+                    ++ndrain;
+                    open = false;
+                } else {
+                    open = true;
+                }
+            }
+        }
+    } else if (warp >= 4 && warp < 12) {
+        // ===================== decode: packed 2-bit codes -> u8 A operand in this CTA's TMEM, 8 warps per A block ====
+        ev_role = 2;
+        const int q = (warp - 4) & 3;   // TMEM lane quadrant (== warp % 4)
+        const int h = (warp - 4) >> 2;  // which half of every stage this warp unpacks
+        const int m = q * 32 + lane;    // weight row inside the strip == TMEM lane
+        constexpr int CPS = 2 * SPS;    // 64-k chunks per stage
+        constexpr int CPH = CPS / 2;    // chunks per half
+        const uint32_t afull_leader0 = ptx::mapa(ptx::smem_u32(&s_afull[0]), 0);
+        const uint32_t afull_leader1 = ptx::mapa(ptx::smem_u32(&s_afull[1]), 0);
+        Walk w;
+        w.init(p, u0, u1);
+        Ring st, ar;
+        st.init(S);
+        ar.init(2);
+        for (; w.valid(); w.next()) {
+            for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
+                const int na = min(SPA, w.nsub - ab0);
+                bool a_free = false;
+                const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + ar.i * A_COLS;
+                for (int s0 = 0; s0 < na; s0 += SPS) {
+                    const int ns = min(SPS, na - s0);
+                    ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
+                    mark(0);
+                    const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
+                    uint4 cw[CPH];
+#pragma unroll
+                    for (int c = 0; c < CPH; c++)
+                        if (h * CPH + c < 2 * ns) cw[c] = ptx::lds128(w_s + (h * CPH + c) * TILE_BYTES);
+                    __syncwarp();
+                    if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));  // this warp's share is consumed
+                    st.advance();
+                    if (!a_free) {
+                        ptx::mbar_wait(ptx::smem_u32(&s_aempty[ar.i]), ar.ph ^ 1);
+                        mark(1);
+                        ptx::tc_fence_after();
+                        a_free = true;
+                    }
+#pragma unroll
+                    for (int c = 0; c < CPH; c++) {
+                        if (h * CPH + c < 2 * ns) {
+                            const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+                            uint32_t r[16];
+#pragma unroll
+                            for (int j = 0; j < 4; j++) {
+                                // shifts as multiply-high on the FMA pipe, masks on the ALU pipe: both pipes work
+                                r[4 * j + 0] = wv[j] & 0x03030303u;
+                                r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                                r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                                r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
+                            }
+                            if (!(p.abl & 1)) ptx::tmem_st_32x32b_x16(taddr0 + s0 * 32 + (h * CPH + c) * 16, r);
+                        }
+                    }
+                }
+                if (!(p.abl & 4)) ptx::tmem_st_wait();
+                ptx::tc_fence_before();
+                __syncwarp();
+                // A-ready goes to the leader; it also tells the leader that this CTA's activation half has landed
+                if (lane == 0) ptx::mbar_arrive_cluster(ar.i ? afull_leader1 : afull_leader0);
+                mark(9);
+                ar.advance();
+            }
+        }
+    } else if (warp < 4) {
+        // ===================== epilogue: this CTA's 128 rows x NT tokens =====================
+        ev_role = 3;
+        const int ew = warp;
+        const int m = ew * 32 + lane;
+        const int et = threadIdx.x;  // 0..127
+        if (p.pdl) ptx::pdl_wait();  // reads predecessor outputs; owns all global writes of this kernel
+        uint32_t ndrain = 0;
+        const uint32_t accempty_leader0 = ptx::mapa(ptx::smem_u32(&s_accempty[0]), 0);
+        const uint32_t accempty_leader1 = ptx::mapa(ptx::smem_u32(&s_accempty[1]), 0);
+        // exact-path running totals: this CTA's scratch tile in the (L2-resident) workspace
+        int32_t *const tots = p.g.part + ((int64_t) gridDim.x * 2 + blockIdx.x) * (NT * 128);
+        Walk w;
+        w.init(p, u0, u1);
+        while (w.valid()) {
+            // ---- one tile run: units [ra, rb] of one output tile ----
+            const int ra = w.u, rb = w.run_last();
+            const int g_begin = w.g, g_end = w.g + (rb - ra);
+            const bool fast = tile_fast(w.tt);
+            const bool complete = (g_begin == 0) && (g_end == p.G - 1);
+            const int run_slot = (ra == u0) ? 0 : 1;
+            const int tile = w.tile;
+            const int64_t n = ((int64_t) 2 * w.rp + rank) * TILE_ROWS + m;
+            const int64_t t0 = (int64_t) w.tt * NT;
+            int32_t *const slot = p.g.part + ((int64_t) blockIdx.x * 2 + run_slot) * (NT * 128);
+            if (et < NT) s_sc[et] = __ldg(p.g.act.scales + t0 + et);
+
+            auto emit = [&](int c0, const int32_t (&vals)[16]) {
+                if (complete) {
+                    if (n < p.g.N && !(p.abl & 8)) {
+#pragma unroll
+                        for (int i = 0; i < 16; i++) {
+                            if (t0 + c0 + i < p.g.T) {
+                                float v = (float) vals[i] * s_sc[c0 + i];
+                                if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
+                                store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c0 + i) * p.g.ldo + n, v);
+                            }
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 16; i++) __stcg(slot + (c0 + i) * 128 + m, vals[i]);
+                }
+            };
+
+            for (int u = ra; u <= rb; u++, w.next()) {
+                if (fast && u != rb) continue;  // fast path: a single drain at the end of the run
+                const uint32_t ab = ndrain & 1;
+                for (int i = et; i < NT; i += 128)
+                    s_gs[i] = __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + w.g + 1) -
+                              __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + (fast ? g_begin : w.g));
+                ptx::bar_sync(1, 128);
+                ptx::mbar_wait(ptx::smem_u32(&s_accfull[ab]), (ndrain >> 1) & 1);
+                mark(0);
+                ptx::tc_fence_after();
+                const uint32_t ta = tmem_base + ((uint32_t) (ew * 32) << 16) + ab * NT;
+                if (fast) {
+                    // hot path: one drain per tile run, branch-free per value (epilogue.cuh)
+                    const int64_t idx0 = t0 * p.g.ldo + n;
+                    const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
+                    if (complete)
+                        epi::drain_fast<NT, OUT, false>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                                                        p.g.ldo, tvalid, n < p.g.N, nullptr);
+                    else
+                        epi::drain_fast<NT, OUT, true>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                                                       p.g.ldo, tvalid, n < p.g.N, slot + m);
+                } else {
+                    // exact path: int16 wrap per K-group, running totals in the scratch tile
+#pragma unroll 1
+                    for (int c0 = 0; c0 < NT; c0 += 16) {
+                        uint32_t v[16];
+                        ptx::tmem_ld_32x32b_x16(ta + c0, v);
+                        ptx::tmem_ld_wait();
+                        int32_t vals[16];
+#pragma unroll
+                        for (int i = 0; i < 16; i++) {
+                            const int32_t x = (int32_t) v[i] - s_gs[c0 + i];
+                            vals[i] = (u == ra) ? wrap16(x) : tots[(c0 + i) * 128 + et] + wrap16(x);
+                        }
+                        if (u == rb) {
+                            emit(c0, vals);
+                        } else {
+#pragma unroll
+                            for (int i = 0; i < 16; i++) tots[(c0 + i) * 128 + et] = vals[i];
+                        }
+                    }
+                }
+                ptx::tc_fence_before();
+                __syncwarp();
+                if (lane == 0) ptx::mbar_arrive_cluster(ab ? accempty_leader1 : accempty_leader0);
+                mark(7);
+                ++ndrain;
+                ptx::bar_sync(1, 128);  // s_gs is rewritten by the next drain
+            }
+
+            if (!complete) {
+                // split tile (stream-K): partial parked above; the last CTA to arrive sums all slots and finishes
+                __threadfence();
+                ptx::bar_sync(1, 128);
+                int32_t *const counter = p.g.counters + tile * 2 + rank;
+                if (et == 0) {
+                    const int ndone = g_end - g_begin + 1;
+                    const int old = atomicAdd(counter, ndone);
+                    s_last = (old + ndone == p.G);
+                }
+                ptx::bar_sync(1, 128);
+                if (s_last) {
+                    __threadfence();
+                    const long long ua = (long long) tile * p.G, ub = ua + p.G - 1;
+                    const int b_lo = (int) (((ua + 1) * npairs - 1) / p.U);
+                    const int b_hi = (int) (((ub + 1) * npairs - 1) / p.U);
+#pragma unroll 1
+                    for (int c0 = 0; c0 < NT; c0 += 16) {
+                        int32_t acc[16];
+#pragma unroll
+                        for (int i = 0; i < 16; i++) acc[i] = 0;
+                        for (int b = b_lo; b <= b_hi; b++) {
+                            const int b_u0 = (int) (((long long) b * p.U) / npairs);
+                            const int b_slot = (b_u0 / p.G == tile) ? 0 : 1;
+                            const int32_t *ps = p.g.part + ((int64_t) (2 * b + rank) * 2 + b_slot) * (NT * 128) + m;
+                            int32_t a[16];
+#pragma unroll
+                            for (int i = 0; i < 16; i++) a[i] = __ldcg(ps + (c0 + i) * 128);
+#pragma unroll
+                            for (int i = 0; i < 16; i++) acc[i] += a[i];
+                        }
+                        if (n < p.g.N)
+                            epi::store16<OUT>(acc, s_sc + c0, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs, p.g.n_out,
+                                              (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0));
+                    }
+                    if (et == 0) *counter = 0;
+                }
+            }
+            ptx::bar_sync(1, 128);  // s_sc / s_last are reused by the next run
+        }
+    }
+
+    // ---- teardown: nobody leaves (or frees TMEM) while the peer may still read this CTA's shared memory / TMEM ----
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::cluster_sync();
+    if (warp == 14) {
+        ptx::tc_fence_after();
+        ptx::tmem_dealloc_pair(tmem_base, 512);
+    }
+}
+
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return v ? atoi(v) : dflt;
+}
+
+template <int NT, int SPS, int OUT>
+static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
+    const int budget = env_int("VLUT_TC_SMEM_KB", 200) * 1024;
+    p.stage_bytes = SPS * (NT / 2 * 128 + SUB_W_BYTES);  // multiple of 1024
+    int ns = (budget - 1024) / p.stage_bytes;
+    if (ns > MAX_STAGES) ns = MAX_STAGES;
+    int forced = env_int("VLUT_TC_STAGES", 0);
+    if (forced > 0 && forced < SPA / SPS) forced = SPA / SPS;
+    if (forced > 0 && forced < ns) ns = forced;
+    if (ns < SPA / SPS) return cudaErrorInvalidValue;  // every stage of one A block is live at once
+    p.nstages = ns;
+    const size_t smem = (size_t) ns * p.stage_bytes + 1024;
+    auto kern = kernel<NT, SPS, OUT>;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    if (e != cudaSuccess) return e;
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = p.pdl ? 1 : 0;
+    // persistent: one CTA pair per co-resident cluster
+    int npairs = sm_count / 2;
+    static int max_clusters[3][3] = {};  // cached per (NT, OUT) instantiation below
+    int &cached = max_clusters[NT == 128 ? 0 : (NT == 64 ? 1 : 2)][OUT];
+    if (cached == 0) {
+        cfg.gridDim = dim3((unsigned) (2 * npairs));
+        int n = 0;
+        e = cudaOccupancyMaxActiveClusters(&n, kern, &cfg);
+        if (e != cudaSuccess) return e;
+        if (n < 1) return cudaErrorInvalidConfiguration;
+        cached = n;
+    }
+    if (npairs > cached) npairs = cached;
+    const int ptiles = p.RP * p.TT;
+    if (ptiles <= npairs && ptiles * 10 >= npairs * 7) npairs = ptiles;  // whole tiles per pair: no fix-up
+    npairs = env_int("VLUT_TC_GRID", 2 * npairs) / 2;
+    if (npairs > p.U) npairs = p.U;
+    if (npairs < 1) npairs = 1;
+    cfg.gridDim = dim3((unsigned) (2 * npairs));
+    return cudaLaunchKernelEx(&cfg, kern, p);
+}
+
+template <int NT, int SPS>
+static cudaError_t launch_one(Params &p, int sm_count, cudaStream_t s) {
+    if (p.g.n_out == 0) return launch_out<NT, SPS, 0>(p, sm_count, s);
+    return p.g.multicast ? launch_out<NT, SPS, 2>(p, sm_count, s) : launch_out<NT, SPS, 1>(p, sm_count, s);
+}
+
+}  // namespace tc5
+
+bool gemm_tc5_supported(int type, int64_t K, int64_t N, int64_t T) {
+    return type_valid(type) && T > 32 && K >= 4 && N >= 1 && ceil_div(K, group_size(type)) <= 64;
+}
+
+cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
+    tc5::Params p{};
+    p.g = g;
+    p.KB = (int) (g.act.Kpad / 128);
+    p.gsub = g.act.gsize / 128;
+    p.G = g.act.G;
+    p.RT = (int) (g.Npad / TILE_ROWS);
+    p.RP = (p.RT + 1) / 2;
+    const int NT = g.act.NT;
+    p.TT = (int) (g.act.Tpad / NT);
+    p.U = p.RP * p.TT * p.G;
+    p.allow_fast = tc5::env_int("VLUT_TC_FAST", 1);
+    p.pdl = tc5::env_int("VLUT_PDL", 1);
+    p.abl = tc5::env_int("VLUT_TC_ABL", 0);
+    p.dbg = tc5::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, tc5::env_int("VLUT_TC_DEBUG_SKIP", 0)) : nullptr;
+    if (launches) *launches += 1;
+    switch (NT) {
+        case 64: return tc5::launch_one<64, 2>(p, g.sm_count, s);
+        case 128: return tc5::launch_one<128, 2>(p, g.sm_count, s);
+        default: return cudaErrorInvalidValue;
+    }
+}
+
+}  // namespace vlut
