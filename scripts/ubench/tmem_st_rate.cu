@@ -83,6 +83,108 @@ void run(const char *name) {
     cudaFree(d);
 }
 
+
+// decode step (as MODE 2) while one more warp keeps the tensor pipe busy with TS-mode MMAs reading the other TMEM columns
+__device__ __forceinline__ uint64_t mk_desc(uint32_t a) {
+    uint64_t d = 0;
+    d |= (uint64_t) ((a & 0x3FFFFu) >> 4);
+    d |= (uint64_t) 1 << 16;
+    d |= (uint64_t) (1024 >> 4) << 32;
+    d |= (uint64_t) 1 << 46;
+    d |= (uint64_t) 2 << 61;
+    return d;
+}
+template <int NW, int N, int NSPIN, int WAITMODE>
+__global__ void __launch_bounds__(NW * 32 + 32 + NSPIN * 32, 1) kmix(long long *out, int iters, int with_mma) {
+    extern __shared__ __align__(1024) uint8_t dyn[];
+    __shared__ __align__(16) uint4 packed[128 * 8];
+    __shared__ uint32_t tbase;
+    __shared__ __align__(8) uint64_t bar, spinbar;
+    __shared__ volatile int stop;
+    const uint32_t bsm = (ptx::smem_u32(dyn) + 1023u) & ~1023u;
+    for (int i = threadIdx.x; i < 128 * 8; i += blockDim.x) packed[i] = make_uint4(i * 2654435761u, i * 40503u, ~i, i ^ 0x55aa55aau);
+    for (int i = threadIdx.x; i < 16384 / 4; i += blockDim.x) ((uint32_t *) dyn)[i + 256] = 0x01010101u;
+    if (threadIdx.x == 0) { stop = 0; ptx::mbar_init(ptx::smem_u32(&bar), 1); ptx::mbar_init(ptx::smem_u32(&spinbar), 1); ptx::fence_barrier_init(); }
+    if (threadIdx.x < 32) { ptx::tmem_alloc(ptx::smem_u32(&tbase), 512); ptx::tmem_relinquish(); }
+    ptx::fence_proxy_async();
+    ptx::tc_fence_before();
+    __syncthreads();
+    ptx::tc_fence_after();
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (warp > NW) {
+        // waits until the decode warps are done: 0 plain try_wait loop, 1 try_wait with a suspend-time hint, 2 nanosleep back-off
+        const uint32_t sb = ptx::smem_u32(&spinbar);
+        if (WAITMODE == 0) {
+            ptx::mbar_wait(sb, 0);
+        } else if (WAITMODE == 1) {
+            uint32_t ok;
+            do {
+                asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                             : "=r"(ok) : "r"(sb), "r"(0u), "r"(0x989680u) : "memory");
+            } while (!ok);
+        } else {
+            while (!ptx::mbar_try_wait(sb, 0)) __nanosleep(64);
+        }
+    } else if (warp == NW) {
+        if (with_mma) {
+            constexpr uint32_t idesc = (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (128 >> 4) << 24);
+            const uint64_t b_desc = mk_desc(bsm);
+            uint32_t ph = 0;
+            while (!stop) {
+                if (ptx::elect_one()) {
+                    for (int j = 0; j < 16; j++) ptx::umma_i8_ts(tbase + 256, tbase + 384 + (j & 3) * 8, b_desc + (j & 3) * 2, idesc, 1);
+                    ptx::umma_commit(ptx::smem_u32(&bar));
+                }
+                __syncwarp();
+                ptx::mbar_wait(ptx::smem_u32(&bar), ph);
+                ph ^= 1;
+            }
+        }
+    } else {
+        const uint32_t taddr = tbase + ((uint32_t) ((warp & 3) * 32) << 16) + (warp >> 2) * 128;
+        const uint32_t base = ptx::smem_u32(packed) + ((warp & 3) * 32 + lane) * 16;
+        const long long t0 = clock64();
+        for (int it = 0; it < iters; it++) {
+#pragma unroll
+            for (int c = 0; c < 8; c++) {
+                uint4 w = ptx::lds128(base + c * 2048);
+                w.x += it;  // keep the unpack inside the loop
+                const uint32_t wv[4] = {w.x, w.y, w.z, w.w};
+                uint32_t v[16];
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    v[4 * j + 0] = wv[j] & 0x03030303u;
+                    v[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                    v[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                    v[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
+                }
+                ptx::tmem_st_32x32b_x16(taddr + c * 16, v);
+            }
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        const long long t1 = clock64();
+        if (threadIdx.x == 0) out[blockIdx.x] = t1 - t0;
+        asm volatile("bar.sync 1, %0;" ::"r"(NW * 32));
+        if (threadIdx.x == 0) { stop = 1; ptx::mbar_arrive(ptx::smem_u32(&spinbar)); }
+    }
+    ptx::tc_fence_before();
+    __syncthreads();
+    if (threadIdx.x < 32) { ptx::tc_fence_after(); ptx::tmem_dealloc(tbase, 512); }
+}
+template <int NW, int N, int NSPIN, int WAITMODE = 0>
+void runmix(int with_mma) {
+    long long *d; cudaMalloc(&d, 148 * sizeof(long long));
+    const int iters = 200;
+    cudaFuncSetAttribute(kmix<NW, N, NSPIN, WAITMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, 40 * 1024);
+    for (int r = 0; r < 2; r++) kmix<NW, N, NSPIN, WAITMODE><<<148, NW * 32 + 32 + NSPIN * 32, 40 * 1024>>>(d, iters, with_mma);
+    cudaError_t e = cudaDeviceSynchronize();
+    long long h[148]; cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
+    double cyc = 0; for (int i = 0; i < 148; i++) cyc += h[i]; cyc /= 148;
+    printf("decode step, %d warps x 8 chunks, %2d waiting warps (mode %d), concurrent TS MMA N=%3d %s: %.0f clk per iteration (%s)\n", NW, NSPIN, WAITMODE, N, with_mma ? "ON " : "off",
+           cyc / iters, cudaGetErrorString(e));
+    cudaFree(d);
+}
+
 int main() {
     run<4, 0>("st.32x32b.x16");
     run<8, 0>("st.32x32b.x16");
@@ -90,5 +192,9 @@ int main() {
     run<8, 1>("st.32x32b.x32");
     run<4, 2>("LDS+decode+st.x16");
     run<8, 2>("LDS+decode+st.x16");
+    runmix<4, 16, 0>(0); runmix<4, 16, 0>(1); runmix<8, 16, 0>(0); runmix<8, 16, 0>(1);
+    runmix<4, 128, 0>(1); runmix<8, 128, 0>(1);
+    runmix<4, 16, 4>(1); runmix<4, 16, 12>(1); runmix<8, 16, 8>(1);
+    runmix<4, 16, 12, 1>(1); runmix<8, 16, 8, 1>(1); runmix<4, 16, 12, 2>(1); runmix<8, 16, 8, 2>(1);
     return 0;
 }

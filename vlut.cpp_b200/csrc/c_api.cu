@@ -276,7 +276,7 @@ int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t r
 }
 
 // (re)shape the activation workspace of ctx for (type, K, T)
-static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
+static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, bool pair_layout) {
     const int64_t Kpad = round_up(K, BLOCK_K);
     const int NT = token_tile(T);
     const int64_t Tpad = round_up(T, NT);
@@ -304,21 +304,28 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T) {
     c->act.G = G;
     c->act.gsize = gsize;
     c->act.NT = NT;
+    c->act.sw_tile = (pair_layout && NT >= 64) ? NT / 2 : NT;
     c->act_K = K;
     c->act_T = T;
     c->act_type = type;
     return VLUT_OK;
 }
 
-int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
+// quantise for the kernel `algo` resolves to (the CTA-pair kernel wants half-height swizzled tiles)
+static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T, int algo) {
     if (!c || !x_dev || T <= 0 || ldx < K) return VLUT_ERR_INVALID;
     if (!type_valid(type) || K <= 0 || K % 4) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
-    int rc = prepare_act(c, type, K, T);
+    if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, 1, T);
+    int rc = prepare_act(c, type, K, T, algo == VLUT_ALGO_TCP);
     if (rc) return rc;
     CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream));
     c->launches++;
     return VLUT_OK;
+}
+
+int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
+    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO);
 }
 
 int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
@@ -327,10 +334,10 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
     // crossover table from B200 measurements (profiles/r1_crossover.txt):
-    //   T <= 256   TC   (one CTA per 128-row strip, 8-warp unpack, PDL): lowest latency
-    //   T  > 256   TCP  (CTA pairs, cta_group::2: each CTA stages half of the token tile -> less L2 -> shared-memory fill)
+    //   T <= 64   TC   (one CTA per 128-row strip, 8-warp unpack, PDL): lowest latency
+    //   T  > 64   TCP  (CTA pairs, cta_group::2: each CTA stages half of the 128-token tile -> half the activation fill)
     // TC1 / TC2 (earlier generations) stay selectable for comparison.
-    if (T > 256 && gemm_tc5_supported(type, K, N, T)) return VLUT_ALGO_TCP;
+    if (T > 64 && gemm_tc5_supported(type, K, N, T)) return VLUT_ALGO_TCP;
     if (gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
     if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
     return VLUT_ALGO_SIMPLE;
@@ -380,11 +387,21 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
 
     int launches = 0;
     cudaError_t e;
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP) {
+        // the workspace was quantised for another kernel's swizzled-tile height: rewrite q_sw from q_rm
+        const int want = (algo == VLUT_ALGO_TCP && c->act.NT >= 64) ? c->act.NT / 2 : c->act.NT;
+        if (c->act.sw_tile != want) {
+            c->act.sw_tile = want;
+            CK(launch_relayout(c->act, c->stream));
+            launches++;
+        }
+        g.act = c->act;
+    }
     switch (algo) {
         case VLUT_ALGO_SIMPLE:
             if (g.n_out) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_simple(g, c->stream);
-            launches = 1;
+            launches += 1;
             break;
         case VLUT_ALGO_TC:
             if (!gemm_tc4_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
@@ -427,14 +444,14 @@ int vlut_mul_mat_scatter(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T,
                          int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
                          int algo) {
     if (!outs_dev || n_out < 1 || n_out > 8 || (multicast && n_out != 1)) return VLUT_ERR_INVALID;
-    int rc = vlut_quantize_act(c, type, x_dev, ldx, K, T);
+    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo);
     if (rc) return rc;
     return gemm_impl(c, type, K, N, T, t2_dev, nullptr, outs_dev, n_out, multicast, ldo, w_scale, algo);
 }
 
 int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                  int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo) {
-    int rc = vlut_quantize_act(c, type, x_dev, ldx, K, T);
+    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo);
     if (rc) return rc;
     return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
 }

@@ -544,6 +544,7 @@ static cudaError_t launch_one(TcParams &p, int grid, cudaStream_t s) {
 }
 
 cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches) {
+    if (g.act.sw_tile != g.act.NT) return cudaErrorInvalidValue;  // wants full-height swizzled activation tiles
     TcParams p{};
     p.g = g;
     p.KB = (int) (g.act.Kpad / SUB_K);

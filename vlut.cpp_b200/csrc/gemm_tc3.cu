@@ -566,6 +566,7 @@ bool gemm_tc3_supported(int type, int64_t K, int64_t N, int64_t T) {
 }
 
 cudaError_t launch_gemm_tc3(const GemmArgs &g, cudaStream_t s, int *launches) {
+    if (g.act.sw_tile != g.act.NT) return cudaErrorInvalidValue;  // wants full-height swizzled activation tiles
     tc3::Params p{};
     p.g = g;
     p.KB = (int) (g.act.Kpad / 128);

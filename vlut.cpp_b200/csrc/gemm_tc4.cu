@@ -15,7 +15,7 @@
 //   * the epilogue store flavour (local, NVLink peer scatter, NVSwitch multicast) is a template parameter.
 //
 //   warps 0-3   epilogue            warps 4-11  decode (quadrant q = w%4, half h = (w-4)/4)
-//   warp 12     TMA producer        warp 13     MMA issuer          warp 14  TMEM allocator
+//   warp 12     activation producer warp 13     MMA issuer          warp 14  TMEM allocator, then weight producer
 #include <stdlib.h>
 
 #include "epilogue.cuh"
@@ -28,7 +28,9 @@ long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
 
 namespace tc4 {
 
-constexpr int THREADS = 480;
+__host__ __device__ constexpr int npw_for(int dg) { return dg == 3 ? 3 : 2; }  // weight-producer warps
+// 4 epilogue + decode + activation producer + MMA + weight producers (the first one also allocates TMEM)
+__host__ __device__ constexpr int threads_for(int dg) { return (6 + (dg == 3 ? 12 : 8) + npw_for(dg)) * 32; }
 constexpr int SPA = 4;             // 128-k sub-blocks per A stage / decode->MMA hand-off
 constexpr int A_COLS = SPA * 32;   // TMEM columns of one A stage
 constexpr int MAX_STAGES = 10;
@@ -40,6 +42,7 @@ struct Params {
     int nstages, stage_bytes;
     int allow_fast, pdl;
     long long *dbg;  // optional timeline buffer (VLUT_TC_DEBUG), else null
+    int dbg_skip;    // events to skip per role before recording
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
@@ -83,16 +86,25 @@ struct Ring {
 };
 
 // OUT: epilogue store flavour (0 local, 1 peer scatter, 2 NVSwitch multicast)
-template <int NT, int SPS, int OUT>
-__global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
+// DG: decode organisation.  1: eight warps share every A block (two A stages).  3 (small token tiles): three groups of four
+// warps take every third A block, one whole block (= one shared-memory stage) per group and turn, three A stages: three
+// decode chains (stage wait, LDS, unpack, tcgen05.st, wait::st, hand-over: ~1600 clk of mostly latency) run side by side.
+template <int NT, int SPS, int OUT, int DG>
+__global__ void __launch_bounds__(threads_for(DG), 1) kernel(const __grid_constant__ Params p) {
     static_assert(SPA % SPS == 0, "an A stage is a whole number of shared-memory stages");
+    static_assert(DG == 1 || (DG == 3 && SPS == SPA), "grouped decode: one shared-memory stage per A block");
+    constexpr int NDEC = (DG == 3) ? 12 : 8;   // decode warps 4 .. 4+NDEC-1
+    constexpr int W_ACT = 4 + NDEC, W_MMA = 5 + NDEC, W_ALLOC = 6 + NDEC;
+    constexpr int NPW = npw_for(DG);             // weight producers: warps W_ALLOC .. W_ALLOC+NPW-1, stage s by producer s % NPW
+    constexpr int NA = (DG == 3) ? 3 : 2;      // A stages in TMEM
+    constexpr int DEC_PER_BLOCK = (DG == 3) ? 4 : 8;
     constexpr int ACT_BYTES = NT * 128;
     constexpr int W_OFF = SPS * ACT_BYTES;          // stage: [activations][weights]
     constexpr uint32_t A_COL0 = 2 * NT;             // two accumulators of NT columns, then two A stages
-    static_assert(A_COL0 + 2 * A_COLS <= 512, "TMEM budget");
+    static_assert(A_COL0 + NA * A_COLS <= 512, "TMEM budget");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_full[MAX_STAGES], s_empty[MAX_STAGES];
-    __shared__ __align__(8) uint64_t s_afull[2], s_aempty[2];
+    __shared__ __align__(8) uint64_t s_afull[NA], s_aempty[NA];
     __shared__ __align__(8) uint64_t s_accfull[2], s_accempty[2];
     __shared__ uint32_t s_tmem_base;
     __shared__ int s_last;
@@ -108,18 +120,20 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; s++) {
-            ptx::mbar_init(ptx::smem_u32(&s_full[s]), 1);
-            ptx::mbar_init(ptx::smem_u32(&s_empty[s]), 8 + 1);  // 8 decode warps + the MMA commit
+            ptx::mbar_init(ptx::smem_u32(&s_full[s]), 2);       // the two producer warps (arrive.expect_tx each)
+            ptx::mbar_init(ptx::smem_u32(&s_empty[s]), DEC_PER_BLOCK + 1);  // decode warps of the block + the MMA commit
+        }
+        for (int d = 0; d < NA; d++) {
+            ptx::mbar_init(ptx::smem_u32(&s_afull[d]), DEC_PER_BLOCK);
+            ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
         }
         for (int d = 0; d < 2; d++) {
-            ptx::mbar_init(ptx::smem_u32(&s_afull[d]), 8);
-            ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
             ptx::mbar_init(ptx::smem_u32(&s_accfull[d]), 1);
             ptx::mbar_init(ptx::smem_u32(&s_accempty[d]), 4);
         }
         ptx::fence_barrier_init();
     }
-    if (warp == 14) {
+    if (warp == W_ALLOC) {
         ptx::tmem_alloc(ptx::smem_u32(&s_tmem_base), 512);
         ptx::tmem_relinquish();
     }
@@ -133,12 +147,12 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     const int u1 = (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
     auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
-    const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
+    const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0 && (warp <= 4 || warp >= 4 + NDEC);
     const long long t_start = dbg_on ? clock64() : 0;
     int n_ev = 0, ev_role = 0;
     auto mark = [&](int kind) {
         if (dbg_on) {
-            const int k = n_ev - (int) p.dbg[0];
+            const int k = n_ev - p.dbg_skip;  // (no global load here: it would stall every marked point)
             if (k >= 0 && k < 24) {
                 p.dbg[8192 + (ev_role * 24 + k) * 2] = clock64() - t_start;
                 p.dbg[8192 + (ev_role * 24 + k) * 2 + 1] = kind;
@@ -147,88 +161,54 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         }
     };
 
-    if (warp == 12) {
+    if (warp == W_ACT || warp >= W_ALLOC) {
         ev_role = 0;
-        // ===================== TMA producer =====================
-        const uint64_t pol_w = ptx::policy_evict_first();
-        const uint64_t pol_a = ptx::policy_evict_last();
+        // ===================== TMA producers =====================
+        // A warp gets one cp.async.bulk through about every memory round trip, whatever the size (~280 clk from L2, ~900 clk
+        // when the source is HBM: profiles/r1_microbench_b200.txt and the small-T timelines), but warps issue
+        // independently.  So the weight stream is issued by NPW warps taking the stages round robin (the ring length is a
+        // multiple of NPW: every barrier has one fixed producer, no phase is skipped), activations by their own warp.
+        const bool is_w = (warp >= W_ALLOC);
+        const int me = warp - W_ALLOC;
+        const uint64_t pol = is_w ? ptx::policy_evict_first() : ptx::policy_evict_last();
         Walk w;
         w.init(p, u0, u1);
         Ring st;
         st.init(S);
-        // With PDL the first S stages get their WEIGHTS before griddepcontrol.wait (weights are static), their
-        // activations (written by the predecessor kernel) after it.
-        int early = p.pdl ? S : 0;
-        bool waited = !p.pdl;
-        Walk wa = w;  // activation issue trails the weight issue while `early` stages are outstanding
-        Ring sta = st;
-        auto issue = [&](Walk &ww, Ring &rr, bool do_w, bool do_a, int ab0, int s0, int ns) {
-            const uint32_t full = ptx::smem_u32(&s_full[rr.i]);
-            const uint32_t dst = smem_base + rr.i * p.stage_bytes;
-            if (do_w) {
-                ptx::mbar_arrive_expect_tx(full, ns * (ACT_BYTES + SUB_W_BYTES));
-                const uint8_t *w0 = p.g.w + ((int64_t) ww.rt * p.KB + ww.kb0 + ab0 + s0) * SUB_W_BYTES;
-                ptx::bulk_g2s_hint(dst + W_OFF, w0, ns * SUB_W_BYTES, full, pol_w);
-            }
-            if (do_a) {
-                const int8_t *a = p.g.act.q_sw + ((int64_t) ww.tt * p.KB + ww.kb0 + ab0 + s0) * ACT_BYTES;
-                ptx::bulk_g2s_hint(dst, a, ns * ACT_BYTES, full, pol_a);
-            }
-        };
+        int turn = 0;
+        // weights are static: with PDL their stream starts while the predecessor (quantise) kernel is still running;
+        // activations are the predecessor's output
+        if (!is_w && p.pdl) ptx::pdl_wait();
         for (; w.valid(); w.next()) {
             for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
                 const int na = min(SPA, w.nsub - ab0);
                 for (int s0 = 0; s0 < na; s0 += SPS) {
-                    const int ns = min(SPS, na - s0);
-                    if (early > 0) {
-                        if (ptx::elect_one()) issue(w, st, true, false, ab0, s0, ns);  // fresh barrier: no empty wait needed
-                        __syncwarp();
-                        st.advance();
-                        --early;
-                        continue;
-                    }
-                    if (!waited) {
-                        // all early weight loads are in flight: now order against the predecessor and send activations
-                        ptx::pdl_wait();
-                        waited = true;
-                        Walk wb = wa;
-                        Ring rb = sta;
-                        for (int e = 0; e < S && wb.valid();) {
-                            for (int b0 = 0; b0 < wb.nsub && e < S; b0 += SPA) {
-                                const int nb = min(SPA, wb.nsub - b0);
-                                for (int t0 = 0; t0 < nb && e < S; t0 += SPS, ++e) {
-                                    if (ptx::elect_one()) issue(wb, rb, false, true, b0, t0, min(SPS, nb - t0));
-                                    __syncwarp();
-                                    rb.advance();
-                                }
+                    if (!is_w || turn == me) {
+                        const int ns = min(SPS, na - s0);
+                        ptx::mbar_wait(ptx::smem_u32(&s_empty[st.i]), st.ph ^ 1);
+                        if (!is_w) mark(0);
+                        if (ptx::elect_one()) {
+                            const uint32_t full = ptx::smem_u32(&s_full[st.i]);
+                            const uint32_t dst = smem_base + st.i * p.stage_bytes;
+                            const int64_t kb = w.kb0 + ab0 + s0;
+                            if (is_w) {
+                                ptx::mbar_arrive_expect_tx(full, ns * SUB_W_BYTES);
+                                ptx::bulk_g2s_hint(dst + W_OFF, p.g.w + ((int64_t) w.rt * p.KB + kb) * SUB_W_BYTES,
+                                                   ns * SUB_W_BYTES, full, pol);
+                            } else {
+                                ptx::mbar_arrive_expect_tx(full, ns * ACT_BYTES);
+                                ptx::bulk_g2s_hint(dst, p.g.act.q_sw + ((int64_t) w.tt * p.KB + kb) * ACT_BYTES, ns * ACT_BYTES,
+                                                   full, pol);
                             }
-                            wb.next();
                         }
+                        __syncwarp();
                     }
-                    ptx::mbar_wait(ptx::smem_u32(&s_empty[st.i]), st.ph ^ 1);
-                    mark(0);
-                    if (ptx::elect_one()) issue(w, st, true, true, ab0, s0, ns);
-                    __syncwarp();
                     st.advance();
+                    if (++turn == NPW) turn = 0;
                 }
             }
         }
-        if (!waited) {
-            // fewer than S stages in total: activations still have to be sent
-            ptx::pdl_wait();
-            Walk wb = wa;
-            Ring rb = sta;
-            for (; wb.valid(); wb.next())
-                for (int b0 = 0; b0 < wb.nsub; b0 += SPA) {
-                    const int nb = min(SPA, wb.nsub - b0);
-                    for (int t0 = 0; t0 < nb; t0 += SPS) {
-                        if (ptx::elect_one()) issue(wb, rb, false, true, b0, t0, min(SPS, nb - t0));
-                        __syncwarp();
-                        rb.advance();
-                    }
-                }
-        }
-    } else if (warp == 13) {
+    } else if (warp == W_MMA) {
         ev_role = 1;
         // ===================== MMA issuer =====================
         constexpr uint32_t idesc = make_idesc(NT);
@@ -236,7 +216,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         w.init(p, u0, u1);
         Ring st, ar;
         st.init(S);
-        ar.init(2);
+        ar.init(NA);
         uint32_t ndrain = 0;  // drains committed so far; accumulator buffer = ndrain % 2
         if (p.pdl) ptx::pdl_wait();  // tile_fast below is written by the predecessor (quantise) kernel
         int run_tile = -1;
@@ -292,9 +272,73 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 open = true;
             }
         }
-    } else if (warp >= 4 && warp < 12) {
+    } else if (warp >= 4 && warp < 4 + NDEC) {
         // ===================== decode: packed 2-bit codes -> u8 A operand in TMEM, 8 warps per A block ==============
+        // Software-pipelined over the flattened stage sequence: the packed words of the NEXT stage are fetched (stage
+        // wait, LDS, stage release) while the tcgen05.st of the current one drain, so the per-block chain is
+        // A-free wait -> unpack -> st -> wait::st -> A-ready instead of also carrying the stage wait and the LDS latency.
         ev_role = 2;
+        if constexpr (DG == 3) {
+            // ---- grouped decode: group g = (warp - 4) / 4 owns A blocks b = g (mod 3), shared-memory stages s = g (mod 3)
+            // (the ring length is a multiple of 3 and every block is exactly one stage, so a barrier is only ever waited on
+            // by its own group: no phase is skipped) and A stage g.  A warp unpacks its lane quadrant of the whole block.
+            const int q = (warp - 4) & 3;
+            const int g = (warp - 4) >> 2;
+            const int m = q * 32 + lane;
+            const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + g * A_COLS;
+            Walk w;
+            w.init(p, u0, u1);
+            Ring st;
+            st.init(S);
+            int turn = 0;          // block index mod 3
+            uint32_t a_ph = 0;     // phase of this group's A stage
+            for (; w.valid(); w.next()) {
+                for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
+                    if (turn == g) {
+                        const int ns = min(SPA, w.nsub - ab0);
+                        ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
+                        mark(0);
+                        const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
+                        uint4 cw[2 * SPA];
+#pragma unroll
+                        for (int c = 0; c < 2 * SPA; c++)
+                            if (c < 2 * ns) cw[c] = ptx::lds128(w_s + c * TILE_BYTES);
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));
+                        ptx::mbar_wait(ptx::smem_u32(&s_aempty[g]), a_ph ^ 1);
+                        mark(1);
+                        ptx::tc_fence_after();
+                        mark(5);
+#pragma unroll
+                        for (int c = 0; c < 2 * SPA; c++) {
+                            if (c < 2 * ns) {
+                                const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+                                uint32_t r[16];
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    r[4 * j + 0] = wv[j] & 0x03030303u;
+                                    r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                                    r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                                    r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
+                                }
+                                ptx::tmem_st_32x32b_x16(taddr0 + c * 16, r);
+                                if (c == 0 || c == 3) mark(6);
+                            }
+                        }
+                        mark(2);
+                        ptx::tmem_st_wait();
+                        mark(4);
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[g]));
+                        mark(9);
+                        a_ph ^= 1;
+                    }
+                    st.advance();
+                    if (++turn == 3) turn = 0;
+                }
+            }
+        } else {
         const int q = (warp - 4) & 3;   // TMEM lane quadrant (== warp % 4)
         const int h = (warp - 4) >> 2;  // which half of every stage this warp unpacks
         const int m = q * 32 + lane;    // weight row inside the strip == TMEM lane
@@ -305,47 +349,61 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         Ring st, ar;
         st.init(S);
         ar.init(2);
-        for (; w.valid(); w.next()) {
-            for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
-                const int na = min(SPA, w.nsub - ab0);
-                bool a_free = false;
-                const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + ar.i * A_COLS;
-                for (int s0 = 0; s0 < na; s0 += SPS) {
-                    const int ns = min(SPS, na - s0);
-                    ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
-                    mark(0);
-                    const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
-                    uint4 cw[CPH];
+        int ab0 = 0, s0 = 0;            // position of the stage whose words are in cw: unit w, A block ab0, sub-block s0
+        uint4 cw[CPH];
+        int ns = 0;
+        auto fetch = [&]() {            // words of stage (w, ab0, s0) -> cw; the stage goes back to the producers
+            ns = min(SPS, min(SPA, w.nsub - ab0) - s0);
+            ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
+            mark(0);
+            const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
 #pragma unroll
-                    for (int c = 0; c < CPH; c++)
-                        if (h * CPH + c < 2 * ns) cw[c] = ptx::lds128(w_s + (h * CPH + c) * TILE_BYTES);
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));  // this warp's share is consumed
-                    st.advance();
-                    if (!a_free) {
-                        ptx::mbar_wait(ptx::smem_u32(&s_aempty[ar.i]), ar.ph ^ 1);
-                        mark(1);
-                        ptx::tc_fence_after();
-                        a_free = true;
+            for (int c = 0; c < CPH; c++)
+                if (h * CPH + c < 2 * ns) cw[c] = ptx::lds128(w_s + (h * CPH + c) * TILE_BYTES);
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));
+            st.advance();
+        };
+        if (w.valid()) fetch();
+        while (w.valid()) {
+            const int cur_s0 = s0, cur_ns = ns;
+            const int na = min(SPA, w.nsub - ab0);
+            const bool first = (s0 == 0), last = (s0 + SPS >= na);
+            // advance the position to the next stage
+            s0 += SPS;
+            if (last) {
+                s0 = 0;
+                ab0 += SPA;
+                if (ab0 >= w.nsub) { ab0 = 0; w.next(); }
+            }
+            if (first) {
+                ptx::mbar_wait(ptx::smem_u32(&s_aempty[ar.i]), ar.ph ^ 1);
+                mark(1);
+                ptx::tc_fence_after();
+            }
+            const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + ar.i * A_COLS;
+#pragma unroll
+            for (int c = 0; c < CPH; c++) {
+                if (h * CPH + c < 2 * cur_ns) {
+                    const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+                    uint32_t r[16];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        // shifts as multiply-high on the FMA pipe, masks on the ALU pipe: both pipes work
+                        r[4 * j + 0] = wv[j] & 0x03030303u;
+                        r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                        r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                        r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
                     }
-#pragma unroll
-                    for (int c = 0; c < CPH; c++) {
-                        if (h * CPH + c < 2 * ns) {
-                            const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
-                            uint32_t r[16];
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                // shifts as multiply-high on the FMA pipe, masks on the ALU pipe: both pipes work
-                                r[4 * j + 0] = wv[j] & 0x03030303u;
-                                r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
-                                r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
-                                r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
-                            }
-                            ptx::tmem_st_32x32b_x16(taddr0 + s0 * 32 + (h * CPH + c) * 16, r);
-                        }
-                    }
+                    ptx::tmem_st_32x32b_x16(taddr0 + cur_s0 * 32 + (h * CPH + c) * 16, r);
                 }
+            }
+            mark(2);
+            if (w.valid()) fetch();  // next stage's words, while the stores above complete
+            if (last) {
+                mark(3);
                 ptx::tmem_st_wait();
+                mark(4);
                 ptx::tc_fence_before();
                 __syncwarp();
                 if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ar.i]));
@@ -353,6 +411,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 ar.advance();
             }
         }
+        }  // DG == 1
     } else if (warp < 4) {
         // ===================== epilogue =====================
         const int ew = warp;
@@ -492,7 +551,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     // ---- teardown ----
     ptx::tc_fence_before();
     __syncthreads();
-    if (warp == 14) {
+    if (warp == W_ALLOC) {
         ptx::tc_fence_after();
         ptx::tmem_dealloc(tmem_base, 512);
     }
@@ -503,24 +562,30 @@ static int env_int(const char *name, int dflt) {
     return v ? atoi(v) : dflt;
 }
 
-template <int NT, int SPS, int OUT>
+template <int NT, int SPS, int OUT, int DG>
 static cudaError_t launch_out(Params &p, int grid, cudaStream_t s) {
     const int budget = env_int("VLUT_TC_SMEM_KB", 200) * 1024;
     p.stage_bytes = SPS * (NT * 128 + SUB_W_BYTES);  // multiple of 1024
     int ns = (budget - 1024) / p.stage_bytes;
     if (ns > MAX_STAGES) ns = MAX_STAGES;
     int forced = env_int("VLUT_TC_STAGES", 0);
-    if (forced > 0 && forced < SPA / SPS) forced = SPA / SPS;
+    // the decode warps fetch the first stage of the next A block before they hand over the current one: the ring must
+    // hold one stage more than an A block, or that fetch would wait for an MMA that waits for the hand-over
+    constexpr int MIN_STAGES = SPA / SPS + 1;
+    if (forced > 0 && forced < MIN_STAGES) forced = MIN_STAGES;
+    constexpr int QUANT = (DG == 3) ? 3 : npw_for(DG);  // stage -> decode group / weight producer mapping must be static
+    if (forced > 0) forced = (forced + QUANT - 1) / QUANT * QUANT;
     if (forced > 0 && forced < ns) ns = forced;
-    if (ns < SPA / SPS) return cudaErrorInvalidValue;  // every stage of one A block is live at once
+    ns -= ns % QUANT;
+    if (ns < MIN_STAGES || ns < QUANT) return cudaErrorInvalidValue;
     p.nstages = ns;
     const size_t smem = (size_t) ns * p.stage_bytes + 1024;
-    auto kern = kernel<NT, SPS, OUT>;
+    auto kern = kernel<NT, SPS, OUT, DG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) grid);
-    cfg.blockDim = dim3(THREADS);
+    cfg.blockDim = dim3(threads_for(DG));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -531,10 +596,10 @@ static cudaError_t launch_out(Params &p, int grid, cudaStream_t s) {
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int NT, int SPS>
+template <int NT, int SPS, int DG>
 static cudaError_t launch_one(Params &p, int grid, cudaStream_t s) {
-    if (p.g.n_out == 0) return launch_out<NT, SPS, 0>(p, grid, s);
-    return p.g.multicast ? launch_out<NT, SPS, 2>(p, grid, s) : launch_out<NT, SPS, 1>(p, grid, s);
+    if (p.g.n_out == 0) return launch_out<NT, SPS, 0, DG>(p, grid, s);
+    return p.g.multicast ? launch_out<NT, SPS, 2, DG>(p, grid, s) : launch_out<NT, SPS, 1, DG>(p, grid, s);
 }
 
 }  // namespace tc4
@@ -544,6 +609,7 @@ bool gemm_tc4_supported(int type, int64_t K, int64_t N, int64_t T) {
 }
 
 cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches) {
+    if (g.act.sw_tile != g.act.NT) return cudaErrorInvalidValue;  // wants full-height swizzled activation tiles
     tc4::Params p{};
     p.g = g;
     p.KB = (int) (g.act.Kpad / 128);
@@ -555,6 +621,7 @@ cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.U = p.RT * p.TT * p.G;
     p.allow_fast = tc4::env_int("VLUT_TC_FAST", 1);
     p.pdl = tc4::env_int("VLUT_PDL", 1);
+    p.dbg_skip = tc4::env_int("VLUT_TC_DEBUG_SKIP", 0);
     p.dbg = tc4::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, tc4::env_int("VLUT_TC_DEBUG_SKIP", 0)) : nullptr;
     int grid = g.sm_count;
     const int tiles = p.RT * p.TT;
@@ -563,11 +630,12 @@ cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches) {
     if (grid > p.U) grid = p.U;
     if (grid < 1) grid = 1;
     if (launches) *launches += 1;
+    const bool dg3 = tc4::env_int("VLUT_TC_DGROUPS", 1) == 3;  // grouped decode (experimental: measured within 4 % of the default)
     switch (NT) {
-        case 16: return tc4::launch_one<16, 4>(p, grid, s);
-        case 32: return tc4::launch_one<32, 4>(p, grid, s);
-        case 64: return tc4::launch_one<64, 2>(p, grid, s);
-        case 128: return tc4::launch_one<128, 2>(p, grid, s);
+        case 16: return dg3 ? tc4::launch_one<16, 4, 3>(p, grid, s) : tc4::launch_one<16, 4, 1>(p, grid, s);
+        case 32: return dg3 ? tc4::launch_one<32, 4, 3>(p, grid, s) : tc4::launch_one<32, 4, 1>(p, grid, s);
+        case 64: return tc4::launch_one<64, 2, 1>(p, grid, s);
+        case 128: return tc4::launch_one<128, 2, 1>(p, grid, s);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -10,7 +10,8 @@
 // 24 KB, eight stages = four A blocks of look-ahead.
 //
 // Roles per CTA (same warp layout as gemm_tc4.cu):
-//   warps 0-3 epilogue, 4-11 decode, 12 TMA producer, 13 MMA issuer (even CTA only), 14 TMEM allocator.
+//   warps 0-3 epilogue, 4-11 decode, 12 activation producer, 13 MMA issuer (even CTA only), 14 TMEM allocator, then
+//   weight producer.
 // Cross-CTA protocol: every CTA has its own stage ring (full/empty), A ring (aempty) and accumulator barriers (accfull);
 // the even CTA ("leader") owns afull[] (16 arrivals: 8 decode warps of each CTA -- a decode warp has waited for its CTA's
 // stage, so A-ready implies that CTA's half of the activations has landed) and accempty[] (8 arrivals: 4 epilogue warps of
@@ -40,6 +41,7 @@ struct Params {
     int allow_fast, pdl;
     int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores, 16 no drain
     long long *dbg;
+    int dbg_skip;
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
@@ -112,7 +114,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < S; s++) {
-            ptx::mbar_init(ptx::smem_u32(&s_full[s]), 1);
+            ptx::mbar_init(ptx::smem_u32(&s_full[s]), 2);       // the two producer warps (arrive.expect_tx each)
             ptx::mbar_init(ptx::smem_u32(&s_empty[s]), 8 + 1);  // 8 local decode warps + the leader's multicast commit
         }
         for (int d = 0; d < 2; d++) {
@@ -143,7 +145,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     int n_ev = 0, ev_role = 0;
     auto mark = [&](int kind) {
         if (dbg_on) {
-            const int k = n_ev - (int) p.dbg[0];
+            const int k = n_ev - p.dbg_skip;  // (no global load here: it would stall every marked point)
             if (k >= 0 && k < 24) {
                 p.dbg[8192 + (ev_role * 24 + k) * 2] = clock64() - t_start;
                 p.dbg[8192 + (ev_role * 24 + k) * 2 + 1] = kind;
@@ -152,76 +154,47 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         }
     };
 
-    if (warp == 12) {
+    if (warp == 12 || warp == 14) {
         ev_role = 0;
-        // ===================== TMA producer: this CTA's weight rows and its half of the activation tile ==============
-        const uint64_t pol_w = ptx::policy_evict_first();
-        const uint64_t pol_a = ptx::policy_evict_last();
+        // ===================== two TMA producers: warp 14 streams this CTA's weight rows, warp 12 its half of the
+        // activation tile.  One cp.async.bulk costs its issuing thread ~280 clk whatever its size
+        // (profiles/r1_microbench_b200.txt): few, large copies, issued from two warps. ==============
+        const bool is_w = (warp == 14);
+        const uint64_t pol = is_w ? ptx::policy_evict_first() : ptx::policy_evict_last();
         Walk w;
         w.init(p, u0, u1);
         Ring st;
         st.init(S);
-        int early = p.pdl ? S : 0;  // stages whose WEIGHTS are requested before griddepcontrol.wait (static data)
-        bool waited = !p.pdl;
-        const Walk wa = w;
-        const Ring sta = st;
-        auto issue = [&](const Walk &ww, const Ring &rr, bool do_w, bool do_a, int ab0, int s0, int ns) {
-            const uint32_t full = ptx::smem_u32(&s_full[rr.i]);
-            const uint32_t dst = smem_base + rr.i * p.stage_bytes;
-            if (do_w) {
-                ptx::mbar_arrive_expect_tx(full, ns * (ACT_BYTES + SUB_W_BYTES));
-                const int rt = min(2 * ww.rp + (int) rank, p.RT - 1);  // odd strip count: the last peer re-reads a valid strip
-                const uint8_t *w0 = p.g.w + ((int64_t) rt * p.KB + ww.kb0 + ab0 + s0) * SUB_W_BYTES;
-                ptx::bulk_g2s_hint(dst + W_OFF, w0, ns * SUB_W_BYTES, full, pol_w);
-            }
-            if (do_a) {
-                const int8_t *a = p.g.act.q_sw + (((int64_t) ww.tt * p.KB + ww.kb0 + ab0 + s0) * NT + rank * NH) * 128;
-                for (int sb = 0; sb < ns; sb++)
-                    ptx::bulk_g2s_hint(dst + sb * ACT_BYTES, a + (int64_t) sb * NT * 128, ACT_BYTES, full, pol_a);
-            }
-        };
-        // activations of the first `n` stages (the ones whose weights went out early)
-        auto late_acts = [&](int n) {
-            Walk wb = wa;
-            Ring rb = sta;
-            for (int e = 0; e < n && wb.valid(); wb.next())
-                for (int b0 = 0; b0 < wb.nsub && e < n; b0 += SPA) {
-                    const int nb = min(SPA, wb.nsub - b0);
-                    for (int t0 = 0; t0 < nb && e < n; t0 += SPS, ++e) {
-                        if (ptx::elect_one()) issue(wb, rb, false, true, b0, t0, min(SPS, nb - t0));
-                        __syncwarp();
-                        rb.advance();
-                    }
-                }
-        };
+        // weights are static: with PDL their stream starts while the predecessor (quantise) kernel is still running;
+        // activations are the predecessor's output
+        if (!is_w && p.pdl) ptx::pdl_wait();
         for (; w.valid(); w.next()) {
+            const int rt = min(2 * w.rp + (int) rank, p.RT - 1);  // odd strip count: the last peer re-reads a valid strip
             for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
                 const int na = min(SPA, w.nsub - ab0);
                 for (int s0 = 0; s0 < na; s0 += SPS) {
                     const int ns = min(SPS, na - s0);
-                    if (early > 0) {
-                        if (ptx::elect_one()) issue(w, st, true, false, ab0, s0, ns);  // fresh barrier: no empty wait
-                        __syncwarp();
-                        st.advance();
-                        --early;
-                        continue;
-                    }
-                    if (!waited) {
-                        ptx::pdl_wait();
-                        waited = true;
-                        late_acts(S);
-                    }
                     ptx::mbar_wait(ptx::smem_u32(&s_empty[st.i]), st.ph ^ 1);
-                    mark(0);
-                    if (ptx::elect_one()) issue(w, st, true, true, ab0, s0, ns);
+                    if (!is_w) mark(0);
+                    if (ptx::elect_one()) {
+                        const uint32_t full = ptx::smem_u32(&s_full[st.i]);
+                        const uint32_t dst = smem_base + st.i * p.stage_bytes;
+                        const int64_t kb = w.kb0 + ab0 + s0;
+                        if (is_w) {
+                            ptx::mbar_arrive_expect_tx(full, ns * SUB_W_BYTES);
+                            ptx::bulk_g2s_hint(dst + W_OFF, p.g.w + ((int64_t) rt * p.KB + kb) * SUB_W_BYTES, ns * SUB_W_BYTES,
+                                               full, pol);
+                        } else {
+                            // q_sw holds swizzled tiles of NH tokens: this CTA's half is contiguous over kb
+                            ptx::mbar_arrive_expect_tx(full, ns * ACT_BYTES);
+                            ptx::bulk_g2s_hint(dst, p.g.act.q_sw + (((int64_t) (2 * w.tt + rank) * p.KB) + kb) * ACT_BYTES,
+                                               ns * ACT_BYTES, full, pol);
+                        }
+                    }
                     __syncwarp();
                     st.advance();
                 }
             }
-        }
-        if (!waited) {
-            ptx::pdl_wait();  // fewer than S stages in total
-            late_acts(S);
         }
     } else if (warp == 13) {
         ev_role = 1;
@@ -291,7 +264,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             }
         }
     } else if (warp >= 4 && warp < 12) {
-        // ===================== decode: packed 2-bit codes -> u8 A operand in this CTA's TMEM, 8 warps per A block ====
+        // ===================== decode: packed 2-bit codes -> u8 A operand in TMEM, 8 warps per A block ==============
+        // Software-pipelined over the flattened stage sequence: the packed words of the NEXT stage are fetched (stage
+        // wait, LDS, stage release) while the tcgen05.st of the current one drain, so the per-block chain is
+        // A-free wait -> unpack -> st -> wait::st -> A-ready instead of also carrying the stage wait and the LDS latency.
         ev_role = 2;
         const int q = (warp - 4) & 3;   // TMEM lane quadrant (== warp % 4)
         const int h = (warp - 4) >> 2;  // which half of every stage this warp unpacks
@@ -305,46 +281,57 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         Ring st, ar;
         st.init(S);
         ar.init(2);
-        for (; w.valid(); w.next()) {
-            for (int ab0 = 0; ab0 < w.nsub; ab0 += SPA) {
-                const int na = min(SPA, w.nsub - ab0);
-                bool a_free = false;
-                const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + ar.i * A_COLS;
-                for (int s0 = 0; s0 < na; s0 += SPS) {
-                    const int ns = min(SPS, na - s0);
-                    ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
-                    mark(0);
-                    const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
-                    uint4 cw[CPH];
+        int ab0 = 0, s0 = 0;            // position of the stage whose words are in cw: unit w, A block ab0, sub-block s0
+        uint4 cw[CPH];
+        int ns = 0;
+        auto fetch = [&]() {            // words of stage (w, ab0, s0) -> cw; the stage goes back to the producers
+            ns = min(SPS, min(SPA, w.nsub - ab0) - s0);
+            ptx::mbar_wait(ptx::smem_u32(&s_full[st.i]), st.ph);
+            mark(0);
+            const uint32_t w_s = smem_base + st.i * p.stage_bytes + W_OFF + m * 16;
 #pragma unroll
-                    for (int c = 0; c < CPH; c++)
-                        if (h * CPH + c < 2 * ns) cw[c] = ptx::lds128(w_s + (h * CPH + c) * TILE_BYTES);
-                    __syncwarp();
-                    if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));  // this warp's share is consumed
-                    st.advance();
-                    if (!a_free) {
-                        ptx::mbar_wait(ptx::smem_u32(&s_aempty[ar.i]), ar.ph ^ 1);
-                        mark(1);
-                        ptx::tc_fence_after();
-                        a_free = true;
+            for (int c = 0; c < CPH; c++)
+                if (h * CPH + c < 2 * ns) cw[c] = ptx::lds128(w_s + (h * CPH + c) * TILE_BYTES);
+            __syncwarp();
+            if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_empty[st.i]));
+            st.advance();
+        };
+        if (w.valid()) fetch();
+        while (w.valid()) {
+            const int cur_s0 = s0, cur_ns = ns;
+            const int na = min(SPA, w.nsub - ab0);
+            const bool first = (s0 == 0), last = (s0 + SPS >= na);
+            // advance the position to the next stage
+            s0 += SPS;
+            if (last) {
+                s0 = 0;
+                ab0 += SPA;
+                if (ab0 >= w.nsub) { ab0 = 0; w.next(); }
+            }
+            if (first) {
+                ptx::mbar_wait(ptx::smem_u32(&s_aempty[ar.i]), ar.ph ^ 1);
+                mark(1);
+                ptx::tc_fence_after();
+            }
+            const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + ar.i * A_COLS;
+#pragma unroll
+            for (int c = 0; c < CPH; c++) {
+                if (h * CPH + c < 2 * cur_ns) {
+                    const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+                    uint32_t r[16];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        // shifts as multiply-high on the FMA pipe, masks on the ALU pipe: both pipes work
+                        r[4 * j + 0] = wv[j] & 0x03030303u;
+                        r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                        r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                        r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
                     }
-#pragma unroll
-                    for (int c = 0; c < CPH; c++) {
-                        if (h * CPH + c < 2 * ns) {
-                            const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
-                            uint32_t r[16];
-#pragma unroll
-                            for (int j = 0; j < 4; j++) {
-                                // shifts as multiply-high on the FMA pipe, masks on the ALU pipe: both pipes work
-                                r[4 * j + 0] = wv[j] & 0x03030303u;
-                                r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
-                                r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
-                                r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
-                            }
-                            if (!(p.abl & 1)) ptx::tmem_st_32x32b_x16(taddr0 + s0 * 32 + (h * CPH + c) * 16, r);
-                        }
-                    }
+                    if (!(p.abl & 1)) ptx::tmem_st_32x32b_x16(taddr0 + cur_s0 * 32 + (h * CPH + c) * 16, r);
                 }
+            }
+            if (w.valid()) fetch();  // next stage's words, while the stores above complete
+            if (last) {
                 if (!(p.abl & 4)) ptx::tmem_st_wait();
                 ptx::tc_fence_before();
                 __syncwarp();
@@ -513,9 +500,12 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     int ns = (budget - 1024) / p.stage_bytes;
     if (ns > MAX_STAGES) ns = MAX_STAGES;
     int forced = env_int("VLUT_TC_STAGES", 0);
-    if (forced > 0 && forced < SPA / SPS) forced = SPA / SPS;
+    // the decode warps fetch the first stage of the next A block before they hand over the current one: the ring must
+    // hold one stage more than an A block, or that fetch would wait for an MMA that waits for the hand-over
+    constexpr int MIN_STAGES = SPA / SPS + 1;
+    if (forced > 0 && forced < MIN_STAGES) forced = MIN_STAGES;
     if (forced > 0 && forced < ns) ns = forced;
-    if (ns < SPA / SPS) return cudaErrorInvalidValue;  // every stage of one A block is live at once
+    if (ns < MIN_STAGES) return cudaErrorInvalidValue;
     p.nstages = ns;
     const size_t smem = (size_t) ns * p.stage_bytes + 1024;
     auto kern = kernel<NT, SPS, OUT>;
@@ -565,6 +555,7 @@ bool gemm_tc5_supported(int type, int64_t K, int64_t N, int64_t T) {
 }
 
 cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
+    if (g.act.sw_tile * 2 != g.act.NT) return cudaErrorInvalidValue;  // wants half-height swizzled activation tiles
     tc5::Params p{};
     p.g = g;
     p.KB = (int) (g.act.Kpad / 128);
@@ -578,11 +569,12 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.allow_fast = tc5::env_int("VLUT_TC_FAST", 1);
     p.pdl = tc5::env_int("VLUT_PDL", 1);
     p.abl = tc5::env_int("VLUT_TC_ABL", 0);
+    p.dbg_skip = tc5::env_int("VLUT_TC_DEBUG_SKIP", 0);
     p.dbg = tc5::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, tc5::env_int("VLUT_TC_DEBUG_SKIP", 0)) : nullptr;
     if (launches) *launches += 1;
     switch (NT) {
         case 64: return tc5::launch_one<64, 2>(p, g.sm_count, s);
-        case 128: return tc5::launch_one<128, 2>(p, g.sm_count, s);
+        case 128: return tc5::launch_one<128, 4>(p, g.sm_count, s);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -85,7 +85,8 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         const int64_t kb = k / BLOCK_K;
         const int kk = (int) (k % BLOCK_K);
         const int c = kk / 16;
-        const int64_t off = (((int64_t) (t / a.NT) * (Kpad / BLOCK_K) + kb) * a.NT + (t % a.NT)) * 128 + ((c ^ (t & 7)) << 4) + (kk & 15);
+        const int64_t off = (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 +
+                            ((c ^ (t & 7)) << 4) + (kk & 15);
         *reinterpret_cast<uint32_t *>(a.q_sw + off) = pk;
         // the 32 lanes of a warp cover 128 consecutive, 128-aligned k here: one K-group (512 and 640 are multiples of
         // 128), so reduce with shuffles and touch shared memory once per warp (Kpad % 128 == 0: the loop is warp-uniform)
@@ -115,6 +116,27 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         // a token tile takes the single-drain path unless one of its tokens stamps it with this call's epoch
         if (!safe) a.tile_unsafe[t / a.NT] = a.epoch;
     }
+}
+
+// Rewrite q_sw from q_rm with swizzled tiles of `a.sw_tile` tokens (used when a GEMM kernel that wants the other tile height
+// is forced on a workspace quantised for the default one).  One thread per 16-byte chunk.
+__global__ void relayout_kernel(ActView a) {
+    const int64_t chunks_per_row = a.Kpad / 16;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t) a.Tpad * chunks_per_row) return;
+    const int64_t t = i / chunks_per_row;
+    const int64_t k = (i % chunks_per_row) * 16;
+    const uint4 v = *reinterpret_cast<const uint4 *>(a.q_rm + t * a.Kpad + k);
+    const int64_t kb = k / BLOCK_K;
+    const int c = (int) (k % BLOCK_K) / 16;
+    const int64_t off = (((t / a.sw_tile) * (a.Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 + ((c ^ (int) (t & 7)) << 4);
+    *reinterpret_cast<uint4 *>(a.q_sw + off) = v;
+}
+
+cudaError_t launch_relayout(const ActView &a, cudaStream_t s) {
+    const int64_t n = (int64_t) a.Tpad * (a.Kpad / 16);
+    relayout_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
 }
 
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s) {

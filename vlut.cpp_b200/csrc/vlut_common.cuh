@@ -82,6 +82,7 @@ struct ActView {
     uint32_t epoch;
     int64_t Kpad, Tpad;
     int G, gsize, NT;
+    int sw_tile;  // tokens per swizzled tile of q_sw: NT, or NT / 2 for the CTA-pair kernel (each CTA stages one half tile)
 };
 
 struct GemmArgs {
@@ -122,6 +123,7 @@ inline __device__ int32_t wrap16(int32_t v) { return (int32_t) (int16_t) (uint16
 cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, uint8_t *t2, cudaStream_t s);
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s);
+cudaError_t launch_relayout(const ActView &a, cudaStream_t s);  // rewrite q_sw from q_rm for a.sw_tile
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
 cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);   // single pipeline (TS or SS)
 bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
