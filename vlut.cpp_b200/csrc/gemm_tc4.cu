@@ -41,6 +41,7 @@ struct Params {
     int KB, G, gsub, RT, TT, U;
     int nstages, stage_bytes;
     int allow_fast, pdl;
+    int whole;  // 1: every CTA gets whole output tiles (no fix-up); 0: stream-K over (tile, K-group) units
     long long *dbg;  // optional timeline buffer (VLUT_TC_DEBUG), else null
     int dbg_skip;    // events to skip per role before recording
 };
@@ -143,8 +144,10 @@ __global__ void __launch_bounds__(threads_for(DG), 1) kernel(const __grid_consta
     const uint32_t tmem_base = s_tmem_base;
     float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
 
-    const int u0 = (int) (((int64_t) blockIdx.x * p.U) / gridDim.x);
-    const int u1 = (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
+    const int ntiles = p.RT * p.TT;
+    const int u0 = p.whole ? (int) (((int64_t) blockIdx.x * ntiles) / gridDim.x) * p.G : (int) (((int64_t) blockIdx.x * p.U) / gridDim.x);
+    const int u1 = p.whole ? (int) (((int64_t) (blockIdx.x + 1) * ntiles) / gridDim.x) * p.G
+                           : (int) (((int64_t) (blockIdx.x + 1) * p.U) / gridDim.x);
     auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
     const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0 && (warp <= 4 || warp >= 4 + NDEC);
@@ -623,10 +626,17 @@ cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.pdl = tc4::env_int("VLUT_PDL", 1);
     p.dbg_skip = tc4::env_int("VLUT_TC_DEBUG_SKIP", 0);
     p.dbg = tc4::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, tc4::env_int("VLUT_TC_DEBUG_SKIP", 0)) : nullptr;
+    // whole tiles per CTA unless stream-K's perfect balance beats the cost of fixing up split tiles (see gemm_tc5.cu)
     int grid = g.sm_count;
     const int tiles = p.RT * p.TT;
-    if (tiles <= g.sm_count && tiles * 10 >= g.sm_count * 7) grid = tiles;  // whole tiles per CTA: no fix-up
-    grid = tc4::env_int("VLUT_TC_GRID", grid);
+    constexpr int FIXUP_UNITS = 10;
+    const int rounds = (tiles + grid - 1) / grid;
+    p.whole = (rounds * p.G <= (p.U + grid - 1) / grid + FIXUP_UNITS) ? 1 : 0;
+    const int forced_grid = tc4::env_int("VLUT_TC_GRID", 0);  // tests: force a grid (and with it the stream-K split paths)
+    if (forced_grid > 0) p.whole = 0;
+    p.whole = tc4::env_int("VLUT_TC_WHOLE", p.whole);
+    if (forced_grid > 0) grid = forced_grid;
+    else if (p.whole) grid = (tiles + rounds - 1) / rounds;
     if (grid > p.U) grid = p.U;
     if (grid < 1) grid = 1;
     if (launches) *launches += 1;

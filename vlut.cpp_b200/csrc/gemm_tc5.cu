@@ -39,6 +39,7 @@ struct Params {
     int KB, G, gsub, RT, RP, TT, U;
     int nstages, stage_bytes;
     int allow_fast, pdl;
+    int whole;  // 1: every pair gets whole output tiles (no split tiles, no fix-up); 0: stream-K over (tile, K-group) units
     int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores, 16 no drain
     long long *dbg;
     int dbg_skip;
@@ -136,8 +137,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     const uint32_t tmem_base = s_tmem_base;
     float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
 
-    const int u0 = (int) (((int64_t) pair * p.U) / npairs);
-    const int u1 = (int) (((int64_t) (pair + 1) * p.U) / npairs);
+    const int ntiles = p.RP * p.TT;
+    const int u0 = p.whole ? (int) (((int64_t) pair * ntiles) / npairs) * p.G : (int) (((int64_t) pair * p.U) / npairs);
+    const int u1 = p.whole ? (int) (((int64_t) (pair + 1) * ntiles) / npairs) * p.G : (int) (((int64_t) (pair + 1) * p.U) / npairs);
     auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
     const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
@@ -533,9 +535,19 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
         cached = n;
     }
     if (npairs > cached) npairs = cached;
+    // Work split.  Stream-K (equal units per pair, tiles split across pairs and fixed up through the workspace) balances
+    // perfectly but every split tile costs about ten A blocks of time at the tail (slot write, fence, counter, the last
+    // arriver's reduction: measured T=512: 39.6 us split vs 33.9 us with whole tiles on only 56 of the 74 pairs).  So whole
+    // tiles unless the rounding loss is larger than that: rounds * G  vs  U / npairs + FIXUP_UNITS.
     const int ptiles = p.RP * p.TT;
-    if (ptiles <= npairs && ptiles * 10 >= npairs * 7) npairs = ptiles;  // whole tiles per pair: no fix-up
-    npairs = env_int("VLUT_TC_GRID", 2 * npairs) / 2;
+    constexpr int FIXUP_UNITS = 10;
+    const int rounds = (ptiles + npairs - 1) / npairs;
+    p.whole = (rounds * p.G <= (p.U + npairs - 1) / npairs + FIXUP_UNITS) ? 1 : 0;
+    const int forced_grid = env_int("VLUT_TC_GRID", 0);  // tests: force a grid (and with it the stream-K split paths)
+    if (forced_grid > 0) p.whole = 0;
+    p.whole = env_int("VLUT_TC_WHOLE", p.whole);
+    if (forced_grid > 0) npairs = forced_grid / 2;
+    else if (p.whole) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;
     if (npairs < 1) npairs = 1;
     cfg.gridDim = dim3((unsigned) (2 * npairs));
