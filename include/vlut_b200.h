@@ -46,6 +46,7 @@ extern "C" {
 #define VLUT_ALGO_TC1     5   /* first generation: 4 decode warps; A operand in TMEM or (VLUT_TC_TS=0) shared memory    */
 #define VLUT_ALGO_TC2     6   /* 256 weight rows per CTA, two pipelines sharing every activation stage                  */
 #define VLUT_ALGO_TCP     7   /* CTA pairs (cluster of 2, cta_group::2, M = 256): each CTA stages half the token tile, T > 32 */
+#define VLUT_ALGO_TCS     8   /* T <= 64: per-thread cp.async weight stream, K split over a thread-block cluster (DSMEM reduce)    */
 #define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate, T <= 16 (measured candidate)     */
 
 typedef struct vlut_ctx vlut_ctx;

@@ -33,7 +33,8 @@ def api():
 def algos_for(T):
     a = api()
     return ([a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_LUT] if T <= 16 else []) +
-            ([a.ALGO_TCP] if T > 32 else []))  # CTA-pair kernel: token tiles of 64 / 128
+            ([a.ALGO_TCP] if T > 32 else []) +  # CTA-pair kernel: token tiles of 64 / 128
+            ([a.ALGO_TCS] if T <= 64 else []))  # small-T streaming kernel
 
 
 def run(ctx, type_, packed, x, N, algo, w_scale=1.0):
@@ -69,7 +70,7 @@ def test_repack_round_trip(ctx, orc, type_, K, N):
 
 
 @pytest.mark.parametrize("kind", ["normal", "uniform", "outlier", "negative", "zeros", "ones"])
-@pytest.mark.parametrize("T,K", [(1, 512), (7, 4096), (33, 3200), (70, 1300)])
+@pytest.mark.parametrize("T,K", [(1, 512), (7, 4096), (33, 3200), (70, 1300), (5, 8640), (18, 14336), (3, 16400)])
 def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
     x = O.make_acts(T, K, seed=T + K, kind=kind)
     q_ref, s_ref = orc.quantize(x)
@@ -77,6 +78,27 @@ def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
     q, s = ctx.get_act(K, T)
     assert np.array_equal(q, q_ref)
     assert np.array_equal(bits(s), bits(s_ref))
+
+
+@pytest.mark.parametrize("two_pass", [0, 1], ids=["register-kernel", "two-pass-kernel"])
+def test_quantize_ties_and_saturation(ctx, orc, monkeypatch, two_pass):
+    """round() is half AWAY from zero and the clamp is asymmetric: exact .5 products (row max 127 -> scale 1), values far
+    outside the int8 range, and a row whose signed max is negative (everything saturates to -128)."""
+    monkeypatch.setenv("VLUT_QUANT_2PASS", str(two_pass))
+    K = 1024
+    x = np.zeros((3, K), dtype=np.float32)
+    ties = np.array([0.5, -0.5, 1.5, -1.5, 2.5, -2.5, 126.5, -126.5, -127.5, -128.5, -129.0, -1000.0, 127.0, 0.49999997,
+                     -0.49999997, 63.5], dtype=np.float32)
+    x[0, :ties.size] = ties
+    x[0, 500] = 127.0
+    x[1] = np.linspace(-300, 127, K, dtype=np.float32)
+    x[2] = -np.abs(O.make_acts(1, K, seed=5)[0]) - 0.25
+    q_ref, s_ref = orc.quantize(x)
+    ctx.quantize_act(O.I2_V_4, torch.from_numpy(x).cuda())
+    q, s = ctx.get_act(K, 3)
+    assert np.array_equal(q, q_ref)
+    assert np.array_equal(bits(s), bits(s_ref))
+    assert list(q[0, :6]) == [1, -1, 2, -2, 3, -3]
 
 
 def test_quantize_strided_rows(ctx, orc):
@@ -89,6 +111,11 @@ def test_quantize_strided_rows(ctx, orc):
     q, s = ctx.get_act(K, T)
     q_ref, s_ref = orc.quantize(buf[:, :K])
     assert np.array_equal(q, q_ref) and np.array_equal(bits(s), bits(s_ref))
+    # rows that are not 16-byte aligned take the two-pass kernel
+    xd2 = torch.from_numpy(np.ascontiguousarray(np.pad(buf, ((0, 0), (1, 0)))) ).cuda()[:, 1:K + 1]
+    ctx.quantize_act(O.I2_V_4, xd2)
+    q2, s2 = ctx.get_act(K, T)
+    assert np.array_equal(q2, q_ref) and np.array_equal(bits(s2), bits(s_ref))
 
 
 @pytest.mark.parametrize("path", FIXTURES, ids=lambda p: Path(p).stem)
@@ -150,7 +177,7 @@ def test_full_size_known_answers(ctx):
             pytest.skip("numpy RNG stream differs from the one the fixtures were made with")
         packed = O.Oracle().pack(k["type"], w)
         assert hashlib.sha256(packed.tobytes()).hexdigest() == k["sha256_packed"]
-        for algo in [api().ALGO_TC]:
+        for algo in [api().ALGO_TC, api().ALGO_AUTO] + ([api().ALGO_TCS] if k["T"] <= 64 else []):
             out = run(ctx, k["type"], packed, x, k["N"], algo)
             assert hashlib.sha256(out.tobytes()).hexdigest() == k["sha256_out"], f"{name} algo={algo}"
 
@@ -245,6 +272,29 @@ def test_streamk_split_tiles_and_ring_wrap(ctx, orc, monkeypatch, grid, stages, 
             for rep in range(2):  # second run sees the workspace the first one left behind
                 out = run(ctx, type_, packed, x, N, algo)
                 assert np.array_equal(bits(out), bits(ref)), f"algo={algo} rep={rep}"
+
+
+@pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
+@pytest.mark.parametrize("split", [1, 2, 3, 5, 8])
+@pytest.mark.parametrize("T", [1, 9, 16, 31, 64])
+def test_tcs_cluster_split_k(ctx, orc, monkeypatch, split, T, fast):
+    """VLUT_ALGO_TCS with the K-groups of every strip forced onto `split` CTAs of a thread-block cluster (capped at the
+    number of K-groups): distributed-shared-memory reduction, uneven group and token slices, activation-ring wrap-around
+    (VLUT_TCS_NAS=2), both drain policies, I2 (512-k groups) and I1 (640-k groups, odd sub-block count, 4-weight tail)."""
+    a = api()
+    monkeypatch.setenv("VLUT_TCS_SPLIT", str(split))
+    monkeypatch.setenv("VLUT_TCS_NAS", "2" if split % 2 else "0")
+    monkeypatch.setenv("VLUT_TC_FAST", str(fast))
+    for type_, K, N in [(O.I2_V_4, 4096, 640), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 129), (O.I1_V, 3072, 72),
+                        (O.I2_V_4, 14336, 256)]:
+        w = O.make_ternary(N, K, seed=split)
+        x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "normal")  # uniform: sum|q| often > 32767
+        packed = orc.pack(type_, w)
+        ref = orc.mul_mat(type_, packed, x, N)
+        for rep in range(2):
+            out = run(ctx, type_, packed, x, N, a.ALGO_TCS)
+            bad = bits(out) != bits(ref)
+            assert not bad.any(), f"type={type_} K={K} rep={rep}: {bad.sum()} of {bad.size} differ, first at {np.argwhere(bad)[0]}"
 
 
 def test_fused_scatter_epilogue_single_gpu_emulation(ctx, orc):

@@ -23,8 +23,8 @@ I2_V, I2_V_4, I2_V_8, I1_V, I1_V_2 = 40, 42, 43, 45, 46
 TYPE_NAMES = {I2_V: "I2_V", I2_V_4: "I2_V_4", I2_V_8: "I2_V_8", I1_V: "I1_V", I1_V_2: "I1_V_2"}
 TYPE_BY_NAME = {v: k for k, v in TYPE_NAMES.items()}
 
-ALGO_AUTO, ALGO_SIMPLE, ALGO_TC, ALGO_LUT, ALGO_TC1, ALGO_TC2, ALGO_TCP = 0, 1, 3, 4, 5, 6, 7
-ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_TC: "tc", ALGO_LUT: "lut", ALGO_TC1: "tc1", ALGO_TC2: "tc2", ALGO_TCP: "tcp"}
+ALGO_AUTO, ALGO_SIMPLE, ALGO_TC, ALGO_LUT, ALGO_TC1, ALGO_TC2, ALGO_TCP, ALGO_TCS = 0, 1, 3, 4, 5, 6, 7, 8
+ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_TC: "tc", ALGO_LUT: "lut", ALGO_TC1: "tc1", ALGO_TC2: "tc2", ALGO_TCP: "tcp", ALGO_TCS: "tcs"}
 
 
 def nbytes(type_: int, K: int, N: int) -> int:

@@ -387,7 +387,8 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
 
     int launches = 0;
     cudaError_t e;
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP) {
+    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP ||
+        algo == VLUT_ALGO_TCS) {
         // the workspace was quantised for another kernel's swizzled-tile height: rewrite q_sw from q_rm
         const int want = (algo == VLUT_ALGO_TCP && c->act.NT >= 64) ? c->act.NT / 2 : c->act.NT;
         if (c->act.sw_tile != want) {
@@ -406,6 +407,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
         case VLUT_ALGO_TC:
             if (!gemm_tc4_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tc4(g, c->stream, &launches);
+            break;
+        case VLUT_ALGO_TCS:
+            if (!gemm_tcs_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            e = launch_gemm_tcs(g, c->stream, &launches);
             break;
         case VLUT_ALGO_TC2:
             if (!gemm_tc3_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;

@@ -11,6 +11,8 @@
 // 128-bit loads of x, 32-bit stores of q in two layouts (row-major, and pre-swizzled K-major UMMA operand tiles
 // that a TMA bulk copy drops into shared memory ready for tcgen05.mma), plus per (token, K-group): the sum of q
 // that undoes the +1 offset of the u8 weight codes, and whether sum|q| rules out any int16 wrap.
+#include <stdlib.h>
+
 #include "vlut_common.cuh"
 
 namespace vlut {
@@ -118,6 +120,143 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
     }
 }
 
+// ---- register-resident single-pass kernel (K <= 16384, 16-byte aligned rows) ---------------------------------------
+// One CTA per token; thread i owns the 16-element chunks i, i + 256, ... of the row: 4 x LDG.128 per chunk, all issued
+// before the first use, the row stays in registers between the max pass and the quantise pass (the two-pass kernel above
+// re-reads it through L1/L2 and costs ~6 us per call whatever T).  Output per chunk: one 16-byte store into q_rm and one
+// into its pre-swizzled position of q_sw (16 bytes = the swizzle granule).  Group sums with dp4a + redux.sync, prefix sums
+// by a warp scan.  Launched with the programmatic-serialisation attribute: the CTA is resident and past its prologue when
+// the predecessor (the previous GEMM, which reads the workspace this kernel rewrites) drains; griddepcontrol.wait orders
+// every global access after it.
+__device__ __forceinline__ int quant1(float x, double is) {
+    // clamp(round((double) x * is), -128, 127) with round = half away from zero, exactly: the clamp is applied first (it
+    // commutes with rounding at integers), then truncation and an exact fractional test
+    double p = (double) x * is;
+    p = fmin(fmax(p, -129.0), 128.0);
+    int ti = __double2int_rz(p);
+    const double fr = p - (double) ti;
+    ti += (fr >= 0.5) - (fr <= -0.5);
+    return max(-128, min(127, ti));
+}
+
+template <int CH>
+__global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
+                                                          ActView a) {
+    const int t = blockIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    __shared__ float s_red[QT / 32];
+    __shared__ int s_gsum[64];
+    __shared__ int s_gabs[64];
+    if (tid < 64) { s_gsum[tid] = 0; s_gabs[tid] = 0; }
+    const int64_t Kpad = a.Kpad;
+    const bool live = t < T;
+    const float *xr = x + (int64_t) t * ldx;
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    float4 v[CH][4];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < CH; j++) {
+        const int64_t k = (int64_t) (j * QT + tid) * 16;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (live && k + 4 * i < K) v[j][i] = __ldg(reinterpret_cast<const float4 *>(xr + k + 4 * i));
+            else v[j][i] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < CH; j++)
+#pragma unroll
+        for (int i = 0; i < 4; i++) mx = fmaxf(mx, fmaxf(fmaxf(v[j][i].x, v[j][i].y), fmaxf(v[j][i].z, v[j][i].w)));
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (lane == 0) s_red[warp] = mx;
+    __syncthreads();
+    float m = s_red[0];
+#pragma unroll
+    for (int i = 1; i < QT / 32; i++) m = fmaxf(m, s_red[i]);
+    double dm = (double) m;
+    if (!(dm > 1e-5)) dm = 1e-5;  // MAX(eps, .) with eps = 1e-5
+    const double sd = dm / 127;
+    const double is = 1e0 / (sd > 1e-5 ? sd : 1e-5);
+    if (tid == 0) a.scales[t] = live ? (float) sd : 0.0f;
+
+    const int gsize = a.gsize;
+#pragma unroll
+    for (int j = 0; j < CH; j++) {
+        const int64_t k = (int64_t) (j * QT + tid) * 16;
+        const int kw = (j * QT + warp * 32) * 16;   // first k of this warp's 512-k span
+        if (kw >= Kpad) break;                      // warp-uniform: nothing left for this warp
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            if (live && k + 4 * i < K) {
+                const int q0 = quant1(v[j][i].x, is), q1 = quant1(v[j][i].y, is), q2 = quant1(v[j][i].z, is),
+                          q3 = quant1(v[j][i].w, is);
+                pk[i] = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) |
+                        ((uint32_t) (q3 & 0xff) << 24);
+            } else {
+                pk[i] = 0;
+            }
+        }
+        int sum = 0;
+        unsigned asum = 0;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            sum = __dp4a((int) pk[i], 0x01010101, sum);
+            asum = __dp4a(__vabs4(pk[i]), 0x01010101u, asum);
+        }
+        if (k < Kpad) {
+            *reinterpret_cast<uint4 *>(a.q_rm + (int64_t) t * Kpad + k) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
+            const int64_t kb = k / BLOCK_K;
+            const int c = (int) (k % BLOCK_K) / 16;
+            const int64_t off =
+                (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 + ((c ^ (t & 7)) << 4);
+            *reinterpret_cast<uint4 *>(a.q_sw + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+        }
+        // the warp covers 512 consecutive k: at most two K-groups (512 or 640 k per group)
+        const int gA = kw / gsize;
+        const bool inA = (int) (k / gsize) == gA;
+        const int sA = __reduce_add_sync(0xffffffffu, inA ? sum : 0);
+        const int aA = __reduce_add_sync(0xffffffffu, inA ? (int) asum : 0);
+        const int sB = __reduce_add_sync(0xffffffffu, inA ? 0 : sum);
+        const int aB = __reduce_add_sync(0xffffffffu, inA ? 0 : (int) asum);
+        if (lane == 0) {
+            if (aA) { atomicAdd(&s_gsum[gA], sA); atomicAdd(&s_gabs[gA], aA); }
+            if (aB) { atomicAdd(&s_gsum[gA + 1], sB); atomicAdd(&s_gabs[gA + 1], aB); }
+        }
+    }
+    __syncthreads();
+    if (warp == 0) {
+        // exclusive prefix sums of the group sums (warp scan, 32 groups per pass)
+        int32_t *pre = a.gpre + (int64_t) t * (a.G + 1);
+        int carry = 0;
+        bool safe = true;
+        for (int base = 0; base < a.G; base += 32) {
+            const int g = base + lane;
+            const int gv = (g < a.G) ? s_gsum[g] : 0;
+            safe = safe && !((g < a.G) && s_gabs[g] > 32767);
+            int inc = gv;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const int y = __shfl_up_sync(0xffffffffu, inc, o);
+                if (lane >= o) inc += y;
+            }
+            if (g < a.G) pre[g] = carry + inc - gv;
+            carry += __shfl_sync(0xffffffffu, inc, 31);
+        }
+        safe = __all_sync(0xffffffffu, safe);
+        if (lane == 0) {
+            pre[a.G] = carry;
+            a.nowrap[t] = safe ? 1 : 0;
+            // a token tile takes the single-drain path unless one of its tokens stamps it with this call's epoch
+            if (!safe) a.tile_unsafe[t / a.NT] = a.epoch;
+        }
+    }
+}
+
 // Rewrite q_sw from q_rm with swizzled tiles of `a.sw_tile` tokens (used when a GEMM kernel that wants the other tile height
 // is forced on a workspace quantised for the default one).  One thread per 16-byte chunk.
 __global__ void relayout_kernel(ActView a) {
@@ -139,8 +278,32 @@ cudaError_t launch_relayout(const ActView &a, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+template <int CH>
+static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned) a.Tpad);
+    cfg.blockDim = dim3(QT);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a);
+}
+
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s) {
     if (a.G > 64) return cudaErrorInvalidValue;
+    const char *e2 = getenv("VLUT_QUANT_2PASS"), *ep = getenv("VLUT_PDL");
+    const bool two_pass = e2 && atoi(e2) != 0;
+    const bool pdl = ep ? atoi(ep) != 0 : true;
+    const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
+    if (!two_pass && aligned && a.Kpad <= 16384) {
+        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl);
+        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl);
+        return launch_reg<4>(x, ldx, K, T, a, s, pdl);
+    }
     quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a);
     return cudaGetLastError();
 }

@@ -133,6 +133,8 @@ cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches);  
 bool gemm_tc4_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches);  // CTA pairs, cta_group::2
 bool gemm_tc5_supported(int type, int64_t K, int64_t N, int64_t T);
+cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches);  // small T: cp.async weight stream, cluster split-K
+bool gemm_tcs_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_lut(const GemmArgs &g, cudaStream_t s, int *launches);
 bool gemm_lut_supported(int type, int64_t K, int64_t N, int64_t T);
 
