@@ -10,7 +10,10 @@ import re
 from pathlib import Path
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "csrc" / "build" / "libvlut_b200.so"
+import os
+
+# VLUT_B200_LIB: an alternative build of the same library (instrumented variants used by scripts/timeline_tcs.py)
+LIB_PATH = Path(os.environ.get("VLUT_B200_LIB") or (HERE / "csrc" / "build" / "libvlut_b200.so"))
 HEADER = HERE.parent / "include" / "vlut_b200.h"
 
 _lib = None

@@ -26,7 +26,15 @@
 #include "ptx.cuh"
 #include "vlut_common.cuh"
 
+#ifndef VLUT_TCS_DEC_MARKS
+#define VLUT_TCS_DEC_MARKS 31
+#endif
+#define DECM(bit) ((VLUT_TCS_DEC_MARKS & (bit)) != 0)
+
 namespace vlut {
+
+long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
+
 namespace tcs {
 
 constexpr int THREADS = 14 * 32;
@@ -44,6 +52,8 @@ struct Params {
     int S;          // CTAs per strip (cluster size): K-groups split [r*G/S, (r+1)*G/S)
     int NAS, ASB;   // activation ring: NAS stages of ASB 128-k sub-blocks
     int allow_fast, pdl;
+    long long *dbg;   // optional timeline of one CTA (VLUT_TC_DEBUG=1): [4 roles][256] x (clock64, kind)
+    int dbg_cta, dbg_mask;
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {  // K-major, SWIZZLE_128B, 8-row atoms 1024 B apart
@@ -59,23 +69,7 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {  // D s32, A u8, B s8
     return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (128 >> 4) << 24);
 }
 
-// A blocks of this CTA's K slice, in order: group g in [g0, g1), inside a group blocks of <= SPA sub-blocks
-struct Blocks {
-    int g, g1, ab0, gsub, KB;
-    __device__ __forceinline__ void init(int g0, int g1_, int gsub_, int KB_) { g = g0; g1 = g1_; ab0 = 0; gsub = gsub_; KB = KB_; }
-    __device__ __forceinline__ bool valid() const { return g < g1; }
-    __device__ __forceinline__ int nsub() const { return min(gsub, KB - g * gsub); }
-    __device__ __forceinline__ int kb() const { return g * gsub + ab0; }
-    __device__ __forceinline__ int ns() const { return min(SPA, nsub() - ab0); }
-    __device__ __forceinline__ bool first_in_group() const { return ab0 == 0; }
-    __device__ __forceinline__ bool last_in_group() const { return ab0 + SPA >= nsub(); }
-    __device__ __forceinline__ void next() {
-        ab0 += SPA;
-        if (ab0 >= nsub()) { ab0 = 0; ++g; }
-    }
-};
-
-template <int NT, int OUT, int D>
+template <int NT, int OUT, int D, bool DBG>
 __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __grid_constant__ Params p) {
     constexpr int NA = (NT == 64) ? 2 : 3;            // A stages in TMEM
     constexpr uint32_t A_COL0 = 2 * NT;               // two accumulators of NT columns, then the A stages
@@ -105,6 +99,25 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
     const uint32_t red_base = wring + D * W_BLOCK_BYTES;
     int32_t *const red = reinterpret_cast<int32_t *>(smem_raw + (red_base - ptx::smem_u32(smem_raw)));
 
+    // optional timeline (absolute SM clock, so the roles of one CTA share a time base).  Compiled in only for DBG kernels;
+    // branch-free (a predicated store), so that it cannot de-converge a warp in front of an aligned tcgen05 instruction.
+    const uint32_t dbg_lane0 = (DBG && p.dbg != nullptr && (int) blockIdx.x == p.dbg_cta && lane == 0) ? 1u : 0u;
+    int n_ev = 0, ev_role = 0;
+    auto mark = [&](int kind) {
+        if constexpr (DBG) {
+#ifdef VLUT_TCS_MARK_ROLES
+            if (!((VLUT_TCS_MARK_ROLES >> ev_role) & 1)) return;
+#endif
+            const uint32_t on = (dbg_lane0 && n_ev < 256 && ((p.dbg_mask >> ev_role) & 1)) ? 1u : 0u;
+            long long *dst = p.dbg + (ev_role * 256 + min(n_ev, 255)) * 2;
+            const long long now = clock64();
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %0, 0;\n\t@p st.global.v2.u64 [%1], {%2, %3};\n\t}" ::"r"(on),
+                         "l"(dst), "l"(now), "l"((long long) kind)
+                         : "memory");
+            ++n_ev;
+        }
+    };
+
     // let the next kernel of the stream start its prologue (and its own weight prefetch) as early as resources allow
     if (p.pdl) ptx::pdl_launch_dependents();
 
@@ -113,26 +126,28 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
         const int q = (warp - W_DEC0) & 3, h = (warp - W_DEC0) >> 2;
         const int m = q * 32 + lane;
         const int dt = (warp - W_DEC0) * 32 + lane;
+        ev_role = 0;
+        const bool dmark = (warp == W_DEC0);
+        if (dmark && DECM(16)) mark(10);
         const uint64_t pol = ptx::policy_evict_first();
-        const uint8_t *const wsrc = p.g.w + (int64_t) rt * (2 * p.KB) * TILE_BYTES + m * 16;
+        // A blocks of this CTA: pairs of 128-k sub-blocks over the K slice, whatever the K-groups are (group boundaries only
+        // concern the MMA issuer and the epilogue); this thread unpacks sub-block h of every block: 2 x 16 B, 8 KB further
+        // on for every block
+        const int nblk = (nsub_slice + SPA - 1) / SPA;
+        const uint8_t *wsrc = p.g.w + ((int64_t) rt * (2 * p.KB) + 2 * (kb_begin + h)) * TILE_BYTES + m * 16;
         const uint32_t wdst = wring + dt * 16;
-        Blocks pf, cs;
-        pf.init(g0, g1, p.gsub, p.KB);
-        cs.init(g0, g1, p.gsub, p.KB);
-        auto issue = [&](int slot) {   // this thread's 32 bytes of block `pf` -> ring slot; always one commit group
-            if (pf.valid()) {
-                if (h < pf.ns()) {
-                    const uint8_t *src = wsrc + (int64_t) (2 * (pf.kb() + h)) * TILE_BYTES;
-                    ptx::cp_async16_hint(wdst + (slot * 2 + 0) * (DEC_THREADS * 16), src, pol);
-                    ptx::cp_async16_hint(wdst + (slot * 2 + 1) * (DEC_THREADS * 16), src + TILE_BYTES, pol);
-                }
-                pf.next();
+        auto have = [&](int b) { return SPA * b + h < nsub_slice; };
+        auto issue = [&](int b, int slot) {   // this thread's 32 bytes of block b -> ring slot; always one commit group
+            if (b < nblk && have(b)) {
+                const uint8_t *src = wsrc + (int64_t) b * W_BLOCK_BYTES;
+                ptx::cp_async16_hint(wdst + (slot * 2 + 0) * (DEC_THREADS * 16), src, pol);
+                ptx::cp_async16_hint(wdst + (slot * 2 + 1) * (DEC_THREADS * 16), src + TILE_BYTES, pol);
             }
             ptx::cp_async_commit();
         };
         // weights are static data: the stream starts now, whatever the predecessor kernel (quantise) is still doing
 #pragma unroll
-        for (int i = 0; i < D; i++) issue(i);
+        for (int i = 0; i < D; i++) issue(i, i);
         // barriers / TMEM address are set up by warp 12 meanwhile
         ptx::bar_sync(2, THREADS);
         ptx::tc_fence_after();
@@ -140,18 +155,21 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
         const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + h * 32;
         int slot = 0, ai = 0;
         uint32_t aph = 0;
-        for (; cs.valid(); cs.next()) {
+#pragma unroll 1
+        for (int b = 0; b < nblk; b++) {
             ptx::cp_async_wait<D - 1>();
-            const bool have = h < cs.ns();
+            if (dmark && DECM(1)) mark(0);
+            const bool hv = have(b);
             uint4 cw[2];
-            if (have) {
+            if (hv) {
                 cw[0] = ptx::lds128(wdst + (slot * 2 + 0) * (DEC_THREADS * 16));
                 cw[1] = ptx::lds128(wdst + (slot * 2 + 1) * (DEC_THREADS * 16));
             }
-            issue(slot);   // refill the slot just read (same thread: program order)
+            issue(b + D, slot);   // refill the slot just read (same thread: program order)
             ptx::mbar_wait(ptx::smem_u32(&s_aempty[ai]), aph ^ 1);
             ptx::tc_fence_after();
-            if (have) {
+            if (dmark && DECM(2)) mark(1);
+            if (hv) {
 #pragma unroll
                 for (int c = 0; c < 2; c++) {
                     const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
@@ -166,11 +184,14 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                     }
                     ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + c * 16, r);
                 }
+                if (dmark && DECM(4)) mark(2);
                 ptx::tmem_st_wait();
             }
+            if (dmark && DECM(8)) mark(3);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ai]));
+            __syncwarp();
             if (++ai == NA) { ai = 0; aph ^= 1; }
             if (++slot == D) slot = 0;
         }
@@ -206,6 +227,8 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
 
         if (warp == W_ACT) {
             // ===================== activation producer: one bulk copy per stage of ASB sub-blocks =====================
+            ev_role = 3;
+            mark(0);
             const uint64_t pol = ptx::policy_evict_last();
             const int n_as = (nsub_slice + p.ASB - 1) / p.ASB;
             const int8_t *src0 = p.g.act.q_sw + ((int64_t) tt * p.KB + kb_begin) * ACT_BYTES;
@@ -219,68 +242,110 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                                        bytes, full, pol);
                 }
                 __syncwarp();
+                mark(1);
                 if (++ring == p.NAS) { ring = 0; ph ^= 1; }
             }
         } else if (warp == W_MMA) {
             // ===================== MMA issuer =====================
             constexpr uint32_t idesc = make_idesc(NT);
-            Blocks w;
-            w.init(g0, g1, p.gsub, p.KB);
-            int ai = 0, rel = 0, as_ring = 0, asr = 0;
+            constexpr uint32_t SUBD = ACT_BYTES >> 4;   // shared-memory descriptor units per 128-k sub-block
+            ev_role = 1;
+            mark(10);
+            const uint64_t desc0 = make_smem_desc(act_base);
+            const int nblk = (nsub_slice + SPA - 1) / SPA;
+            int ai = 0, ring = 0, asr = 0;   // A stage; activation ring stage and sub-block position inside it
             uint32_t aph = 0, as_ph = 0;
-            uint32_t ndrain = 0;
-            bool open = false, fresh = true;
-            uint32_t ab = 0;
-            for (; w.valid(); w.next()) {
-                if (w.first_in_group() && !open) {
-                    ab = ndrain & 1;
-                    ptx::mbar_wait(ptx::smem_u32(&s_accempty[ab]), ((ndrain >> 1) & 1) ^ 1);
+            if (fast) {
+                // Hot loop.  One thread feeds the tensor pipe and its scalar instruction stream IS the critical path at
+                // N = 16 (scripts/ubench/umma_contend.cu: 40-65 clk per MMA with per-MMA operand set-up and a re-election
+                // per sub-block, against ~18 clk for the MMA itself): one wait, one election and one straight-line burst
+                // of 8 MMAs + commits per A block, every operand an increment of a uniform register.
+                const uint32_t d_tmem = tmem_base;
+#pragma unroll 1
+                for (int b = 0; b < nblk; b++) {
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), aph);
+                    if (asr == 0) ptx::mbar_wait(ptx::smem_u32(&s_actfull[ring]), as_ph);
                     ptx::tc_fence_after();
-                    fresh = true;
-                }
-                ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), aph);
-                ptx::tc_fence_after();
-                const int ns = w.ns();
-                for (int s = 0; s < ns; s++) {
-                    if (asr == 0) ptx::mbar_wait(ptx::smem_u32(&s_actfull[as_ring]), as_ph);
-                    const bool release_as = (asr == p.ASB - 1) || (rel == nsub_slice - 1);
+                    mark(0);
+                    const bool two = SPA * b + 1 < nsub_slice;
+                    const bool last = (b == nblk - 1);
+                    const bool rel_as = (asr + SPA >= p.ASB) || last;
                     if (ptx::elect_one()) {
-                        const uint32_t d_tmem = tmem_base + ab * NT;
-                        const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS + s * 32;
-                        const uint64_t b_desc = make_smem_desc(act_base + (uint32_t) (as_ring * p.ASB + asr) * ACT_BYTES);
+                        const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS;
+                        const uint64_t bd = desc0 + (uint64_t) ((uint32_t) (ring * p.ASB + asr) * SUBD);
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++)
-                            ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, b_desc + (uint64_t) (ks * 2), idesc, (fresh && ks == 0) ? 0u : 1u);
-                        if (release_as) ptx::umma_commit(ptx::smem_u32(&s_actempty[as_ring]));
+                            ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (b > 0 || ks > 0) ? 1u : 0u);
+                        if (two) {
+#pragma unroll
+                            for (int ks = 0; ks < 4; ks++)
+                                ptx::umma_i8_ts(d_tmem, a_tmem + 32 + ks * 8, bd + (uint64_t) (SUBD + ks * 2), idesc, 1u);
+                        }
+                        ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
+                        if (rel_as) ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                        if (last) ptx::umma_commit(ptx::smem_u32(&s_accfull[0]));
                     }
                     __syncwarp();
-                    fresh = false;
-                    ++rel;
-                    if (release_as) {
+                    mark(1);
+                    if (++ai == NA) { ai = 0; aph ^= 1; }
+                    asr += SPA;
+                    if (rel_as) {
                         asr = 0;
-                        if (++as_ring == p.NAS) { as_ring = 0; as_ph ^= 1; }
-                    } else {
-                        ++asr;
+                        if (++ring == p.NAS) { ring = 0; as_ph ^= 1; }
                     }
                 }
-                if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
-                __syncwarp();
-                if (++ai == NA) { ai = 0; aph ^= 1; }
-                if (w.last_in_group()) {
-                    // exact path: one drain per K-group; fast path: one drain for the whole slice
-                    if (!fast || w.g == g1 - 1) {
-                        if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_accfull[ab]));
+            } else {
+                // Exact path (some token of the tile can overflow int16 inside a K-group): one accumulator drain per K-group,
+                // the two accumulators alternate.  Generic per-sub-block loop; group boundaries may fall inside an A block.
+                uint32_t ndrain = 0, ab = 0;
+                int g = g0, gpos = 0;          // current K-group and sub-block position inside it
+                bool fresh = true;
+#pragma unroll 1
+                for (int b = 0; b < nblk; b++) {
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), aph);
+                    ptx::tc_fence_after();
+                    const int ns = min(SPA, nsub_slice - SPA * b);
+                    for (int s = 0; s < ns; s++) {
+                        const int kb = kb_begin + SPA * b + s;
+                        if (gpos == 0) {
+                            ab = ndrain & 1;
+                            ptx::mbar_wait(ptx::smem_u32(&s_accempty[ab]), ((ndrain >> 1) & 1) ^ 1);
+                            ptx::tc_fence_after();
+                            fresh = true;
+                        }
+                        if (asr == 0) ptx::mbar_wait(ptx::smem_u32(&s_actfull[ring]), as_ph);
+                        const bool rel_as = (asr == p.ASB - 1) || (kb == kb_end - 1);
+                        const bool group_end = (gpos + 1 == min(p.gsub, p.KB - g * p.gsub));
+                        if (ptx::elect_one()) {
+                            const uint32_t d_tmem = tmem_base + ab * NT;
+                            const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS + s * 32;
+                            const uint64_t bd = desc0 + (uint64_t) ((uint32_t) (ring * p.ASB + asr) * SUBD);
+#pragma unroll
+                            for (int ks = 0; ks < 4; ks++)
+                                ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (fresh && ks == 0) ? 0u : 1u);
+                            if (rel_as) ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                            if (group_end) ptx::umma_commit(ptx::smem_u32(&s_accfull[ab]));
+                        }
                         __syncwarp();
-                        ++ndrain;
-                        open = false;
-                    } else {
-                        open = true;
+                        fresh = false;
+                        if (group_end) { ++ndrain; ++g; gpos = 0; } else { ++gpos; }
+                        if (rel_as) {
+                            asr = 0;
+                            if (++ring == p.NAS) { ring = 0; as_ph ^= 1; }
+                        } else {
+                            ++asr;
+                        }
                     }
+                    if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
+                    __syncwarp();
+                    if (++ai == NA) { ai = 0; aph ^= 1; }
                 }
             }
         } else {
             // ===================== epilogue warps: TMEM -> (registers | int32 tile in shared memory) =====================
             const int ew = warp;
+            ev_role = 2;
+            if (ew == 0) mark(10);
             const int m = ew * 32 + lane;
             const int et = threadIdx.x;  // 0..127
             const int64_t n = (int64_t) rt * TILE_ROWS + m;
@@ -295,6 +360,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                 ptx::bar_sync(1, 128);
                 ptx::mbar_wait(ptx::smem_u32(&s_accfull[0]), 0);
                 ptx::tc_fence_after();
+                if (ew == 0) mark(0);
                 if (S == 1) {
                     epi::drain_fast<NT, OUT, false>(ta0, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n, p.g.ldo,
                                                     (int) min((int64_t) NT, p.g.T - t0), n < p.g.N, nullptr);
@@ -347,6 +413,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
         }
     }
 
+    if (warp == 0) { ev_role = 2; mark(1); }
     if (S > 1) {
         // ---- split strip: the S partial tiles meet in distributed shared memory; CTA r finishes token slice r ----
         ptx::cluster_sync();
@@ -376,6 +443,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
     }
 
     // ---- teardown ----
+    if (warp == 0) mark(2);
     ptx::tc_fence_before();
     __syncthreads();
     if (warp == W_ACT) {
@@ -397,7 +465,7 @@ static size_t smem_bytes(int nas, int asb) {
     return (size_t) nas * asb * NT * 128 + (size_t) D * W_BLOCK_BYTES + (size_t) NT * 512 + 1024;
 }
 
-template <int NT, int OUT, int D>
+template <int NT, int OUT, int D, bool DBG = false>
 static cudaError_t launch_out(Params &p, cudaStream_t s) {
     // activation ring: stages of ~16 KB, as many as the slice needs / the budget allows
     p.ASB = 16384 / (NT * 128);
@@ -414,7 +482,7 @@ static cudaError_t launch_out(Params &p, cudaStream_t s) {
     if (forced > 0 && forced <= MAX_AS) nas = forced;
     p.NAS = nas;
     const size_t smem = smem_bytes<NT, D>(p.NAS, p.ASB);
-    auto kern = kernel<NT, OUT, D>;
+    auto kern = kernel<NT, OUT, D, DBG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
@@ -443,7 +511,10 @@ static cudaError_t launch_out(Params &p, cudaStream_t s) {
 
 template <int NT, int D>
 static cudaError_t launch_one(Params &p, cudaStream_t s) {
-    if (p.g.n_out == 0) return launch_out<NT, 0, D>(p, s);
+    if (p.g.n_out == 0) {
+        if (D == 8 && NT <= 32 && p.dbg) return launch_out<NT, 0, 8, true>(p, s);   // timeline build (VLUT_TC_DEBUG=1)
+        return launch_out<NT, 0, D>(p, s);
+    }
     return p.g.multicast ? launch_out<NT, 2, D>(p, s) : launch_out<NT, 1, D>(p, s);
 }
 
@@ -489,6 +560,9 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.allow_fast = tcs::env_int("VLUT_TC_FAST", 1);
     p.pdl = tcs::env_int("VLUT_PDL", 1);
     p.S = tcs::pick_split(p, NT);
+    p.dbg = tcs::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, 0) : nullptr;
+    p.dbg_cta = tcs::env_int("VLUT_TCS_DBG_CTA", 0);
+    p.dbg_mask = tcs::env_int("VLUT_TCS_DBG_MASK", 15);
     if (launches) *launches += 1;
     const int deep = tcs::env_int("VLUT_TCS_DEPTH", 8);
     switch (NT) {
