@@ -120,8 +120,8 @@ base = [("tc (old)", TC, {}), ("tc (old), 2pass quant", TC, {"VLUT_QUANT_2PASS":
 tcs_cfgs = [("tcs auto", TCS, {})]
 for s in (1, 2, 4, 8):
     tcs_cfgs.append((f"tcs split={s}", TCS, {"VLUT_TCS_SPLIT": s}))
-tcs_cfgs.append(("tcs split=1 depth=16", TCS, {"VLUT_TCS_SPLIT": 1, "VLUT_TCS_DEPTH": 16}))
-tcs_cfgs.append(("tcs split=2 depth=16", TCS, {"VLUT_TCS_SPLIT": 2, "VLUT_TCS_DEPTH": 16}))
+tcs_cfgs.append(("tcs split=1 depth=8", TCS, {"VLUT_TCS_SPLIT": 1, "VLUT_TCS_DEPTH": 8}))
+tcs_cfgs.append(("tcs split=2 depth=8", TCS, {"VLUT_TCS_SPLIT": 2, "VLUT_TCS_DEPTH": 8}))
 tcs_cfgs.append(("tcs split=1 nopdl", TCS, {"VLUT_TCS_SPLIT": 1, "VLUT_PDL": 0}))
 
 if mode == "quick":

@@ -1,25 +1,28 @@
 // gemm_tcs.cu -- VLUT_ALGO_TCS: the small-token-count Vec-LUT GEMM (T <= 64), built to STREAM the packed weights from HBM.
 //
 // Same arithmetic and exactness contract as gemm_tc4.cu (tcgen05 kind::i8, u8 weight codes x s8 activations -> s32 in TMEM,
-// per-K-group int16 wrap on the exact path, fused fp32 epilogue), reorganised around what the
-// timelines of that kernel showed at T <= 64: the HBM stream, not arithmetic, must set the pace, and every hand-off in
-// the chain  TMA -> mbarrier -> LDS -> unpack -> tcgen05.st -> MMA  costs a memory or barrier round trip.
+// per-K-group int16 wrap on the exact path, fused fp32 epilogue), reorganised around what in-kernel
+// timelines showed at T <= 64 (scripts/timeline_tcs.py, scripts/ubench/umma_contend.cu): nothing is bandwidth- or
+// throughput-bound there; every role is ONE warp walking a serial chain of waits and dependent scalar instructions
+// (~600 clk per 256-k block for a decode warp, ~50 clk of issue per MMA for the MMA thread), so the kernel is built from
+// many short independent chains instead of a few long ones.
 //
-//   * WEIGHTS never pass through a producer warp or an mbarrier.  Decode thread (q, h, lane) owns weight row
-//     m = 32q + lane of the strip and sub-block h of every 256-k A block; it fetches its own 2 x 16 bytes per block with
-//     cp.async (LDGSTS, coalesced 512 B per warp instruction, L2 evict_first) into a private ring of D blocks in shared
-//     memory and reads them back itself (cp.async.wait_group: no cross-thread synchronisation at all).  D x 8 KB per CTA
-//     are in flight from the first instruction of the kernel -- before griddepcontrol.wait, i.e. while the quantise
-//     kernel is still running -- which is what saturating HBM needs (Little: 6.5 TB/s x ~1 us over <= 148 CTAs).
+//   * WEIGHTS never pass through a producer warp or an mbarrier.  Decode thread (q, h, p, lane) owns weight row
+//     m = 32q + lane of the strip, sub-block h of the 256-k A blocks of parity p; it fetches its own 2 x 16 bytes per
+//     block with cp.async (LDGSTS, coalesced 512 B per warp instruction, L2 evict_first) into a private ring of DT blocks
+//     in shared memory and reads them back itself (cp.async.wait_group: no cross-thread synchronisation at all).
+//     DT x 16 KB per CTA are in flight from the first instruction of the kernel -- before griddepcontrol.wait, i.e. while
+//     the quantise kernel is still running.
+//   * SIXTEEN decode warps (two parities) and TWO MMA issuer warps (even / odd A blocks, one TMEM accumulator each, summed
+//     by the epilogue): four A stages in TMEM, two independent decode -> MMA chains.
 //   * K is SPLIT over the CTAs of a thread-block cluster (S = 1..8 CTAs per 128-row strip, whole K-groups each) so that
 //     shapes with few strips (4096 -> 4096: 32) still put >= 128 CTAs on the weight stream.  Partial sums meet in
 //     distributed shared memory: every CTA parks its int32 tile in its own shared memory, one cluster barrier, then CTA r
 //     reduces and stores the token slice r of the tile (ld.shared::cluster).  Integer partials: order-independent, exact.
-//   * 256 TMEM columns and <= ~110 KB of shared memory per CTA at NT <= 32: two CTAs share an SM, so a successor kernel
-//     (PDL) or the second CTA of a split strip overlaps its prologue and weight prefetch with this one's drain.
 //
-//   warps 0-3   epilogue (TMEM lane quadrant = warp)        warps 4-11  decode (quadrant q = (w-4)%4, sub-block h = (w-4)/4)
-//   warp 12     TMEM allocator + activation producer (TMA)  warp 13     MMA issuer
+//   warps 0-3   epilogue (TMEM lane quadrant = warp)
+//   warps 4-19  decode: d = warp - 4, quadrant q = d % 4, sub-block h = (d / 4) % 2, block parity p = d / 8
+//   warp 20     TMEM allocator + activation producer (TMA)     warps 21, 22  MMA issuers (even / odd blocks)
 #include <stdlib.h>
 
 #include "epilogue.cuh"
@@ -27,9 +30,13 @@
 #include "vlut_common.cuh"
 
 #ifndef VLUT_TCS_DEC_MARKS
-#define VLUT_TCS_DEC_MARKS 31
+#define VLUT_TCS_DEC_MARKS 15
 #endif
 #define DECM(bit) ((VLUT_TCS_DEC_MARKS & (bit)) != 0)
+#ifndef VLUT_TCS_ABL
+#define VLUT_TCS_ABL 0   // crash-bisection builds: 1 no tcgen05.st, 2 no tcgen05.mma, 4 no tcgen05.ld, 8 no cp.async, 16 no act copy
+#endif
+#define ABL(bit) ((VLUT_TCS_ABL & (bit)) != 0)
 
 namespace vlut {
 
@@ -37,11 +44,12 @@ long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
 
 namespace tcs {
 
-constexpr int THREADS = 14 * 32;
-constexpr int W_DEC0 = 4, NDEC = 8, W_ACT = 12, W_MMA = 13;
+constexpr int W_DEC0 = 4, NDEC = 16, W_ACT = 20, W_MMA0 = 21;
+constexpr int THREADS = 23 * 32;
 constexpr int SPA = 2;               // 128-k sub-blocks per A block (decode -> MMA hand-off): 256 k
 constexpr int A_COLS = SPA * 32;     // TMEM columns of one A stage
-constexpr int TMEM_COLS = 256;
+constexpr int NA = 4;                // A stages in TMEM; block b uses stage b % 4 (even stages: parity 0, odd: parity 1)
+constexpr int TMEM_COLS = 512;
 constexpr int MAX_AS = 8;            // activation stages (ring)
 constexpr int DEC_THREADS = NDEC * 32;
 constexpr int W_BLOCK_BYTES = 2 * SPA * TILE_BYTES;  // packed bytes of one A block of a strip: 8 KB
@@ -50,8 +58,10 @@ struct Params {
     GemmArgs g;
     int KB, G, gsub, RT;
     int S;          // CTAs per strip (cluster size): K-groups split [r*G/S, (r+1)*G/S)
-    int NAS, ASB;   // activation ring: NAS stages of ASB 128-k sub-blocks
+    int NAS, ASB;   // activation ring: NAS stages of ASB 128-k sub-blocks (ASB a power of two >= 4)
+    int asb_shift;
     int allow_fast, pdl;
+    int issuers;    // MMA issuer warps used on the fast path (2; 1 = experiment / fallback)
     long long *dbg;   // optional timeline of one CTA (VLUT_TC_DEBUG=1): [4 roles][256] x (clock64, kind)
     int dbg_cta, dbg_mask;
 };
@@ -69,9 +79,8 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {  // D s32, A u8, B s8
     return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (128 >> 4) << 24);
 }
 
-template <int NT, int OUT, int D, bool DBG>
-__global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __grid_constant__ Params p) {
-    constexpr int NA = (NT == 64) ? 2 : 3;            // A stages in TMEM
+template <int NT, int OUT, int DT, bool DBG>
+__global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
     constexpr uint32_t A_COL0 = 2 * NT;               // two accumulators of NT columns, then the A stages
     static_assert(A_COL0 + NA * A_COLS <= TMEM_COLS, "TMEM budget");
     constexpr int ACT_BYTES = NT * 128;               // one 128-k sub-block of the token tile, pre-swizzled by the quantiser
@@ -91,12 +100,15 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
     const int g0 = (rank * p.G) / S, g1 = ((rank + 1) * p.G) / S;   // this CTA's K-groups
     const int kb_begin = g0 * p.gsub, kb_end = min(g1 * p.gsub, p.KB);
     const int nsub_slice = kb_end - kb_begin;
+    // A blocks of this CTA: pairs of 128-k sub-blocks over the K slice, whatever the K-groups are (group boundaries only
+    // concern the MMA issuers and the epilogue)
+    const int nblk = (nsub_slice + SPA - 1) / SPA;
 
-    // dynamic shared memory: [activation ring][weight ring: D blocks x 2 chunks x 256 threads x 16 B][int32 tile NT x 128]
+    // dynamic shared memory: [activation ring][weight ring: DT slots x 2 chunks x 512 threads x 16 B][int32 tile NT x 128]
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t act_base = smem_base;
     const uint32_t wring = act_base + (uint32_t) (p.NAS * p.ASB) * ACT_BYTES;
-    const uint32_t red_base = wring + D * W_BLOCK_BYTES;
+    const uint32_t red_base = wring + DT * 2 * DEC_THREADS * 16;
     int32_t *const red = reinterpret_cast<int32_t *>(smem_raw + (red_base - ptx::smem_u32(smem_raw)));
 
     // optional timeline (absolute SM clock, so the roles of one CTA share a time base).  Compiled in only for DBG kernels;
@@ -118,46 +130,43 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
         }
     };
 
-    // let the next kernel of the stream start its prologue (and its own weight prefetch) as early as resources allow
+    // let the next kernel of the stream start its prologue as early as resources allow
     if (p.pdl) ptx::pdl_launch_dependents();
 
     if (warp >= W_DEC0 && warp < W_DEC0 + NDEC) {
         // ===================== decode: HBM -> (cp.async ring) -> registers -> u8 A operand in TMEM =====================
-        const int q = (warp - W_DEC0) & 3, h = (warp - W_DEC0) >> 2;
+        const int d = warp - W_DEC0;
+        const int q = d & 3, h = (d >> 2) & 1, par = d >> 3;
         const int m = q * 32 + lane;
-        const int dt = (warp - W_DEC0) * 32 + lane;
+        const int dt = d * 32 + lane;
         ev_role = 0;
-        const bool dmark = (warp == W_DEC0);
-        if (dmark && DECM(16)) mark(10);
-        const uint64_t pol = ptx::policy_evict_first();
-        // A blocks of this CTA: pairs of 128-k sub-blocks over the K slice, whatever the K-groups are (group boundaries only
-        // concern the MMA issuer and the epilogue); this thread unpacks sub-block h of every block: 2 x 16 B, 8 KB further
-        // on for every block
-        const int nblk = (nsub_slice + SPA - 1) / SPA;
+        const bool dmark = (d == 0);
+        // this thread unpacks sub-block h of the blocks b = par, par + 2, ...: 2 x 16 B per block, 16 KB further on each time
         const uint8_t *wsrc = p.g.w + ((int64_t) rt * (2 * p.KB) + 2 * (kb_begin + h)) * TILE_BYTES + m * 16;
         const uint32_t wdst = wring + dt * 16;
         auto have = [&](int b) { return SPA * b + h < nsub_slice; };
         auto issue = [&](int b, int slot) {   // this thread's 32 bytes of block b -> ring slot; always one commit group
-            if (b < nblk && have(b)) {
+            if (!ABL(8) && b < nblk && have(b)) {
                 const uint8_t *src = wsrc + (int64_t) b * W_BLOCK_BYTES;
-                ptx::cp_async16_hint(wdst + (slot * 2 + 0) * (DEC_THREADS * 16), src, pol);
-                ptx::cp_async16_hint(wdst + (slot * 2 + 1) * (DEC_THREADS * 16), src + TILE_BYTES, pol);
+                ptx::cp_async16(wdst + (slot * 2 + 0) * (DEC_THREADS * 16), src);
+                ptx::cp_async16(wdst + (slot * 2 + 1) * (DEC_THREADS * 16), src + TILE_BYTES);
             }
             ptx::cp_async_commit();
         };
         // weights are static data: the stream starts now, whatever the predecessor kernel (quantise) is still doing
 #pragma unroll
-        for (int i = 0; i < D; i++) issue(i, i);
-        // barriers / TMEM address are set up by warp 12 meanwhile
+        for (int i = 0; i < DT; i++) issue(par + 2 * i, i);
+        // barriers / TMEM address are set up by warp 20 meanwhile
         ptx::bar_sync(2, THREADS);
         ptx::tc_fence_after();
         const uint32_t tmem_base = s_tmem_base;
         const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + h * 32;
-        int slot = 0, ai = 0;
-        uint32_t aph = 0;
+        int slot = 0;
 #pragma unroll 1
-        for (int b = 0; b < nblk; b++) {
-            ptx::cp_async_wait<D - 1>();
+        for (int b = par; b < nblk; b += 2) {
+            const int ai = b & (NA - 1);
+            const uint32_t aph = (uint32_t) (b >> 2) & 1;
+            ptx::cp_async_wait<DT - 1>();
             if (dmark && DECM(1)) mark(0);
             const bool hv = have(b);
             uint4 cw[2];
@@ -165,7 +174,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                 cw[0] = ptx::lds128(wdst + (slot * 2 + 0) * (DEC_THREADS * 16));
                 cw[1] = ptx::lds128(wdst + (slot * 2 + 1) * (DEC_THREADS * 16));
             }
-            issue(b + D, slot);   // refill the slot just read (same thread: program order)
+            issue(b + 2 * DT, slot);   // refill the slot just read (same thread: program order)
             ptx::mbar_wait(ptx::smem_u32(&s_aempty[ai]), aph ^ 1);
             ptx::tc_fence_after();
             if (dmark && DECM(2)) mark(1);
@@ -182,7 +191,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                         r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
                         r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
                     }
-                    ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + c * 16, r);
+                    if (!ABL(1)) ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + c * 16, r);
                 }
                 if (dmark && DECM(4)) mark(2);
                 ptx::tmem_st_wait();
@@ -192,8 +201,7 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ai]));
             __syncwarp();
-            if (++ai == NA) { ai = 0; aph ^= 1; }
-            if (++slot == D) slot = 0;
+            if (++slot == DT) slot = 0;
         }
         ptx::cp_async_wait<0>();
     } else {
@@ -201,10 +209,10 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
             if (lane == 0) {
                 for (int s = 0; s < p.NAS; s++) {
                     ptx::mbar_init(ptx::smem_u32(&s_actfull[s]), 1);
-                    ptx::mbar_init(ptx::smem_u32(&s_actempty[s]), 1);
+                    ptx::mbar_init(ptx::smem_u32(&s_actempty[s]), 2);   // one commit per MMA issuer
                 }
                 for (int d = 0; d < NA; d++) {
-                    ptx::mbar_init(ptx::smem_u32(&s_afull[d]), NDEC);
+                    ptx::mbar_init(ptx::smem_u32(&s_afull[d]), NDEC / 2);   // the decode warps of one parity
                     ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
                 }
                 for (int d = 0; d < 2; d++) {
@@ -230,79 +238,94 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
             ev_role = 3;
             mark(0);
             const uint64_t pol = ptx::policy_evict_last();
-            const int n_as = (nsub_slice + p.ASB - 1) / p.ASB;
+            const int n_as = (nsub_slice + p.ASB - 1) >> p.asb_shift;
             const int8_t *src0 = p.g.act.q_sw + ((int64_t) tt * p.KB + kb_begin) * ACT_BYTES;
             for (int asi = 0, ring = 0, ph = 0; asi < n_as; asi++) {
                 ptx::mbar_wait(ptx::smem_u32(&s_actempty[ring]), ph ^ 1);
                 if (ptx::elect_one()) {
                     const uint32_t bytes = (uint32_t) min(p.ASB, nsub_slice - asi * p.ASB) * ACT_BYTES;
                     const uint32_t full = ptx::smem_u32(&s_actfull[ring]);
-                    ptx::mbar_arrive_expect_tx(full, bytes);
-                    ptx::bulk_g2s_hint(act_base + (uint32_t) (ring * p.ASB) * ACT_BYTES, src0 + (int64_t) asi * p.ASB * ACT_BYTES,
+                    if (ABL(16)) ptx::mbar_arrive(full);
+                    else ptx::mbar_arrive_expect_tx(full, bytes);
+                    if (!ABL(16)) ptx::bulk_g2s_hint(act_base + (uint32_t) (ring * p.ASB) * ACT_BYTES, src0 + (int64_t) asi * p.ASB * ACT_BYTES,
                                        bytes, full, pol);
                 }
                 __syncwarp();
                 mark(1);
                 if (++ring == p.NAS) { ring = 0; ph ^= 1; }
             }
-        } else if (warp == W_MMA) {
-            // ===================== MMA issuer =====================
+        } else if (warp >= W_MMA0) {
+            // ===================== MMA issuers =====================
             constexpr uint32_t idesc = make_idesc(NT);
             constexpr uint32_t SUBD = ACT_BYTES >> 4;   // shared-memory descriptor units per 128-k sub-block
+            const int w = warp - W_MMA0;
             ev_role = 1;
-            mark(10);
+            if (w == 0) mark(10);
             const uint64_t desc0 = make_smem_desc(act_base);
-            const int nblk = (nsub_slice + SPA - 1) / SPA;
-            int ai = 0, ring = 0, asr = 0;   // A stage; activation ring stage and sub-block position inside it
-            uint32_t aph = 0, as_ph = 0;
             if (fast) {
-                // Hot loop.  One thread feeds the tensor pipe and its scalar instruction stream IS the critical path at
-                // N = 16 (scripts/ubench/umma_contend.cu: 40-65 clk per MMA with per-MMA operand set-up and a re-election
-                // per sub-block, against ~18 clk for the MMA itself): one wait, one election and one straight-line burst
-                // of 8 MMAs + commits per A block, every operand an increment of a uniform register.
-                const uint32_t d_tmem = tmem_base;
+                // Hot loop.  One thread feeds the tensor pipe and its scalar instruction stream is a critical path at N = 16
+                // (scripts/ubench/umma_contend.cu: 40-65 clk per MMA with per-MMA operand set-up and a re-election per
+                // sub-block, against ~18 clk for the MMA itself): per A block one wait, one election and one straight-line
+                // burst of 8 MMAs + commits, every operand an increment of a uniform register -- and two issuers, on
+                // alternate blocks, each with its own accumulator (the epilogue adds the two).
+                const uint32_t d_tmem = tmem_base + w * NT;
+                int asi_seen = -1, ring = 0;
+                uint32_t as_ph = 0;
 #pragma unroll 1
-                for (int b = 0; b < nblk; b++) {
-                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), aph);
-                    if (asr == 0) ptx::mbar_wait(ptx::smem_u32(&s_actfull[ring]), as_ph);
+                const int bstep = p.issuers;
+                for (int b = (bstep == 2 ? w : (w == 0 ? 0 : nblk)); b < nblk; b += bstep) {
+                    const int ai = b & (NA - 1);
+                    const int rel = SPA * b, asi = rel >> p.asb_shift, asr = rel & (p.ASB - 1);
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), (uint32_t) (b >> 2) & 1);
+                    if (asi != asi_seen) {
+                        // stages are visited in order, one or two steps at a time (a stage holds >= 2 blocks)
+                        for (; asi_seen < asi; ++asi_seen)
+                            if (asi_seen >= 0 && ++ring == p.NAS) { ring = 0; as_ph ^= 1; }
+                        ptx::mbar_wait(ptx::smem_u32(&s_actfull[ring]), as_ph);
+                    }
                     ptx::tc_fence_after();
-                    mark(0);
-                    const bool two = SPA * b + 1 < nsub_slice;
-                    const bool last = (b == nblk - 1);
-                    const bool rel_as = (asr + SPA >= p.ASB) || last;
+                    if (w == 0) mark(0);
+                    const bool two = rel + 1 < nsub_slice;
+                    const bool last = b + bstep >= nblk;
+                    const bool rel_as = last || ((SPA * (b + bstep)) >> p.asb_shift) != asi;   // my last block in this stage
                     if (ptx::elect_one()) {
                         const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS;
                         const uint64_t bd = desc0 + (uint64_t) ((uint32_t) (ring * p.ASB + asr) * SUBD);
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++)
-                            ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (b > 0 || ks > 0) ? 1u : 0u);
+                            if (!ABL(2)) ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (b > w || ks > 0) ? 1u : 0u);
                         if (two) {
 #pragma unroll
                             for (int ks = 0; ks < 4; ks++)
-                                ptx::umma_i8_ts(d_tmem, a_tmem + 32 + ks * 8, bd + (uint64_t) (SUBD + ks * 2), idesc, 1u);
+                                if (!ABL(2)) ptx::umma_i8_ts(d_tmem, a_tmem + 32 + ks * 8, bd + (uint64_t) (SUBD + ks * 2), idesc, 1u);
                         }
                         ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
-                        if (rel_as) ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
-                        if (last) ptx::umma_commit(ptx::smem_u32(&s_accfull[0]));
+                        if (rel_as) {
+                            ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                            if (bstep == 1) ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));   // both arrivals are mine
+                        }
+                        if (last) ptx::umma_commit(ptx::smem_u32(&s_accfull[w]));
                     }
                     __syncwarp();
-                    mark(1);
-                    if (++ai == NA) { ai = 0; aph ^= 1; }
-                    asr += SPA;
-                    if (rel_as) {
-                        asr = 0;
-                        if (++ring == p.NAS) { ring = 0; as_ph ^= 1; }
-                    }
+                    if (w == 0) mark(1);
                 }
-            } else {
+                if (w >= nblk || (bstep == 1 && w == 1)) {   // no block at all for this issuer (a one-block slice): nothing to drain, nothing to wait for
+                    if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_accfull[w]));
+                    __syncwarp();
+                }
+            } else if (w == 0) {
                 // Exact path (some token of the tile can overflow int16 inside a K-group): one accumulator drain per K-group,
-                // the two accumulators alternate.  Generic per-sub-block loop; group boundaries may fall inside an A block.
+                // the two accumulators alternate.  One issuer, generic per-sub-block loop; group boundaries may fall inside
+                // an A block.
                 uint32_t ndrain = 0, ab = 0;
                 int g = g0, gpos = 0;          // current K-group and sub-block position inside it
+                int ring = 0, asr = 0;
+                uint32_t as_ph = 0;
                 bool fresh = true;
 #pragma unroll 1
                 for (int b = 0; b < nblk; b++) {
-                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), aph);
+                    const int ai = b & (NA - 1);
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), (uint32_t) (b >> 2) & 1);
                     ptx::tc_fence_after();
                     const int ns = min(SPA, nsub_slice - SPA * b);
                     for (int s = 0; s < ns; s++) {
@@ -323,7 +346,10 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
 #pragma unroll
                             for (int ks = 0; ks < 4; ks++)
                                 ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (fresh && ks == 0) ? 0u : 1u);
-                            if (rel_as) ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                            if (rel_as) {   // both arrivals of the stage's release barrier come from this issuer here
+                                ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                                ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
+                            }
                             if (group_end) ptx::umma_commit(ptx::smem_u32(&s_accfull[ab]));
                         }
                         __syncwarp();
@@ -338,7 +364,6 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                     }
                     if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
                     __syncwarp();
-                    if (++ai == NA) { ai = 0; aph ^= 1; }
                 }
             }
         } else {
@@ -358,20 +383,30 @@ __global__ void __launch_bounds__(THREADS, (NT <= 32) ? 2 : 1) kernel(const __gr
                 // the +1 offset of the u8 codes over this CTA's whole slice
                 if (et < NT) s_gs[et] = __ldg(pre + g1) - __ldg(pre + g0);
                 ptx::bar_sync(1, 128);
+                const bool both = nblk >= 2 && p.issuers == 2;   // the odd-block issuer had work: its accumulator counts
                 ptx::mbar_wait(ptx::smem_u32(&s_accfull[0]), 0);
+                if (both) ptx::mbar_wait(ptx::smem_u32(&s_accfull[1]), 0);
                 ptx::tc_fence_after();
                 if (ew == 0) mark(0);
-                if (S == 1) {
-                    epi::drain_fast<NT, OUT, false>(ta0, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n, p.g.ldo,
-                                                    (int) min((int64_t) NT, p.g.T - t0), n < p.g.N, nullptr);
-                } else {
+                const bool ws = (p.g.w_scale != 1.0f);
+                const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
 #pragma unroll 1
-                    for (int c0 = 0; c0 < NT; c0 += 16) {
-                        uint32_t v[16];
-                        ptx::tmem_ld_32x32b_x16(ta0 + c0, v);
-                        epi::tmem_ld_wait_dep(v);
+                for (int c0 = 0; c0 < NT; c0 += 16) {
+                    uint32_t va[16], vb[16];
+                    if (!ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + c0, va);
+                    if (both && !ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + NT + c0, vb);
+                    epi::tmem_ld_wait_dep(va);
+                    if (both) {
+                        epi::tmem_ld_wait_dep(vb);
 #pragma unroll
-                        for (int i = 0; i < 16; i++) red[(c0 + i) * 128 + m] = (int32_t) v[i] - s_gs[c0 + i];
+                        for (int i = 0; i < 16; i++) va[i] += vb[i];
+                    }
+                    if (S == 1) {
+                        epi::fast_chunk<OUT, false>(va, c0, s_gs, s_sc, ws, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n,
+                                                    p.g.ldo, tvalid, n < p.g.N, nullptr);
+                    } else {
+#pragma unroll
+                        for (int i = 0; i < 16; i++) red[(c0 + i) * 128 + m] = (int32_t) va[i] - s_gs[c0 + i];
                     }
                 }
             } else {
@@ -457,32 +492,30 @@ static int env_int(const char *name, int dflt) {
     return v ? atoi(v) : dflt;
 }
 
-constexpr int SMEM_PAIR_BUDGET = 112 * 1024;   // two CTAs per SM
-constexpr int SMEM_SOLO_BUDGET = 208 * 1024;
+constexpr int SMEM_BUDGET = 216 * 1024;
 
-template <int NT, int D>
+template <int NT, int DT>
 static size_t smem_bytes(int nas, int asb) {
-    return (size_t) nas * asb * NT * 128 + (size_t) D * W_BLOCK_BYTES + (size_t) NT * 512 + 1024;
+    return (size_t) nas * asb * NT * 128 + (size_t) DT * 2 * DEC_THREADS * 16 + (size_t) NT * 512 + 1024;
 }
 
-template <int NT, int OUT, int D, bool DBG = false>
+template <int NT, int OUT, int DT, bool DBG = false>
 static cudaError_t launch_out(Params &p, cudaStream_t s) {
-    // activation ring: stages of ~16 KB, as many as the slice needs / the budget allows
+    // activation ring: stages of >= 16 KB and >= 4 sub-blocks (two A blocks: one per MMA issuer), as many as the slice
+    // needs / the budget allows
     p.ASB = 16384 / (NT * 128);
+    if (p.ASB < 4) p.ASB = 4;
+    p.asb_shift = p.ASB == 8 ? 3 : 2;
     const int max_groups = (p.G + p.S - 1) / p.S;
     const int need = (max_groups * p.gsub + p.ASB - 1) / p.ASB;
-    const bool pair_ok = (NT <= 32);
-    const bool want_pair = pair_ok && ((int64_t) p.RT * p.S > p.g.sm_count || env_int("VLUT_TCS_PAIR", 1));
     int nas = need < MAX_AS ? need : MAX_AS;
-    if (nas < 2) nas = need < 2 ? need : 2;
     if (nas < 1) nas = 1;
-    const int budget = want_pair ? SMEM_PAIR_BUDGET : SMEM_SOLO_BUDGET;
-    while (nas > 2 && (int) smem_bytes<NT, D>(nas, p.ASB) > budget) --nas;
+    while (nas > 2 && (int) smem_bytes<NT, DT>(nas, p.ASB) > SMEM_BUDGET) --nas;
     const int forced = env_int("VLUT_TCS_NAS", 0);
     if (forced > 0 && forced <= MAX_AS) nas = forced;
     p.NAS = nas;
-    const size_t smem = smem_bytes<NT, D>(p.NAS, p.ASB);
-    auto kern = kernel<NT, OUT, D, DBG>;
+    const size_t smem = smem_bytes<NT, DT>(p.NAS, p.ASB);
+    auto kern = kernel<NT, OUT, DT, DBG>;
     cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
@@ -509,22 +542,23 @@ static cudaError_t launch_out(Params &p, cudaStream_t s) {
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int NT, int D>
+template <int NT, int DT>
 static cudaError_t launch_one(Params &p, cudaStream_t s) {
     if (p.g.n_out == 0) {
-        if (D == 8 && NT <= 32 && p.dbg) return launch_out<NT, 0, 8, true>(p, s);   // timeline build (VLUT_TC_DEBUG=1)
-        return launch_out<NT, 0, D>(p, s);
+        if (DT == 4 && NT <= 32 && p.dbg) return launch_out<NT, 0, 4, true>(p, s);   // timeline build (VLUT_TC_DEBUG=1)
+        return launch_out<NT, 0, DT>(p, s);
     }
-    return p.g.multicast ? launch_out<NT, 2, D>(p, s) : launch_out<NT, 1, D>(p, s);
+    return p.g.multicast ? launch_out<NT, 2, DT>(p, s) : launch_out<NT, 1, DT>(p, s);
 }
 
-// CTAs per strip.  More CTAs = more weight bytes in flight and shorter per-CTA streams; a split strip pays one cluster
-// barrier and a distributed-shared-memory reduction.  Whole K-groups per CTA, at most 8 (portable cluster size).
-static int pick_split(const Params &p, int NT) {
+// CTAs per strip.  More CTAs = more weight bytes in flight and shorter per-CTA chains; a split strip pays one cluster
+// barrier and a distributed-shared-memory reduction.  Whole K-groups per CTA, at most 8 (portable cluster size), one CTA
+// per SM.
+static int pick_split(const Params &p) {
     const int forced = env_int("VLUT_TCS_SPLIT", 0);
     const int smax = p.G < 8 ? p.G : 8;
     if (forced > 0) return forced < smax ? forced : smax;
-    const int slots = p.g.sm_count * (NT <= 32 ? 2 : 1);   // co-resident CTAs
+    const int slots = p.g.sm_count;
     int best = 1;
     double best_cost = 1e30;
     for (int s = 1; s <= smax; s++) {
@@ -532,10 +566,8 @@ static int pick_split(const Params &p, int NT) {
         if (ctas > slots && s > 1) break;
         const int max_groups = (p.G + s - 1) / s;
         const int waves = (int) ((ctas + slots - 1) / slots);
-        // time ~ the longest per-CTA stream, but never less than the whole matrix at full HBM rate, + a fixed cost per split
-        const double stream = (double) max_groups * waves;
-        const double floor_ = (double) p.RT * p.G / 120.0;   // ~120 CTA-streams saturate HBM
-        const double cost = (stream > floor_ ? stream : floor_) + 0.35 * (s > 1) + 0.05 * s;
+        // time ~ fixed start/drain cost (about 3 K-groups' worth) + the longest per-CTA chain + a cost per split
+        const double cost = (double) max_groups * waves + 3.0 + 0.6 * (s > 1) + 0.05 * s;
         if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
     }
     return best;
@@ -559,16 +591,17 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.RT = (int) (g.Npad / TILE_ROWS);
     p.allow_fast = tcs::env_int("VLUT_TC_FAST", 1);
     p.pdl = tcs::env_int("VLUT_PDL", 1);
-    p.S = tcs::pick_split(p, NT);
+    p.S = tcs::pick_split(p);
+    p.issuers = tcs::env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
     p.dbg = tcs::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, 0) : nullptr;
     p.dbg_cta = tcs::env_int("VLUT_TCS_DBG_CTA", 0);
     p.dbg_mask = tcs::env_int("VLUT_TCS_DBG_MASK", 15);
     if (launches) *launches += 1;
-    const int deep = tcs::env_int("VLUT_TCS_DEPTH", 8);
+    const int deep = tcs::env_int("VLUT_TCS_DEPTH", 4);   // ring slots per decode thread: 16 KB per CTA each
     switch (NT) {
-        case 16: return deep >= 16 ? tcs::launch_one<16, 16>(p, s) : tcs::launch_one<16, 8>(p, s);
-        case 32: return deep >= 16 ? tcs::launch_one<32, 16>(p, s) : tcs::launch_one<32, 8>(p, s);
-        case 64: return tcs::launch_one<64, 8>(p, s);
+        case 16: return deep >= 8 ? tcs::launch_one<16, 8>(p, s) : tcs::launch_one<16, 4>(p, s);
+        case 32: return deep >= 8 ? tcs::launch_one<32, 8>(p, s) : tcs::launch_one<32, 4>(p, s);
+        case 64: return tcs::launch_one<64, 4>(p, s);
         default: return cudaErrorInvalidValue;
     }
 }

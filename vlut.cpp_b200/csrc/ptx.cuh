@@ -171,9 +171,12 @@ __device__ __forceinline__ void umma_i8_ts(uint32_t d_tmem, uint32_t a_tmem, uin
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---- cp.async (LDGSTS): per-thread 16-byte global -> shared copies, completion tracked per thread in commit groups ----
-__device__ __forceinline__ void cp_async16_hint(uint32_t dst_smem, const void *src_gmem, uint64_t policy) {
-    asm volatile("cp.async.cg.shared.global.L2::cache_hint [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src_gmem), "l"(policy)
-                 : "memory");
+// No L2::cache_hint variant on purpose: with the policy operand ptxas 12.9 keeps the descriptor in a uniform register pair
+// that it re-materialises under per-thread predicates around other uniform-register uses; builds that differed only in
+// unrelated code (a debug mark, one more warp role) died with "illegal instruction" at the first LDGSTS, and the variant
+// without the policy operand never did (scripts/check_abl.py).
+__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void *src_gmem) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst_smem), "l"(src_gmem) : "memory");
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
