@@ -34,9 +34,14 @@
 #endif
 #define DECM(bit) ((VLUT_TCS_DEC_MARKS & (bit)) != 0)
 #ifndef VLUT_TCS_ABL
-#define VLUT_TCS_ABL 0   // crash-bisection builds: 1 no tcgen05.st, 2 no tcgen05.mma, 4 no tcgen05.ld, 8 no cp.async, 16 no act copy
+#define VLUT_TCS_ABL 0   // timing / bisection builds (wrong results): 1 no tcgen05.st, 2 no tcgen05.mma, 4 no tcgen05.ld, 8 no cp.async,
+                         // 16 no act copy, 32 no wait::st, 64 decode ignores A-stage-free, 128 MMA ignores A-stage-full
 #endif
 #define ABL(bit) ((VLUT_TCS_ABL & (bit)) != 0)
+#ifndef VLUT_TCS_BACKOFF
+#define VLUT_TCS_BACKOFF 0   // which waits sleep between polls: 1 epilogue, 2 activation producer, 4 MMA issuers, 8 decode
+#endif
+#define WAIT(bit, ns, bar, par) do { if (VLUT_TCS_BACKOFF & (bit)) ptx::mbar_wait_backoff(bar, par, ns); else ptx::mbar_wait(bar, par); } while (0)
 
 namespace vlut {
 
@@ -48,7 +53,8 @@ constexpr int W_DEC0 = 4, NDEC = 16, W_ACT = 20, W_MMA0 = 21;
 constexpr int THREADS = 23 * 32;
 constexpr int SPA = 2;               // 128-k sub-blocks per A block (decode -> MMA hand-off): 256 k
 constexpr int A_COLS = SPA * 32;     // TMEM columns of one A stage
-constexpr int NA = 4;                // A stages in TMEM; block b uses stage b % 4 (even stages: parity 0, odd: parity 1)
+constexpr int NAP = 3;               // A stages per block parity
+constexpr int NA = 2 * NAP;          // A stages in TMEM; the i-th block of parity p (b = 2i + p) uses stage 2 (i % 3) + p
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_AS = 8;            // activation stages (ring)
 constexpr int DEC_THREADS = NDEC * 32;
@@ -161,40 +167,44 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         ptx::tc_fence_after();
         const uint32_t tmem_base = s_tmem_base;
         const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + h * 32;
-        int slot = 0;
+        int slot = 0, k3 = 0;
+        uint32_t aph = 0;
 #pragma unroll 1
         for (int b = par; b < nblk; b += 2) {
-            const int ai = b & (NA - 1);
-            const uint32_t aph = (uint32_t) (b >> 2) & 1;
+            const int ai = 2 * k3 + par;
             ptx::cp_async_wait<DT - 1>();
             if (dmark && DECM(1)) mark(0);
             const bool hv = have(b);
-            uint4 cw[2];
+            uint4 cw[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
             if (hv) {
                 cw[0] = ptx::lds128(wdst + (slot * 2 + 0) * (DEC_THREADS * 16));
                 cw[1] = ptx::lds128(wdst + (slot * 2 + 1) * (DEC_THREADS * 16));
             }
             issue(b + 2 * DT, slot);   // refill the slot just read (same thread: program order)
-            ptx::mbar_wait(ptx::smem_u32(&s_aempty[ai]), aph ^ 1);
+            // unpack into registers BEFORE the A stage is known to be free: only the two stores stay on the hand-off chain
+            uint32_t r[2][16];
+#pragma unroll
+            for (int c = 0; c < 2; c++) {
+                const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    // shifts as multiply-high on the FMA pipe, masks on the ALU pipe
+                    r[c][4 * j + 0] = wv[j] & 0x03030303u;
+                    r[c][4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
+                    r[c][4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
+                    r[c][4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
+                }
+            }
+            if (!ABL(64)) WAIT(8, 20, ptx::smem_u32(&s_aempty[ai]), aph ^ 1);
             ptx::tc_fence_after();
             if (dmark && DECM(2)) mark(1);
             if (hv) {
-#pragma unroll
-                for (int c = 0; c < 2; c++) {
-                    const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
-                    uint32_t r[16];
-#pragma unroll
-                    for (int j = 0; j < 4; j++) {
-                        // shifts as multiply-high on the FMA pipe, masks on the ALU pipe
-                        r[4 * j + 0] = wv[j] & 0x03030303u;
-                        r[4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
-                        r[4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
-                        r[4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
-                    }
-                    if (!ABL(1)) ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + c * 16, r);
+                if (!ABL(1)) {
+                    ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS, r[0]);
+                    ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + 16, r[1]);
                 }
                 if (dmark && DECM(4)) mark(2);
-                ptx::tmem_st_wait();
+                if (!ABL(32)) ptx::tmem_st_wait();
             }
             if (dmark && DECM(8)) mark(3);
             ptx::tc_fence_before();
@@ -202,6 +212,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ai]));
             __syncwarp();
             if (++slot == DT) slot = 0;
+            if (++k3 == NAP) { k3 = 0; aph ^= 1; }
         }
         ptx::cp_async_wait<0>();
     } else {
@@ -241,7 +252,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             const int n_as = (nsub_slice + p.ASB - 1) >> p.asb_shift;
             const int8_t *src0 = p.g.act.q_sw + ((int64_t) tt * p.KB + kb_begin) * ACT_BYTES;
             for (int asi = 0, ring = 0, ph = 0; asi < n_as; asi++) {
-                ptx::mbar_wait(ptx::smem_u32(&s_actempty[ring]), ph ^ 1);
+                WAIT(2, 100, ptx::smem_u32(&s_actempty[ring]), ph ^ 1);
                 if (ptx::elect_one()) {
                     const uint32_t bytes = (uint32_t) min(p.ASB, nsub_slice - asi * p.ASB) * ACT_BYTES;
                     const uint32_t full = ptx::smem_u32(&s_actfull[ring]);
@@ -271,12 +282,18 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 const uint32_t d_tmem = tmem_base + w * NT;
                 int asi_seen = -1, ring = 0;
                 uint32_t as_ph = 0;
-#pragma unroll 1
                 const int bstep = p.issuers;
+                int k3e = 0, k3o = 0;          // per block parity: position in its ring of NAP A stages, and phase
+                uint32_t aphe = 0, apho = 0;
+#pragma unroll 1
                 for (int b = (bstep == 2 ? w : (w == 0 ? 0 : nblk)); b < nblk; b += bstep) {
-                    const int ai = b & (NA - 1);
+                    const int par = b & 1;
+                    const int ai = 2 * (par ? k3o : k3e) + par;
+                    const uint32_t a_par = par ? apho : aphe;
+                    if (par) { if (++k3o == NAP) { k3o = 0; apho ^= 1; } }
+                    else     { if (++k3e == NAP) { k3e = 0; aphe ^= 1; } }
                     const int rel = SPA * b, asi = rel >> p.asb_shift, asr = rel & (p.ASB - 1);
-                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), (uint32_t) (b >> 2) & 1);
+                    if (!ABL(128)) WAIT(4, 20, ptx::smem_u32(&s_afull[ai]), a_par);
                     if (asi != asi_seen) {
                         // stages are visited in order, one or two steps at a time (a stage holds >= 2 blocks)
                         for (; asi_seen < asi; ++asi_seen)
@@ -322,10 +339,15 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 int ring = 0, asr = 0;
                 uint32_t as_ph = 0;
                 bool fresh = true;
+                int k3e = 0, k3o = 0;
+                uint32_t aphe = 0, apho = 0;
 #pragma unroll 1
                 for (int b = 0; b < nblk; b++) {
-                    const int ai = b & (NA - 1);
-                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), (uint32_t) (b >> 2) & 1);
+                    const int par = b & 1;
+                    const int ai = 2 * (par ? k3o : k3e) + par;
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), par ? apho : aphe);
+                    if (par) { if (++k3o == NAP) { k3o = 0; apho ^= 1; } }
+                    else     { if (++k3e == NAP) { k3e = 0; aphe ^= 1; } }
                     ptx::tc_fence_after();
                     const int ns = min(SPA, nsub_slice - SPA * b);
                     for (int s = 0; s < ns; s++) {
@@ -384,8 +406,8 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 if (et < NT) s_gs[et] = __ldg(pre + g1) - __ldg(pre + g0);
                 ptx::bar_sync(1, 128);
                 const bool both = nblk >= 2 && p.issuers == 2;   // the odd-block issuer had work: its accumulator counts
-                ptx::mbar_wait(ptx::smem_u32(&s_accfull[0]), 0);
-                if (both) ptx::mbar_wait(ptx::smem_u32(&s_accfull[1]), 0);
+                WAIT(1, 200, ptx::smem_u32(&s_accfull[0]), 0);
+                if (both) WAIT(1, 200, ptx::smem_u32(&s_accfull[1]), 0);
                 ptx::tc_fence_after();
                 if (ew == 0) mark(0);
                 const bool ws = (p.g.w_scale != 1.0f);
@@ -415,7 +437,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     const uint32_t gi = (uint32_t) (g - g0), ab = gi & 1;
                     if (et < NT) s_gs[et] = __ldg(pre + g + 1) - __ldg(pre + g);
                     ptx::bar_sync(1, 128);
-                    ptx::mbar_wait(ptx::smem_u32(&s_accfull[ab]), (gi >> 1) & 1);
+                    WAIT(1, 100, ptx::smem_u32(&s_accfull[ab]), (gi >> 1) & 1);
                     ptx::tc_fence_after();
 #pragma unroll 1
                     for (int c0 = 0; c0 < NT; c0 += 16) {

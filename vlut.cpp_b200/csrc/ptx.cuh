@@ -39,6 +39,12 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     }
 }
 
+// wait with back-off: a warp that polls try_wait in a tight loop competes for its scheduler's issue slots with the warps
+// that do the work (several pollers per scheduler slow every other role down); sleeping between polls frees the slots
+__device__ __forceinline__ void mbar_wait_backoff(uint32_t bar, uint32_t parity, uint32_t ns) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(ns);
+}
+
 // ---- TMA -------------------------------------------------------------------------------------------------
 // 1-D bulk copy global -> shared, completion counted in bytes on an mbarrier (SASS: UBLKCP)
 __device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void *src_gmem, uint32_t bytes, uint32_t bar) {
