@@ -190,7 +190,46 @@ def main() -> None:
     nb_gguf = api.nbytes(type_, K, N)
     is_i2 = type_ in (api.I2_V, api.I2_V_4, api.I2_V_8)
 
-    ctx = api.Context(dev)
+    # a capturable (non-default) stream: launch-bound loops (two ~5 us kernels per op at small T against ~6 us of
+    # Python/ctypes launch overhead per call) are captured once into CUDA graphs and replayed
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
+    ctx = api.Context(dev, stream=stream)
+
+    def graph_time_us(fn, iters):
+        """GPU time per call of fn(i), i in [0, iters): one CUDA graph of the whole loop, best of 3 replays, CUDA events
+        on the launch stream.  Falls back to an eager loop if the capture fails."""
+        for i in range(5):
+            fn(i)
+        torch.cuda.synchronize()
+        try:
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=stream):
+                for i in range(iters):
+                    fn(i)
+            g.replay()
+            torch.cuda.synchronize()
+            best = None
+            for _ in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                g.replay()
+                e1.record()
+                torch.cuda.synchronize()
+                t = e0.elapsed_time(e1) / iters * 1e3
+                best = t if best is None else min(best, t)
+            del g
+            return best, "cuda-graph"
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] graph capture failed ({e}); timing an eager loop", file=sys.stderr)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(iters):
+                fn(i)
+            e1.record()
+            torch.cuda.synchronize()
+            return e0.elapsed_time(e1) / iters * 1e3, "eager"
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
 
@@ -280,15 +319,24 @@ def main() -> None:
         step(i)
     barrier()
     launches0 = ctx.launch_count
-    ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-    ev[0].record()
-    for i in range(args.steps):
-        step(i)
-        ev[i + 1].record()
-    barrier()
-    launches = ctx.launch_count - launches0
-    total_ms = ev[0].elapsed_time(ev[-1])
-    per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+    timing_mode = "eager"
+    if world == 1:
+        # single GPU: the K steps are one CUDA graph (same kernels, same order, same rotating buffers)
+        us, timing_mode = graph_time_us(step, args.steps)
+        launches = (ctx.launch_count - launches0) * args.steps // (args.steps + 5) if timing_mode == "cuda-graph" else \
+            (ctx.launch_count - launches0) * args.steps // (2 * args.steps + 5)
+        total_ms = us * args.steps / 1e3
+        per_step = [us / 1e3] * args.steps
+    else:
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
+        ev[0].record()
+        for i in range(args.steps):
+            step(i)
+            ev[i + 1].record()
+        barrier()
+        launches = ctx.launch_count - launches0
+        total_ms = ev[0].elapsed_time(ev[-1])
+        per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
     if world > 1:
         tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -302,29 +350,13 @@ def main() -> None:
     def time_gemm(t, iters, x_list):
         ctx.quantize_act(type_, x_list[0])
         o = torch.empty((t, N), dtype=torch.float32, device=dev)
-        for i in range(5):
-            ctx.gemm(weights[i % n_w], t, out=o)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(iters):
-            ctx.gemm(weights[i % n_w], t, out=o)
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / iters * 1e3, api.ALGO_NAMES[ctx.last_algo]  # us
+        us, _ = graph_time_us(lambda i: ctx.gemm(weights[i % n_w], t, out=o), iters)
+        return us, api.ALGO_NAMES[ctx.last_algo]
 
     def time_op(t, iters, x_list):
         o = torch.empty((t, N), dtype=torch.float32, device=dev)
-        for i in range(5):
-            ctx.mul_mat(weights[i % n_w], x_list[i % n_x], out=o)
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(iters):
-            ctx.mul_mat(weights[i % n_w], x_list[i % n_x], out=o)
-        e1.record()
-        torch.cuda.synchronize()
-        return e0.elapsed_time(e1) / iters * 1e3
+        us, _ = graph_time_us(lambda i: ctx.mul_mat(weights[i % n_w], x_list[i % n_x], out=o), iters)
+        return us
 
     def alg_bytes(t):  # W (GGUF packed size) + A (f32 in) + O (f32 out)
         return nb_gguf + 4 * t * K + 4 * t * N
@@ -426,6 +458,7 @@ def main() -> None:
                              f"{ws_mb:.0f} MB > 126 MB L2",
                        "parallelism": f"row-shard x{world}, gather={gather_mode}" if world > 1 else "single GPU"},
             "median_ms_per_step": statistics.median(per_step),
+            "timing": f"{timing_mode}: K steps timed with CUDA events on the launch stream",
             "gpu_launches": int(launches),
             "roofline": roofline,
             "cpu_baseline": cpu,

@@ -333,10 +333,11 @@ int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
     const char *v = getenv("VLUT_B200_ALGO");
     const int forced = v ? atoi(v) : 0;
     if (forced > 0) return forced;
-    // crossover table from B200 measurements (profiles/r1_crossover.txt):
-    //   T <= 64   TC   (one CTA per 128-row strip, 8-warp unpack, PDL): lowest latency
+    // crossover table from B200 measurements (profiles/):
+    //   T <= 64   TCS  (per-thread cp.async weight stream, 16 decode warps, two MMA issuers, cluster split-K)
     //   T  > 64   TCP  (CTA pairs, cta_group::2: each CTA stages half of the 128-token tile -> half the activation fill)
-    // TC1 / TC2 (earlier generations) stay selectable for comparison.
+    // TC (one CTA per strip, TMA weight stream), TC1 / TC2 (earlier generations) stay selectable for comparison.
+    if (T <= 64 && gemm_tcs_supported(type, K, N, T)) return VLUT_ALGO_TCS;
     if (T > 64 && gemm_tc5_supported(type, K, N, T)) return VLUT_ALGO_TCP;
     if (gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
     if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
