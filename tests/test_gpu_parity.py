@@ -297,6 +297,28 @@ def test_tcs_cluster_split_k(ctx, orc, monkeypatch, split, T, fast):
             assert not bad.any(), f"type={type_} K={K} rep={rep}: {bad.sum()} of {bad.size} differ, first at {np.argwhere(bad)[0]}"
 
 
+@pytest.mark.parametrize("T", [5, 32, 48])
+def test_gemm_on_a_workspace_quantised_for_another_kernel(ctx, orc, T):
+    """vlut_quantize_act lays the int8 operand tiles out for the kernel AUTO would run (tile height, and for the small-T
+    kernel the regrouped K order); a vlut_gemm that names another kernel must re-tile the workspace first, both ways."""
+    a = api()
+    type_, K, N = O.I1_V_2, 3200, 264
+    w = O.make_ternary(N, K, seed=21)
+    x = O.make_acts(T, K, seed=T)
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    W = ctx.upload(type_, K, N, packed)
+    xd = torch.from_numpy(x).cuda()
+    for algo in [a.ALGO_TC, a.ALGO_TCS, a.ALGO_SIMPLE, a.ALGO_TCS, a.ALGO_TC1, a.ALGO_AUTO]:
+        ctx.quantize_act(type_, xd)
+        out = ctx.gemm(W, T, algo=algo)
+        torch.cuda.synchronize()
+        assert np.array_equal(bits(out.cpu().numpy()), bits(ref)), f"algo={algo}"
+        out2 = ctx.gemm(W, T, algo=a.ALGO_TC)   # and back, on the same quantisation
+        torch.cuda.synchronize()
+        assert np.array_equal(bits(out2.cpu().numpy()), bits(ref)), f"algo={algo} then tc"
+
+
 def test_fused_scatter_epilogue_single_gpu_emulation(ctx, orc):
     """The fused all-gather epilogue (vlut_mul_mat_scatter, peer-pointer flavour), with the 'ranks' emulated as two
     shards and two result buffers on ONE GPU: each shard's GEMM writes its column slice into both [T][N] buffers."""

@@ -276,7 +276,11 @@ int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t r
 }
 
 // (re)shape the activation workspace of ctx for (type, K, T)
-static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, bool pair_layout) {
+// q_sw layout a GEMM kernel wants (ActView.sw_tile / ActView.perm)
+static int want_sw_tile(int algo, int NT) { return (algo == VLUT_ALGO_TCP && NT >= 64) ? NT / 2 : NT; }
+static int want_perm(int algo, int NT) { return (algo == VLUT_ALGO_TCS && NT <= 32) ? 1 : 0; }
+
+static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo) {
     const int64_t Kpad = round_up(K, BLOCK_K);
     const int NT = token_tile(T);
     const int64_t Tpad = round_up(T, NT);
@@ -304,7 +308,8 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, bool pair_la
     c->act.G = G;
     c->act.gsize = gsize;
     c->act.NT = NT;
-    c->act.sw_tile = (pair_layout && NT >= 64) ? NT / 2 : NT;
+    c->act.sw_tile = want_sw_tile(algo, NT);
+    c->act.perm = want_perm(algo, NT);
     c->act_K = K;
     c->act_T = T;
     c->act_type = type;
@@ -317,7 +322,7 @@ static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx,
     if (!type_valid(type) || K <= 0 || K % 4) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
     if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, 1, T);
-    int rc = prepare_act(c, type, K, T, algo == VLUT_ALGO_TCP);
+    int rc = prepare_act(c, type, K, T, algo);
     if (rc) return rc;
     CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream));
     c->launches++;
@@ -391,9 +396,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP ||
         algo == VLUT_ALGO_TCS) {
         // the workspace was quantised for another kernel's swizzled-tile height: rewrite q_sw from q_rm
-        const int want = (algo == VLUT_ALGO_TCP && c->act.NT >= 64) ? c->act.NT / 2 : c->act.NT;
-        if (c->act.sw_tile != want) {
+        const int want = want_sw_tile(algo, c->act.NT), wantp = want_perm(algo, c->act.NT);
+        if (c->act.sw_tile != want || c->act.perm != wantp) {
             c->act.sw_tile = want;
+            c->act.perm = wantp;
             CK(launch_relayout(c->act, c->stream));
             launches++;
         }

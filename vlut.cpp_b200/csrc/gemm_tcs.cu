@@ -53,11 +53,16 @@ constexpr int W_DEC0 = 4, NDEC = 16, W_ACT = 20, W_MMA0 = 21;
 constexpr int THREADS = 23 * 32;
 constexpr int SPA = 2;               // 128-k sub-blocks per A block (decode -> MMA hand-off): 256 k
 constexpr int A_COLS = SPA * 32;     // TMEM columns of one A stage
-constexpr int NAP = 3;               // A stages per block parity
-constexpr int NA = 2 * NAP;          // A stages in TMEM; the i-th block of parity p (b = 2i + p) uses stage 2 (i % 3) + p
+constexpr int NPH = 4;               // decode phases: the four warps of phase ph unpack the blocks b = ph (mod 4)
 constexpr int TMEM_COLS = 512;
 constexpr int MAX_AS = 8;            // activation stages (ring)
 constexpr int DEC_THREADS = NDEC * 32;
+// MASK (token tiles <= 32): mask-only weight unpack.  The 2-bit codes are not shifted down: word & (0x03030303 << 2i) is the
+// A operand of bit-pair position i, scaled by 4^i, and goes to accumulator i (4 per issuer); the epilogue adds D_i >> 2i.
+// The activation rows are regrouped to match (ActView.perm).  16 LOP3 per 64 weights instead of 16 LOP3 + 12 IMAD.HI.
+__host__ __device__ constexpr bool mask_mode(int nt) { return nt <= 32; }
+__host__ __device__ constexpr int accs_for(int nt) { return mask_mode(nt) ? 4 : 1; }                 // accumulators per issuer
+__host__ __device__ constexpr int na_for(int nt) { return (TMEM_COLS - 2 * accs_for(nt) * nt) / A_COLS > 6 ? 6 : (TMEM_COLS - 2 * accs_for(nt) * nt) / A_COLS; }
 constexpr int W_BLOCK_BYTES = 2 * SPA * TILE_BYTES;  // packed bytes of one A block of a strip: 8 KB
 
 struct Params {
@@ -87,18 +92,23 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {  // D s32, A u8, B s8
 
 template <int NT, int OUT, int DT, bool DBG>
 __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
-    constexpr uint32_t A_COL0 = 2 * NT;               // two accumulators of NT columns, then the A stages
-    static_assert(A_COL0 + NA * A_COLS <= TMEM_COLS, "TMEM budget");
+    constexpr bool MASK = mask_mode(NT);
+    constexpr int ACCS = accs_for(NT);                // accumulators per MMA issuer (fast path) / per drain set (exact path)
+    constexpr int NA = na_for(NT);                    // A stages in TMEM; block b uses stage b % NA
+    constexpr uint32_t A_COL0 = 2 * ACCS * NT;        // two accumulator sets, then the A stages
+    static_assert(NA >= 4 && A_COL0 + NA * A_COLS <= TMEM_COLS, "TMEM budget");
     constexpr int ACT_BYTES = NT * 128;               // one 128-k sub-block of the token tile, pre-swizzled by the quantiser
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_actfull[MAX_AS], s_actempty[MAX_AS];
-    __shared__ __align__(8) uint64_t s_afull[NA], s_aempty[NA];
+    __shared__ __align__(8) uint64_t s_afull[6], s_aempty[6];
     __shared__ __align__(8) uint64_t s_accfull[2], s_accempty[2];
     __shared__ uint32_t s_tmem_base;
     __shared__ __align__(16) int32_t s_gs[NT];
     __shared__ __align__(16) float s_sc[NT];
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // the warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role loops' state (block
+    // counters, barrier and TMEM addresses, descriptors) in uniform registers instead of converting per use (R2UR)
+    const int warp = __shfl_sync(0xffffffffu, (int) (threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int S = p.S;
     const int rank = (S > 1) ? (int) ptx::cluster_ctarank() : 0;
     const int rt = blockIdx.x / S;
@@ -110,11 +120,11 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     // concern the MMA issuers and the epilogue)
     const int nblk = (nsub_slice + SPA - 1) / SPA;
 
-    // dynamic shared memory: [activation ring][weight ring: DT slots x 2 chunks x 512 threads x 16 B][int32 tile NT x 128]
+    // dynamic shared memory: [activation ring][weight ring: DT slots x 4 chunks x 512 threads x 16 B][int32 tile NT x 128]
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t act_base = smem_base;
     const uint32_t wring = act_base + (uint32_t) (p.NAS * p.ASB) * ACT_BYTES;
-    const uint32_t red_base = wring + DT * 2 * DEC_THREADS * 16;
+    const uint32_t red_base = wring + DT * 4 * DEC_THREADS * 16;
     int32_t *const red = reinterpret_cast<int32_t *>(smem_raw + (red_base - ptx::smem_u32(smem_raw)));
 
     // optional timeline (absolute SM clock, so the roles of one CTA share a time base).  Compiled in only for DBG kernels;
@@ -142,77 +152,94 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     if (warp >= W_DEC0 && warp < W_DEC0 + NDEC) {
         // ===================== decode: HBM -> (cp.async ring) -> registers -> u8 A operand in TMEM =====================
         const int d = warp - W_DEC0;
-        const int q = d & 3, h = (d >> 2) & 1, par = d >> 3;
+        const int q = d & 3, ph = d >> 2;
         const int m = q * 32 + lane;
         const int dt = d * 32 + lane;
         ev_role = 0;
         const bool dmark = (d == 0);
-        // this thread unpacks sub-block h of the blocks b = par, par + 2, ...: 2 x 16 B per block, 16 KB further on each time
-        const uint8_t *wsrc = p.g.w + ((int64_t) rt * (2 * p.KB) + 2 * (kb_begin + h)) * TILE_BYTES + m * 16;
+        // this thread unpacks its row of the blocks b = ph, ph + 4, ...: 4 x 16 B per block (two 128-k sub-blocks of two
+        // 64-k chunks), 32 KB further on each time
+        const uint8_t *wsrc = p.g.w + ((int64_t) rt * (2 * p.KB) + 2 * kb_begin) * TILE_BYTES + m * 16;
         const uint32_t wdst = wring + dt * 16;
-        auto have = [&](int b) { return SPA * b + h < nsub_slice; };
-        auto issue = [&](int b, int slot) {   // this thread's 32 bytes of block b -> ring slot; always one commit group
-            if (!ABL(8) && b < nblk && have(b)) {
+        auto issue = [&](int b, int slot) {   // this thread's 64 bytes of block b -> ring slot; always one commit group
+            if (!ABL(8) && b < nblk) {
                 const uint8_t *src = wsrc + (int64_t) b * W_BLOCK_BYTES;
-                ptx::cp_async16(wdst + (slot * 2 + 0) * (DEC_THREADS * 16), src);
-                ptx::cp_async16(wdst + (slot * 2 + 1) * (DEC_THREADS * 16), src + TILE_BYTES);
+                ptx::cp_async16(wdst + (slot * 4 + 0) * (DEC_THREADS * 16), src);
+                ptx::cp_async16(wdst + (slot * 4 + 1) * (DEC_THREADS * 16), src + TILE_BYTES);
+                if (SPA * b + 1 < nsub_slice) {
+                    ptx::cp_async16(wdst + (slot * 4 + 2) * (DEC_THREADS * 16), src + 2 * TILE_BYTES);
+                    ptx::cp_async16(wdst + (slot * 4 + 3) * (DEC_THREADS * 16), src + 3 * TILE_BYTES);
+                }
             }
             ptx::cp_async_commit();
         };
         // weights are static data: the stream starts now, whatever the predecessor kernel (quantise) is still doing
 #pragma unroll
-        for (int i = 0; i < DT; i++) issue(par + 2 * i, i);
+        for (int i = 0; i < DT; i++) issue(ph + NPH * i, i);
         // barriers / TMEM address are set up by warp 20 meanwhile
         ptx::bar_sync(2, THREADS);
         ptx::tc_fence_after();
         const uint32_t tmem_base = s_tmem_base;
-        const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + h * 32;
-        int slot = 0, k3 = 0;
-        uint32_t aph = 0;
+        const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0;
+        int slot = 0;
+        int ai = ph % NA;              // A stage of block b (= b % NA) and how often it has been used before (b / NA)
+        uint32_t an = ph / NA;
 #pragma unroll 1
-        for (int b = par; b < nblk; b += 2) {
-            const int ai = 2 * k3 + par;
+        for (int b = ph; b < nblk; b += NPH) {
             ptx::cp_async_wait<DT - 1>();
             if (dmark && DECM(1)) mark(0);
-            const bool hv = have(b);
-            uint4 cw[2] = {make_uint4(0, 0, 0, 0), make_uint4(0, 0, 0, 0)};
-            if (hv) {
-                cw[0] = ptx::lds128(wdst + (slot * 2 + 0) * (DEC_THREADS * 16));
-                cw[1] = ptx::lds128(wdst + (slot * 2 + 1) * (DEC_THREADS * 16));
+            const bool two = SPA * b + 1 < nsub_slice;
+            uint4 cw[4];
+#pragma unroll
+            for (int c = 0; c < 4; c++) {
+                if (c < 2 || two) cw[c] = ptx::lds128(wdst + (slot * 4 + c) * (DEC_THREADS * 16));
+                else cw[c] = make_uint4(0x55555555u, 0x55555555u, 0x55555555u, 0x55555555u);   // weight 0 everywhere
             }
-            issue(b + 2 * DT, slot);   // refill the slot just read (same thread: program order)
-            // unpack into registers BEFORE the A stage is known to be free: only the two stores stay on the hand-off chain
-            uint32_t r[2][16];
+            issue(b + NPH * DT, slot);   // refill the slot just read (same thread: program order)
+            // the first sub-block is unpacked into registers BEFORE the A stage is known to be free, the second one while
+            // the first store is in flight (64 + 16 registers for both at once would not fit 736 threads)
+            auto unpack = [&](int sb, uint32_t (&r)[32]) {
+                const uint32_t wv[8] = {cw[2 * sb].x, cw[2 * sb].y, cw[2 * sb].z, cw[2 * sb].w,
+                                        cw[2 * sb + 1].x, cw[2 * sb + 1].y, cw[2 * sb + 1].z, cw[2 * sb + 1].w};
+                if constexpr (MASK) {
+                    // column i*8 + w: the codes at bit-pair position i of word w, left in place (scaled by 4^i)
 #pragma unroll
-            for (int c = 0; c < 2; c++) {
-                const uint32_t wv[4] = {cw[c].x, cw[c].y, cw[c].z, cw[c].w};
+                    for (int i = 0; i < 4; i++)
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    // shifts as multiply-high on the FMA pipe, masks on the ALU pipe
-                    r[c][4 * j + 0] = wv[j] & 0x03030303u;
-                    r[c][4 * j + 1] = __umulhi(wv[j], 1u << 30) & 0x03030303u;
-                    r[c][4 * j + 2] = __umulhi(wv[j], 1u << 28) & 0x03030303u;
-                    r[c][4 * j + 3] = __umulhi(wv[j], 1u << 26) & 0x03030303u;
+                        for (int w8 = 0; w8 < 8; w8++) r[i * 8 + w8] = wv[w8] & (0x03030303u << (2 * i));
+                } else {
+                    // column 4w + i: shifts as multiply-high on the FMA pipe, masks on the ALU pipe
+#pragma unroll
+                    for (int w8 = 0; w8 < 8; w8++) {
+                        r[4 * w8 + 0] = wv[w8] & 0x03030303u;
+                        r[4 * w8 + 1] = __umulhi(wv[w8], 1u << 30) & 0x03030303u;
+                        r[4 * w8 + 2] = __umulhi(wv[w8], 1u << 28) & 0x03030303u;
+                        r[4 * w8 + 3] = __umulhi(wv[w8], 1u << 26) & 0x03030303u;
+                    }
                 }
-            }
-            if (!ABL(64)) WAIT(8, 20, ptx::smem_u32(&s_aempty[ai]), aph ^ 1);
+            };
+            uint32_t r0[32];
+            unpack(0, r0);
+            if (!ABL(64)) WAIT(8, 20, ptx::smem_u32(&s_aempty[ai]), (an & 1) ^ 1);
             ptx::tc_fence_after();
             if (dmark && DECM(2)) mark(1);
-            if (hv) {
-                if (!ABL(1)) {
-                    ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS, r[0]);
-                    ptx::tmem_st_32x32b_x16(taddr0 + ai * A_COLS + 16, r[1]);
-                }
-                if (dmark && DECM(4)) mark(2);
-                if (!ABL(32)) ptx::tmem_st_wait();
+            if (!ABL(1)) ptx::tmem_st_32x32b_x32(taddr0 + ai * A_COLS, r0);
+            if (two) {
+                uint32_t r1[32];
+                unpack(1, r1);
+                if (!ABL(1)) ptx::tmem_st_32x32b_x32(taddr0 + ai * A_COLS + 32, r1);
             }
+            if (dmark && DECM(4)) mark(2);
+            if (!ABL(32)) ptx::tmem_st_wait();
             if (dmark && DECM(8)) mark(3);
             ptx::tc_fence_before();
             __syncwarp();
             if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_afull[ai]));
             __syncwarp();
             if (++slot == DT) slot = 0;
-            if (++k3 == NAP) { k3 = 0; aph ^= 1; }
+            ai += NPH % NA;
+            an += NPH / NA;
+            if (ai >= NA) { ai -= NA; ++an; }
         }
         ptx::cp_async_wait<0>();
     } else {
@@ -223,7 +250,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     ptx::mbar_init(ptx::smem_u32(&s_actempty[s]), 2);   // one commit per MMA issuer
                 }
                 for (int d = 0; d < NA; d++) {
-                    ptx::mbar_init(ptx::smem_u32(&s_afull[d]), NDEC / 2);   // the decode warps of one parity
+                    ptx::mbar_init(ptx::smem_u32(&s_afull[d]), NDEC / NPH);   // the four decode warps of the block's phase
                     ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
                 }
                 for (int d = 0; d < 2; d++) {
@@ -273,27 +300,25 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             ev_role = 1;
             if (w == 0) mark(10);
             const uint64_t desc0 = make_smem_desc(act_base);
+            // One K=32 MMA per (sub-block, quarter ks): A columns ks*8 .. +8 of the sub-block, B bytes ks*32 .. +32 of the
+            // activation rows.  MASK: quarter ks is bit-pair position ks of the weight words -> accumulator ks.
             if (fast) {
                 // Hot loop.  One thread feeds the tensor pipe and its scalar instruction stream is a critical path at N = 16
                 // (scripts/ubench/umma_contend.cu: 40-65 clk per MMA with per-MMA operand set-up and a re-election per
                 // sub-block, against ~18 clk for the MMA itself): per A block one wait, one election and one straight-line
                 // burst of 8 MMAs + commits, every operand an increment of a uniform register -- and two issuers, on
-                // alternate blocks, each with its own accumulator (the epilogue adds the two).
-                const uint32_t d_tmem = tmem_base + w * NT;
+                // alternate blocks, each with its own accumulator set (the epilogue adds the two).
+                const uint32_t d_tmem = tmem_base + w * (ACCS * NT);
                 int asi_seen = -1, ring = 0;
                 uint32_t as_ph = 0;
                 const int bstep = p.issuers;
-                int k3e = 0, k3o = 0;          // per block parity: position in its ring of NAP A stages, and phase
-                uint32_t aphe = 0, apho = 0;
+                const int b0 = (bstep == 2 ? w : (w == 0 ? 0 : nblk));
+                int ai = b0 % NA;
+                uint32_t an = b0 / NA;
 #pragma unroll 1
-                for (int b = (bstep == 2 ? w : (w == 0 ? 0 : nblk)); b < nblk; b += bstep) {
-                    const int par = b & 1;
-                    const int ai = 2 * (par ? k3o : k3e) + par;
-                    const uint32_t a_par = par ? apho : aphe;
-                    if (par) { if (++k3o == NAP) { k3o = 0; apho ^= 1; } }
-                    else     { if (++k3e == NAP) { k3e = 0; aphe ^= 1; } }
+                for (int b = b0; b < nblk; b += bstep) {
                     const int rel = SPA * b, asi = rel >> p.asb_shift, asr = rel & (p.ASB - 1);
-                    if (!ABL(128)) WAIT(4, 20, ptx::smem_u32(&s_afull[ai]), a_par);
+                    if (!ABL(128)) WAIT(4, 20, ptx::smem_u32(&s_afull[ai]), an & 1);
                     if (asi != asi_seen) {
                         // stages are visited in order, one or two steps at a time (a stage holds >= 2 blocks)
                         for (; asi_seen < asi; ++asi_seen)
@@ -303,6 +328,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     ptx::tc_fence_after();
                     if (w == 0) mark(0);
                     const bool two = rel + 1 < nsub_slice;
+                    const bool first = (b == b0);
                     const bool last = b + bstep >= nblk;
                     const bool rel_as = last || ((SPA * (b + bstep)) >> p.asb_shift) != asi;   // my last block in this stage
                     if (ptx::elect_one()) {
@@ -310,11 +336,15 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                         const uint64_t bd = desc0 + (uint64_t) ((uint32_t) (ring * p.ASB + asr) * SUBD);
 #pragma unroll
                         for (int ks = 0; ks < 4; ks++)
-                            if (!ABL(2)) ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (b > w || ks > 0) ? 1u : 0u);
+                            if (!ABL(2))
+                                ptx::umma_i8_ts(d_tmem + (MASK ? ks * NT : 0), a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc,
+                                                (first && (MASK || ks == 0)) ? 0u : 1u);
                         if (two) {
 #pragma unroll
                             for (int ks = 0; ks < 4; ks++)
-                                if (!ABL(2)) ptx::umma_i8_ts(d_tmem, a_tmem + 32 + ks * 8, bd + (uint64_t) (SUBD + ks * 2), idesc, 1u);
+                                if (!ABL(2))
+                                    ptx::umma_i8_ts(d_tmem + (MASK ? ks * NT : 0), a_tmem + 32 + ks * 8, bd + (uint64_t) (SUBD + ks * 2),
+                                                    idesc, 1u);
                         }
                         ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
                         if (rel_as) {
@@ -325,33 +355,31 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     }
                     __syncwarp();
                     if (w == 0) mark(1);
+                    ai += bstep;
+                    if (ai >= NA) { ai -= NA; ++an; }
                 }
-                if (w >= nblk || (bstep == 1 && w == 1)) {   // no block at all for this issuer (a one-block slice): nothing to drain, nothing to wait for
+                if (b0 >= nblk) {   // no block at all for this issuer: nothing to drain, nothing to wait for
                     if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_accfull[w]));
                     __syncwarp();
                 }
             } else if (w == 0) {
                 // Exact path (some token of the tile can overflow int16 inside a K-group): one accumulator drain per K-group,
-                // the two accumulators alternate.  One issuer, generic per-sub-block loop; group boundaries may fall inside
-                // an A block.
+                // the two accumulator sets alternate.  One issuer, generic per-sub-block loop; group boundaries may fall
+                // inside an A block.
                 uint32_t ndrain = 0, ab = 0;
                 int g = g0, gpos = 0;          // current K-group and sub-block position inside it
                 int ring = 0, asr = 0;
                 uint32_t as_ph = 0;
                 bool fresh = true;
-                int k3e = 0, k3o = 0;
-                uint32_t aphe = 0, apho = 0;
+                int ai = 0;
+                uint32_t an = 0;
 #pragma unroll 1
                 for (int b = 0; b < nblk; b++) {
-                    const int par = b & 1;
-                    const int ai = 2 * (par ? k3o : k3e) + par;
-                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), par ? apho : aphe);
-                    if (par) { if (++k3o == NAP) { k3o = 0; apho ^= 1; } }
-                    else     { if (++k3e == NAP) { k3e = 0; aphe ^= 1; } }
+                    ptx::mbar_wait(ptx::smem_u32(&s_afull[ai]), an & 1);
                     ptx::tc_fence_after();
                     const int ns = min(SPA, nsub_slice - SPA * b);
-                    for (int s = 0; s < ns; s++) {
-                        const int kb = kb_begin + SPA * b + s;
+                    for (int sb = 0; sb < ns; sb++) {
+                        const int kb = kb_begin + SPA * b + sb;
                         if (gpos == 0) {
                             ab = ndrain & 1;
                             ptx::mbar_wait(ptx::smem_u32(&s_accempty[ab]), ((ndrain >> 1) & 1) ^ 1);
@@ -362,12 +390,13 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                         const bool rel_as = (asr == p.ASB - 1) || (kb == kb_end - 1);
                         const bool group_end = (gpos + 1 == min(p.gsub, p.KB - g * p.gsub));
                         if (ptx::elect_one()) {
-                            const uint32_t d_tmem = tmem_base + ab * NT;
-                            const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS + s * 32;
+                            const uint32_t d_tmem = tmem_base + ab * (ACCS * NT);
+                            const uint32_t a_tmem = tmem_base + A_COL0 + ai * A_COLS + sb * 32;
                             const uint64_t bd = desc0 + (uint64_t) ((uint32_t) (ring * p.ASB + asr) * SUBD);
 #pragma unroll
                             for (int ks = 0; ks < 4; ks++)
-                                ptx::umma_i8_ts(d_tmem, a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc, (fresh && ks == 0) ? 0u : 1u);
+                                ptx::umma_i8_ts(d_tmem + (MASK ? ks * NT : 0), a_tmem + ks * 8, bd + (uint64_t) (ks * 2), idesc,
+                                                (fresh && (MASK || ks == 0)) ? 0u : 1u);
                             if (rel_as) {   // both arrivals of the stage's release barrier come from this issuer here
                                 ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
                                 ptx::umma_commit(ptx::smem_u32(&s_actempty[ring]));
@@ -386,6 +415,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     }
                     if (ptx::elect_one()) ptx::umma_commit(ptx::smem_u32(&s_aempty[ai]));
                     __syncwarp();
+                    if (++ai == NA) { ai = 0; ++an; }
                 }
             }
         } else {
@@ -405,23 +435,28 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 // the +1 offset of the u8 codes over this CTA's whole slice
                 if (et < NT) s_gs[et] = __ldg(pre + g1) - __ldg(pre + g0);
                 ptx::bar_sync(1, 128);
-                const bool both = nblk >= 2 && p.issuers == 2;   // the odd-block issuer had work: its accumulator counts
+                const int nsets = (nblk >= 2 && p.issuers == 2) ? 2 : 1;   // the odd-block issuer had work: its set counts
                 WAIT(1, 200, ptx::smem_u32(&s_accfull[0]), 0);
-                if (both) WAIT(1, 200, ptx::smem_u32(&s_accfull[1]), 0);
+                if (nsets == 2) WAIT(1, 200, ptx::smem_u32(&s_accfull[1]), 0);
                 ptx::tc_fence_after();
                 if (ew == 0) mark(0);
                 const bool ws = (p.g.w_scale != 1.0f);
                 const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
 #pragma unroll 1
                 for (int c0 = 0; c0 < NT; c0 += 16) {
-                    uint32_t va[16], vb[16];
-                    if (!ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + c0, va);
-                    if (both && !ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + NT + c0, vb);
-                    epi::tmem_ld_wait_dep(va);
-                    if (both) {
-                        epi::tmem_ld_wait_dep(vb);
+                    // sum over the issuers' accumulator sets; MASK: accumulator i holds 4^i x its share
+                    uint32_t va[16];
 #pragma unroll
-                        for (int i = 0; i < 16; i++) va[i] += vb[i];
+                    for (int i = 0; i < 16; i++) va[i] = 0;
+                    for (int set = 0; set < nsets; set++) {
+#pragma unroll
+                        for (int i = 0; i < ACCS; i++) {
+                            uint32_t v[16];
+                            if (!ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + (set * ACCS + i) * NT + c0, v);
+                            epi::tmem_ld_wait_dep(v);
+#pragma unroll
+                            for (int j = 0; j < 16; j++) va[j] += (uint32_t) ((int32_t) v[j] >> (2 * i));
+                        }
                     }
                     if (S == 1) {
                         epi::fast_chunk<OUT, false>(va, c0, s_gs, s_sc, ws, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n,
@@ -441,12 +476,20 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     ptx::tc_fence_after();
 #pragma unroll 1
                     for (int c0 = 0; c0 < NT; c0 += 16) {
-                        uint32_t v[16];
-                        ptx::tmem_ld_32x32b_x16(ta0 + ab * NT + c0, v);
-                        epi::tmem_ld_wait_dep(v);
+                        int32_t acc[16];
+#pragma unroll
+                        for (int i = 0; i < 16; i++) acc[i] = 0;
+#pragma unroll
+                        for (int i = 0; i < ACCS; i++) {
+                            uint32_t v[16];
+                            ptx::tmem_ld_32x32b_x16(ta0 + (ab * ACCS + i) * NT + c0, v);
+                            epi::tmem_ld_wait_dep(v);
+#pragma unroll
+                            for (int j = 0; j < 16; j++) acc[j] += (int32_t) v[j] >> (2 * i);
+                        }
 #pragma unroll
                         for (int i = 0; i < 16; i++) {
-                            const int32_t x = wrap16((int32_t) v[i] - s_gs[c0 + i]);
+                            const int32_t x = wrap16(acc[i] - s_gs[c0 + i]);
                             int32_t *r = red + (c0 + i) * 128 + m;
                             *r = (gi == 0) ? x : *r + x;
                         }
@@ -518,7 +561,7 @@ constexpr int SMEM_BUDGET = 216 * 1024;
 
 template <int NT, int DT>
 static size_t smem_bytes(int nas, int asb) {
-    return (size_t) nas * asb * NT * 128 + (size_t) DT * 2 * DEC_THREADS * 16 + (size_t) NT * 512 + 1024;
+    return (size_t) nas * asb * NT * 128 + (size_t) DT * 4 * DEC_THREADS * 16 + (size_t) NT * 512 + 1024;
 }
 
 template <int NT, int OUT, int DT, bool DBG = false>
@@ -567,7 +610,7 @@ static cudaError_t launch_out(Params &p, cudaStream_t s) {
 template <int NT, int DT>
 static cudaError_t launch_one(Params &p, cudaStream_t s) {
     if (p.g.n_out == 0) {
-        if (DT == 4 && NT <= 32 && p.dbg) return launch_out<NT, 0, 4, true>(p, s);   // timeline build (VLUT_TC_DEBUG=1)
+        if (DT == 3 && NT <= 32 && p.dbg) return launch_out<NT, 0, 3, true>(p, s);   // timeline build (VLUT_TC_DEBUG=1)
         return launch_out<NT, 0, DT>(p, s);
     }
     return p.g.multicast ? launch_out<NT, 2, DT>(p, s) : launch_out<NT, 1, DT>(p, s);
@@ -619,11 +662,12 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.dbg_cta = tcs::env_int("VLUT_TCS_DBG_CTA", 0);
     p.dbg_mask = tcs::env_int("VLUT_TCS_DBG_MASK", 15);
     if (launches) *launches += 1;
-    const int deep = tcs::env_int("VLUT_TCS_DEPTH", 4);   // ring slots per decode thread: 16 KB per CTA each
+    // ring slots per decode thread: 4 phases x DT blocks = DT x 32 KB of packed weights in flight per CTA
+    const int deep = tcs::env_int("VLUT_TCS_DEPTH", 3);
     switch (NT) {
-        case 16: return deep >= 8 ? tcs::launch_one<16, 8>(p, s) : tcs::launch_one<16, 4>(p, s);
-        case 32: return deep >= 8 ? tcs::launch_one<32, 8>(p, s) : tcs::launch_one<32, 4>(p, s);
-        case 64: return tcs::launch_one<64, 4>(p, s);
+        case 16: return deep >= 4 ? tcs::launch_one<16, 4>(p, s) : deep <= 2 ? tcs::launch_one<16, 2>(p, s) : tcs::launch_one<16, 3>(p, s);
+        case 32: return deep <= 2 ? tcs::launch_one<32, 2>(p, s) : tcs::launch_one<32, 3>(p, s);
+        case 64: return deep <= 2 ? tcs::launch_one<64, 2>(p, s) : tcs::launch_one<64, 3>(p, s);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         *reinterpret_cast<uint32_t *>(a.q_rm + (int64_t) t * Kpad + k) = pk;
         // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
         const int64_t kb = k / BLOCK_K;
-        const int kk = (int) (k % BLOCK_K);
+        const int kk = act_row_pos((int) (k % BLOCK_K), a.perm);   // 4 consecutive k stay 4 consecutive bytes in both orders
         const int c = kk / 16;
         const int64_t off = (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 +
                             ((c ^ (t & 7)) << 4) + (kk & 15);
@@ -212,9 +212,17 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
             // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
             const int64_t kb = k / BLOCK_K;
             const int c = (int) (k % BLOCK_K) / 16;
-            const int64_t off =
-                (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 + ((c ^ (t & 7)) << 4);
-            *reinterpret_cast<uint4 *>(a.q_sw + off) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            int8_t *row = a.q_sw + (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128;
+            if (!a.perm) {
+                *reinterpret_cast<uint4 *>(row + ((c ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            } else {
+                // regrouped by bit-pair position: word pk[i] (k = 16c + 4i .. + 3) goes to byte i*32 + c*4 of the row
+#pragma unroll
+                for (int i = 0; i < 4; i++) {
+                    const int pos = i * 32 + c * 4;
+                    *reinterpret_cast<uint32_t *>(row + ((((pos >> 4) ^ (t & 7)) << 4) | (pos & 15))) = pk[i];
+                }
+            }
         }
         // the warp covers 512 consecutive k: at most two K-groups (512 or 640 k per group)
         const int gA = kw / gsize;
@@ -268,8 +276,17 @@ __global__ void relayout_kernel(ActView a) {
     const uint4 v = *reinterpret_cast<const uint4 *>(a.q_rm + t * a.Kpad + k);
     const int64_t kb = k / BLOCK_K;
     const int c = (int) (k % BLOCK_K) / 16;
-    const int64_t off = (((t / a.sw_tile) * (a.Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128 + ((c ^ (int) (t & 7)) << 4);
-    *reinterpret_cast<uint4 *>(a.q_sw + off) = v;
+    int8_t *row = a.q_sw + (((t / a.sw_tile) * (a.Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128;
+    if (!a.perm) {
+        *reinterpret_cast<uint4 *>(row + ((c ^ (int) (t & 7)) << 4)) = v;
+    } else {
+        const uint32_t pk[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const int pos = i * 32 + c * 4;
+            *reinterpret_cast<uint32_t *>(row + ((((pos >> 4) ^ (int) (t & 7)) << 4) | (pos & 15))) = pk[i];
+        }
+    }
 }
 
 cudaError_t launch_relayout(const ActView &a, cudaStream_t s) {

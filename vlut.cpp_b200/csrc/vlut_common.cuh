@@ -83,7 +83,17 @@ struct ActView {
     int64_t Kpad, Tpad;
     int G, gsize, NT;
     int sw_tile;  // tokens per swizzled tile of q_sw: NT, or NT / 2 for the CTA-pair kernel (each CTA stages one half tile)
+    // K order inside every 128-k sub-block row of q_sw.  0: natural.  1 (small-T kernel, mask-only weight unpack): the
+    // 128 bytes are regrouped by bit-pair position i of the packed weight words: byte i*32 + w*4 + b holds k = 16 w + 4 i + b
+    // (w = 0..7 the 16-k word group, b = 0..3), so that the 32 bytes of one K=32 MMA all pair with weight codes that sit
+    // at the same bit position (i) of their words -- the unpack is then a mask, the shift is folded into 4 accumulators.
+    int perm;
 };
+
+// byte position of k (0..127, inside a 128-k sub-block) in a q_sw row
+__host__ __device__ inline int act_row_pos(int k128, int perm) {
+    return perm ? ((k128 & 15) >> 2) * 32 + (k128 >> 4) * 4 + (k128 & 3) : k128;
+}
 
 struct GemmArgs {
     const uint8_t *w;  // T2
