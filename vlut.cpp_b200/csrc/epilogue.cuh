@@ -21,6 +21,14 @@ __device__ __forceinline__ void tmem_ld_wait_dep(uint32_t (&v)[16]) {
                    "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])::"memory");
 }
 
+// no instruction: registers loaded by an earlier tcgen05.ld become "defined" here, i.e. after the wait that precedes this
+// statement (volatile asm statements keep their order), so no consumer can be scheduled above that wait
+__device__ __forceinline__ void reg_fence(uint32_t (&v)[16]) {
+    asm volatile(""
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                   "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])::"memory");
+}
+
 // 16 final int32 sums of one weight row (tokens t .. t+15) -> fp32 outputs: out[(t+i) * ldo + n] = (float) x * s[t+i]
 // (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all).
 template <int OUT>

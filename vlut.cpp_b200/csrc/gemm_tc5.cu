@@ -105,7 +105,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     __shared__ __align__(16) int32_t s_gs[NT];
     __shared__ __align__(16) float s_sc[NT];
 
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // warp index through a shuffle: provably warp-uniform for the compiler, so the role loops keep their state (counters,
+    // barrier / TMEM addresses, descriptors) in uniform registers instead of converting per use (gemm_tcs.cu)
+    const int warp = __shfl_sync(0xffffffffu, (int) (threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int S = p.nstages;
     const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
     const uint32_t rank = ptx::cluster_ctarank();    // 0 = leader (issues the MMAs), 1 = peer

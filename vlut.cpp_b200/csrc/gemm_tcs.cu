@@ -444,19 +444,23 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
 #pragma unroll 1
                 for (int c0 = 0; c0 < NT; c0 += 16) {
-                    // sum over the issuers' accumulator sets; MASK: accumulator i holds 4^i x its share
+                    // sum over the issuers' accumulator sets; MASK: accumulator i holds 4^i x its share.  All loads of a
+                    // set are in flight before the one wait (8 dependent load round trips cost ~1000 clk of tail).
                     uint32_t va[16];
 #pragma unroll
                     for (int i = 0; i < 16; i++) va[i] = 0;
                     for (int set = 0; set < nsets; set++) {
+                        uint32_t v[ACCS][16];
 #pragma unroll
-                        for (int i = 0; i < ACCS; i++) {
-                            uint32_t v[16];
-                            if (!ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + (set * ACCS + i) * NT + c0, v);
-                            epi::tmem_ld_wait_dep(v);
+                        for (int i = 0; i < ACCS; i++)
+                            if (!ABL(4)) ptx::tmem_ld_32x32b_x16(ta0 + (set * ACCS + i) * NT + c0, v[i]);
+                        epi::tmem_ld_wait_dep(v[0]);
 #pragma unroll
-                            for (int j = 0; j < 16; j++) va[j] += (uint32_t) ((int32_t) v[j] >> (2 * i));
-                        }
+                        for (int i = 1; i < ACCS; i++) epi::reg_fence(v[i]);
+#pragma unroll
+                        for (int i = 0; i < ACCS; i++)
+#pragma unroll
+                            for (int j = 0; j < 16; j++) va[j] += (uint32_t) ((int32_t) v[i][j] >> (2 * i));
                     }
                     if (S == 1) {
                         epi::fast_chunk<OUT, false>(va, c0, s_gs, s_sc, ws, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n,
