@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
 // by a warp scan.  Launched with the programmatic-serialisation attribute: the CTA is resident and past its prologue when
 // the predecessor (the previous GEMM, which reads the workspace this kernel rewrites) drains; griddepcontrol.wait orders
 // every global access after it.
-__device__ __forceinline__ int quant1(float x, double is) {
+__device__ __forceinline__ int quant1_exact(float x, double is) {
     // clamp(round((double) x * is), -128, 127) with round = half away from zero, exactly: the clamp is applied first (it
     // commutes with rounding at integers), then truncation and an exact fractional test
     double p = (double) x * is;
@@ -136,6 +136,19 @@ __device__ __forceinline__ int quant1(float x, double is) {
     int ti = __double2int_rz(p);
     const double fr = p - (double) ti;
     ti += (fr >= 0.5) - (fr <= -0.5);
+    return max(-128, min(127, ti));
+}
+
+// Same value, fp32 first: pf = x * (float) is differs from the exact double product by at most |p| * 2^-23 <= 1.6e-5 inside
+// the clamp range, so whenever pf is further than 1e-4 from a rounding boundary (k + 0.5) both round the same way; the
+// few elements closer than that (about 1 in 5000) take the double path.  The FP64 pipe (conversions included) was ~2 us of
+// the kernel at T = 512.
+__device__ __forceinline__ int quant1(float x, double is, float isf) {
+    float pf = fminf(fmaxf(x * isf, -129.0f), 128.0f);
+    const float tr = truncf(pf);
+    const float fr = fabsf(pf - tr);   // exact
+    if (fabsf(fr - 0.5f) <= 1e-4f) return quant1_exact(x, is);
+    const int ti = (int) tr + ((fr > 0.5f) ? (pf < 0.0f ? -1 : 1) : 0);
     return max(-128, min(127, ti));
 }
 
@@ -180,6 +193,7 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
     if (!(dm > 1e-5)) dm = 1e-5;  // MAX(eps, .) with eps = 1e-5
     const double sd = dm / 127;
     const double is = 1e0 / (sd > 1e-5 ? sd : 1e-5);
+    const float isf = (float) is;
     if (tid == 0) a.scales[t] = live ? (float) sd : 0.0f;
 
     const int gsize = a.gsize;
@@ -192,8 +206,8 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
 #pragma unroll
         for (int i = 0; i < 4; i++) {
             if (live && k + 4 * i < K) {
-                const int q0 = quant1(v[j][i].x, is), q1 = quant1(v[j][i].y, is), q2 = quant1(v[j][i].z, is),
-                          q3 = quant1(v[j][i].w, is);
+                const int q0 = quant1(v[j][i].x, is, isf), q1 = quant1(v[j][i].y, is, isf), q2 = quant1(v[j][i].z, is, isf),
+                          q3 = quant1(v[j][i].w, is, isf);
                 pk[i] = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) |
                         ((uint32_t) (q3 & 0xff) << 24);
             } else {
@@ -314,7 +328,10 @@ cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, c
     if (a.G > 64) return cudaErrorInvalidValue;
     const char *e2 = getenv("VLUT_QUANT_2PASS"), *ep = getenv("VLUT_PDL");
     const bool two_pass = e2 && atoi(e2) != 0;
-    const bool pdl = ep ? atoi(ep) != 0 : true;
+    // programmatic launch of the quantiser itself (behind the previous GEMM): measured on the quantise + GEMM chain at
+    // 4096 -> 14336 it gains 0.1-0.5 us for T <= 64 and from T = 1024 up, and loses 1.6-2 us in between (scripts/time_op.py)
+    const char *eq = getenv("VLUT_QUANT_PDL");
+    const bool pdl = (ep ? atoi(ep) != 0 : true) && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512));
     const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
     if (!two_pass && aligned && a.Kpad <= 16384) {
         if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl);
