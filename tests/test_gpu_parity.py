@@ -229,6 +229,26 @@ def test_mul_mat_host_buffers(ctx, orc):
     assert np.array_equal(bits(oh.numpy()), bits(orc.mul_mat(type_, packed, x, N)))
 
 
+@pytest.mark.parametrize("T", [129, 300, 512])
+def test_mul_mat_host_pipeline_chunks(ctx, orc, T):
+    """T > 128 takes the chunked H2D / compute / D2H pipeline of vlut_mul_mat_host (ragged last chunk, strided host
+    rows, pageable and pinned memory, back-to-back calls reusing the staging buffers)."""
+    type_, K, N = O.I2_V_4, 2048, 384
+    w = O.make_ternary(N, K, seed=3)
+    packed = orc.pack(type_, w)
+    W = ctx.upload(type_, K, N, packed)
+    for rep, pinned in enumerate([True, False, True]):
+        x = O.make_acts(T, K, seed=10 + rep, kind="outlier" if rep == 1 else "normal")
+        xh = torch.zeros((T, K + 16), dtype=torch.float32)
+        oh = torch.full((T, N + 8), -3.0, dtype=torch.float32)
+        if pinned:
+            xh, oh = xh.pin_memory(), oh.pin_memory()
+        xh[:, :K] = torch.from_numpy(x)
+        ctx.mul_mat_host(W, xh[:, :K], oh[:, :N])
+        assert np.array_equal(bits(oh[:, :N].numpy()), bits(orc.mul_mat(type_, packed, x, N)))
+        assert (oh[:, N:] == -3.0).all()
+
+
 def test_strided_output_and_errors(ctx, orc):
     a = api()
     type_, K, N, T = O.I1_V_2, 1280, 100, 5

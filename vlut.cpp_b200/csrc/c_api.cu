@@ -6,7 +6,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <algorithm>
 #include <new>
+#include <vector>
 
 #include "vlut_common.cuh"
 
@@ -60,6 +62,9 @@ struct vlut_ctx {
     int64_t launches = 0;
     int last_algo = 0;
     uint32_t epoch = 0;  // quantisation call counter (ActView.epoch)
+    // vlut_mul_mat_host pipeline: one copy stream per PCIe direction and one event pair per token chunk
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    std::vector<cudaEvent_t> ev_in, ev_done;
 };
 
 extern "C" {
@@ -151,6 +156,10 @@ void vlut_ctx_destroy(vlut_ctx *c) {
     DevBuf *bufs[] = {&c->q_rm, &c->q_sw,     &c->scales,  &c->gpre,      &c->nowrap, &c->tile_unsafe,
                       &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
     for (DevBuf *b : bufs) b->release();
+    for (cudaEvent_t e : c->ev_in) cudaEventDestroy(e);
+    for (cudaEvent_t e : c->ev_done) cudaEventDestroy(e);
+    if (c->h2d_stream) cudaStreamDestroy(c->h2d_stream);
+    if (c->d2h_stream) cudaStreamDestroy(c->d2h_stream);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
 }
@@ -468,6 +477,24 @@ int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const v
     return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
 }
 
+// rows x width bytes between host and device; contiguous on both sides -> one 1-D copy (the 2-D path is slower per byte)
+static cudaError_t copy_rows(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t rows,
+                             cudaMemcpyKind kind, cudaStream_t st) {
+    if (dpitch == width && spitch == width) return cudaMemcpyAsync(dst, src, width * rows, kind, st);
+    return cudaMemcpy2DAsync(dst, dpitch, src, spitch, width, rows, kind, st);
+}
+
+// Token chunk of the host-buffer pipeline.  Quantisation is per token, so cutting T is exact; 128 tokens is one TCP token
+// tile (GEMM ~11 us) against ~130 us of D2H for the chunk's 7.3 MB of f32 results at 4096->14336.
+static int host_chunk_tokens() {
+    static const int v = [] {
+        const char *e = getenv("VLUT_HOST_CHUNK");
+        const int n = e ? atoi(e) : 128;
+        return n < 0 ? 0 : n;
+    }();
+    return v;
+}
+
 int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_host,
                       int64_t ldx, float *out_host, int64_t ldo, float w_scale, int algo) {
     if (!c || !x_host || !out_host || T <= 0 || ldx < K || ldo < N) return VLUT_ERR_INVALID;
@@ -476,12 +503,56 @@ int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, co
     CK(cudaSetDevice(c->device));
     if (c->stage_x.reserve((size_t) (T * K) * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->stage_out.reserve((size_t) (T * N) * sizeof(float)) != cudaSuccess) return VLUT_ERR_NOMEM;
-    CK(cudaMemcpy2DAsync(c->stage_x.p, (size_t) K * 4, x_host, (size_t) ldx * 4, (size_t) K * 4, (size_t) T,
-                         cudaMemcpyHostToDevice, c->stream));
-    rc = vlut_mul_mat(c, type, K, N, T, t2_dev, (const float *) c->stage_x.p, K, (float *) c->stage_out.p, N, w_scale, algo);
-    if (rc) return rc;
-    CK(cudaMemcpy2DAsync(out_host, (size_t) ldo * 4, c->stage_out.p, (size_t) N * 4, (size_t) N * 4, (size_t) T,
-                         cudaMemcpyDeviceToHost, c->stream));
+    float *sx = (float *) c->stage_x.p, *so = (float *) c->stage_out.p;
+    const int64_t chunk = host_chunk_tokens();
+    if (chunk == 0 || T <= chunk) {
+        CK(copy_rows(sx, (size_t) K * 4, x_host, (size_t) ldx * 4, (size_t) K * 4, (size_t) T, cudaMemcpyHostToDevice,
+                             c->stream));
+        rc = vlut_mul_mat(c, type, K, N, T, t2_dev, sx, K, so, N, w_scale, algo);
+        if (rc) return rc;
+        CK(copy_rows(out_host, (size_t) ldo * 4, so, (size_t) N * 4, (size_t) N * 4, (size_t) T, cudaMemcpyDeviceToHost,
+                             c->stream));
+        CK(cudaStreamSynchronize(c->stream));
+        return VLUT_OK;
+    }
+    // Three-stage pipeline over token chunks: H2D of chunk i+1 and D2H of chunk i-1 (PCIe is full duplex: one copy
+    // stream per direction) run under the quantise + GEMM of chunk i on the context's stream.  The result copy is the
+    // long pole (4TN bytes against 4TK in), so the op costs ~ D2H(out) + one chunk of H2D + one chunk of compute.
+    if (!c->h2d_stream) CK(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
+    if (!c->d2h_stream) CK(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
+    const int64_t nchunk = (T + chunk - 1) / chunk;
+    while ((int64_t) c->ev_in.size() < nchunk) {
+        cudaEvent_t a, b;
+        CK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&b, cudaEventDisableTiming));
+        c->ev_in.push_back(a);
+        c->ev_done.push_back(b);
+    }
+    // the staging buffers may still be read/written by earlier work queued on the context's stream
+    CK(cudaEventRecord(c->ev_done[0], c->stream));
+    CK(cudaStreamWaitEvent(c->h2d_stream, c->ev_done[0], 0));
+    for (int64_t i = 0; i < nchunk; i++) {
+        const int64_t t0 = i * chunk, tn = std::min(chunk, T - t0);
+        CK(copy_rows(sx + t0 * K, (size_t) K * 4, x_host + t0 * ldx, (size_t) ldx * 4, (size_t) K * 4, (size_t) tn,
+                             cudaMemcpyHostToDevice, c->h2d_stream));
+        CK(cudaEventRecord(c->ev_in[i], c->h2d_stream));
+    }
+    for (int64_t i = 0; i < nchunk; i++) {
+        const int64_t t0 = i * chunk, tn = std::min(chunk, T - t0);
+        CK(cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
+        rc = vlut_mul_mat(c, type, K, N, tn, t2_dev, sx + t0 * K, K, so + t0 * N, N, w_scale, algo);
+        if (rc) {
+            cudaStreamSynchronize(c->h2d_stream);
+            cudaStreamSynchronize(c->stream);
+            cudaStreamSynchronize(c->d2h_stream);
+            return rc;
+        }
+        CK(cudaEventRecord(c->ev_done[i], c->stream));
+        CK(cudaStreamWaitEvent(c->d2h_stream, c->ev_done[i], 0));
+        CK(copy_rows(out_host + t0 * ldo, (size_t) ldo * 4, so + t0 * N, (size_t) N * 4, (size_t) N * 4, (size_t) tn,
+                             cudaMemcpyDeviceToHost, c->d2h_stream));
+    }
+    CK(cudaStreamSynchronize(c->d2h_stream));
     CK(cudaStreamSynchronize(c->stream));
     return VLUT_OK;
 }
