@@ -111,6 +111,12 @@ int vlut_gemm(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const vo
 /* the whole op on device buffers = GGML_OP_MUL_MAT(vlut weight, f32) of ggml-cpu.c:1372-1421 */
 int vlut_mul_mat(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                  int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo);
+/* out[t][n] = x[t][n] * scale on device buffers (in place allowed): GGML_OP_MUL by a one-element f32 tensor -- the
+ * `.scale` of a ternary weight (src/models/bitnet.cpp:33-34, src/llama-graph.cpp:780-783; CPU:
+ * ggml_compute_forward_mul, ggml/src/ggml-cpu/binary-ops.cpp:152) -- for the cases where the plugin cannot fold it
+ * into the preceding GEMM's epilogue through w_scale (the product has other consumers, or is not adjacent). */
+int vlut_scale_rows(vlut_ctx *ctx, const float *x_dev, int64_t ldx, float *out_dev, int64_t ldo, int64_t N, int64_t T,
+                    float scale);
 /* Multi-GPU, row-sharded weights (output-row tensor parallelism: the thread split of ggml-cpu.c:1413-1418 across
  * GPUs): this rank's [K x N] shard produces columns [col0, col0+N) of the [T][N_total] result.  The GEMM epilogue
  * itself performs the all-gather: it stores every element into each rank's result buffer, either through n_out peer

@@ -8,6 +8,11 @@
 //     mode "sched" : weight in the plugin's buffer, activations and result on the CPU backend; ggml_backend_sched
 //                    splits the graph (MUL_MAT -> plugin, following ADD -> CPU) and copies across the boundary, like
 //                    llama_decode does (ggml/src/ggml-backend.cpp:1443-1460)
+//     mode "block" : like "sched", with the weight's per-tensor scales ({1} f32 tensors, as `.scale` in
+//                    src/models/bitnet.cpp:33-34) in the plugin's buffer too.  One input feeds four MUL_MATs:
+//                    q = mul(mul_mat(a,b), sa); k = mul(mul_mat(a,b), sb); v = mul_mat(a,b);
+//                    g = mul_mat(a,b) with two consumers: r1 = mul(g, sa), r2 = g + 1 (CPU).
+//                    out.bin = q,k,v,r1,r2 (5 x [T][N]); prints the plugin's fusion counters.
 // w.bin = GGUF-packed weight bytes, x.bin = f32 [T][K]; out.bin = f32 [T][N] (sched mode: mul_mat result + 1.0).
 #include <cstdio>
 #include <cstdlib>
@@ -109,6 +114,62 @@ int main(int argc, char **argv) {
         printf("sched: %d splits, mul_mat ran on '%s'\n", ggml_backend_sched_get_n_splits(sched),
                ggml_backend_name(ggml_backend_sched_get_tensor_backend(sched, c)));
         ggml_backend_tensor_get(d, out.data(), 0, out.size() * sizeof(float));
+        ggml_backend_sched_free(sched);
+        ggml_backend_buffer_free(wbuf);
+        ggml_free(gctx);
+        ggml_free(wctx);
+        ggml_backend_free(cpu);
+    } else if (mode == "block") {
+        if (argc < 11) { fprintf(stderr, "block mode needs the CPU backend library\n"); return 2; }
+        ggml_backend_reg_t cpu_reg = ggml_backend_load(argv[10]);
+        if (!cpu_reg) { fprintf(stderr, "loading CPU backend failed\n"); return 3; }
+        ggml_backend_t cpu = ggml_backend_dev_init(ggml_backend_reg_dev_get(cpu_reg, 0), nullptr);
+        ggml_init_params ipb = {ggml_tensor_overhead() * 64 + ggml_graph_overhead(), nullptr, true};
+        ggml_context *wctx = ggml_init(ipb);
+        ggml_tensor *a = ggml_new_tensor_2d(wctx, type, K, N);
+        ggml_tensor *sa = ggml_new_tensor_1d(wctx, GGML_TYPE_F32, 1);
+        ggml_tensor *sb = ggml_new_tensor_1d(wctx, GGML_TYPE_F32, 1);
+        ggml_backend_buffer_t wbuf = ggml_backend_alloc_ctx_tensors_from_buft(wctx, buft);
+        if (!wbuf) { fprintf(stderr, "weight alloc failed\n"); return 5; }
+        ggml_backend_buffer_set_usage(wbuf, GGML_BACKEND_BUFFER_USAGE_WEIGHTS);
+        const float sav = 0.37f, sbv = -1.9f, onev = 1.0f;
+        ggml_backend_tensor_set(a, w.data(), 0, w.size());
+        ggml_backend_tensor_set(sa, &sav, 0, sizeof(float));
+        ggml_backend_tensor_set(sb, &sbv, 0, sizeof(float));
+        ggml_context *gctx = ggml_init(ipb);
+        ggml_tensor *b = ggml_new_tensor_2d(gctx, GGML_TYPE_F32, K, T);
+        ggml_set_input(b);
+        ggml_tensor *one = ggml_new_tensor_1d(gctx, GGML_TYPE_F32, 1);
+        ggml_set_input(one);
+        ggml_tensor *q = ggml_mul(gctx, ggml_mul_mat(gctx, a, b), sa);
+        ggml_tensor *k = ggml_mul(gctx, ggml_mul_mat(gctx, a, b), sb);
+        ggml_tensor *v = ggml_mul_mat(gctx, a, b);
+        ggml_tensor *g = ggml_mul_mat(gctx, a, b);
+        ggml_tensor *r1 = ggml_mul(gctx, g, sa);
+        ggml_tensor *r2 = ggml_add(gctx, g, one);
+        ggml_tensor *outs[5] = {q, k, v, r1, r2};
+        ggml_cgraph *gf = ggml_new_graph(gctx);
+        for (ggml_tensor *o : outs) { ggml_set_output(o); ggml_build_forward_expand(gf, o); }
+        ggml_backend_t backends[2] = {backend, cpu};
+        ggml_backend_sched_t sched = ggml_backend_sched_new(backends, nullptr, 2, 64, false, true);
+        if (!ggml_backend_sched_alloc_graph(sched, gf)) { fprintf(stderr, "sched alloc failed\n"); return 5; }
+        ggml_backend_tensor_set(b, x.data(), 0, x.size());
+        ggml_backend_tensor_set(one, &onev, 0, sizeof(float));
+        const ggml_status st = ggml_backend_sched_graph_compute(sched, gf);
+        if (st != GGML_STATUS_SUCCESS) { fprintf(stderr, "sched compute status %d\n", (int) st); return 6; }
+        printf("block: %d splits, scaled product ran on '%s'\n", ggml_backend_sched_get_n_splits(sched),
+               ggml_backend_name(ggml_backend_sched_get_tensor_backend(sched, q)));
+        typedef void (*stats_fn)(ggml_backend_t, int64_t *);
+        stats_fn stats = (stats_fn) ggml_backend_reg_get_proc_address(reg, "vlut_b200_backend_stats");
+        if (stats) {
+            int64_t s4[4];
+            stats(backend, s4);
+            printf("stats: gemm=%lld quantize=%lld fused_scale=%lld scale_rows=%lld\n", (long long) s4[0], (long long) s4[1],
+                   (long long) s4[2], (long long) s4[3]);
+        }
+        out.resize((size_t) 5 * T * N);
+        for (int i = 0; i < 5; i++)
+            ggml_backend_tensor_get(outs[i], out.data() + (size_t) i * T * N, 0, (size_t) T * N * sizeof(float));
         ggml_backend_sched_free(sched);
         ggml_backend_buffer_free(wbuf);
         ggml_free(gctx);

@@ -31,14 +31,15 @@ def bits(a):
     return np.ascontiguousarray(a).view(np.uint32)
 
 
-def run_harness(tmp_path, mode, type_, K, N, T, packed, x):
+def run_harness(tmp_path, mode, type_, K, N, T, packed, x, env=None):
     (tmp_path / "w.bin").write_bytes(packed.tobytes())
     (tmp_path / "x.bin").write_bytes(np.ascontiguousarray(x, dtype=np.float32).tobytes())
     cmd = [str(HARNESS), str(PLUGIN), mode, str(type_), str(K), str(N), str(T), str(tmp_path / "w.bin"), str(tmp_path / "x.bin"),
            str(tmp_path / "out.bin")]
-    if mode == "sched":
+    if mode in ("sched", "block"):
         cmd.append(str(CPU_BACKEND))
-    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120)
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=120,
+                       env={**os.environ, **(env or {})})
     return r
 
 
@@ -97,3 +98,26 @@ def test_mul_mat_through_ggml_sched(tmp_path, orc, type_, K, N, T):
     out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(T, N)
     expect = orc.mul_mat(type_, packed, x, N) + np.float32(1.0)
     assert np.array_equal(bits(out), bits(expect))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fuse", [True, False], ids=["fused", "VLUT_B200_NO_FUSE"])
+@pytest.mark.parametrize("type_,K,N,T", [(O.I2_V_4, 4096, 512, 16), (O.I1_V_2, 3200, 384, 40), (O.I2_V_4, 2048, 1024, 200)])
+def test_scale_fusion_and_shared_activations(tmp_path, orc, type_, K, N, T, fuse):
+    """SURVEY 8f N1 + N3: the `.scale` MUL that follows a ternary MUL_MAT (src/models/bitnet.cpp:33-34) is folded into
+    the GEMM epilogue when the product has one consumer, runs as a stand-alone kernel otherwise, and four MUL_MATs on
+    one input quantise it once.  Bits must equal MUL_MAT (oracle) followed by an fp32 multiply, fused or not."""
+    need_artifacts()
+    w = O.make_ternary(N, K, seed=K + T)
+    x = O.make_acts(T, K, seed=N, kind="outlier")
+    packed = orc.pack(type_, w)
+    r = run_harness(tmp_path, "block", type_, K, N, T, packed, x, env=None if fuse else {"VLUT_B200_NO_FUSE": "1"})
+    assert r.returncode == 0, r.stdout
+    assert "scaled product ran on 'VLUT_B200_0'" in r.stdout, r.stdout
+    out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(5, T, N)
+    base = orc.mul_mat(type_, packed, x, N)
+    expect = [base * np.float32(0.37), base * np.float32(-1.9), base, base * np.float32(0.37), base + np.float32(1.0)]
+    for i, e in enumerate(expect):
+        assert np.array_equal(bits(out[i]), bits(e)), f"output {i} differs"
+    want = "gemm=4 quantize=1 fused_scale=2 scale_rows=1" if fuse else "gemm=4 quantize=1 fused_scale=0 scale_rows=3"
+    assert want in r.stdout, r.stdout

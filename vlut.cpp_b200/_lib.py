@@ -48,6 +48,7 @@ _SIGNATURES = {
     "vlut_mul_mat": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_mul_mat_scatter": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, cint, cint, i64, f32, cint]),
     "vlut_mul_mat_host": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
+    "vlut_scale_rows": (cint, [vp, vp, i64, vp, i64, i64, i64, f32]),
     "vlut_pick_algo": (cint, [cint, i64, i64, i64]),
     "vlut_debug_get_act": (cint, [vp, i64, i64, vp, vp]),
     "vlut_debug_unpack_t2": (cint, [vp, cint, i64, i64, vp, vp]),

@@ -477,6 +477,16 @@ int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const v
     return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
 }
 
+int vlut_scale_rows(vlut_ctx *c, const float *x_dev, int64_t ldx, float *out_dev, int64_t ldo, int64_t N, int64_t T,
+                    float scale) {
+    if (!c || !x_dev || !out_dev || N <= 0 || T <= 0 || ldx < N || ldo < N) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    cudaError_t e = launch_scale_rows(x_dev, ldx, out_dev, ldo, N, T, scale, c->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "scale_rows launch");
+    c->launches += (T + 65534) / 65535;
+    return VLUT_OK;
+}
+
 // rows x width bytes between host and device; contiguous on both sides -> one 1-D copy (the 2-D path is slower per byte)
 static cudaError_t copy_rows(void *dst, size_t dpitch, const void *src, size_t spitch, size_t width, size_t rows,
                              cudaMemcpyKind kind, cudaStream_t st) {

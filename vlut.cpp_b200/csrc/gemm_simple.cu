@@ -43,4 +43,24 @@ cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// out[t][n] = x[t][n] * s: GGML_OP_MUL by a one-element f32 tensor (the `.scale` of a ternary weight,
+// src/models/bitnet.cpp:33-34; ggml_compute_forward_mul, ggml-cpu/binary-ops.cpp:152) when it could not be folded
+// into the GEMM epilogue.  One fp32 rounding, as on the CPU.
+__global__ void __launch_bounds__(256) scale_rows_kernel(const float *__restrict__ x, int64_t ldx, float *__restrict__ out,
+                                                         int64_t ldo, int64_t N, int64_t T, float s) {
+    const int64_t t = blockIdx.y;
+    for (int64_t n = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t) gridDim.x * blockDim.x)
+        out[t * ldo + n] = x[t * ldx + n] * s;
+}
+
+cudaError_t launch_scale_rows(const float *x, int64_t ldx, float *out, int64_t ldo, int64_t N, int64_t T, float sc,
+                              cudaStream_t s) {
+    for (int64_t t0 = 0; t0 < T; t0 += 65535) {
+        const int64_t tn = T - t0 < 65535 ? T - t0 : 65535;
+        dim3 grid((unsigned) (ceil_div(N, 256) < 64 ? ceil_div(N, 256) : 64), (unsigned) tn);
+        scale_rows_kernel<<<grid, 256, 0, s>>>(x + t0 * ldx, ldx, out + t0 * ldo, ldo, N, tn, sc);
+    }
+    return cudaGetLastError();
+}
+
 }  // namespace vlut

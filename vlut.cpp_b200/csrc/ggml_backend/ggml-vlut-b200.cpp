@@ -19,6 +19,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "ggml-backend-impl.h"
@@ -50,13 +51,54 @@ struct device_ctx {
 struct buffer_ctx {
     device_ctx *dev = nullptr;
     void *base = nullptr;
+    // host copies of one-element f32 tensors written through set_tensor (the `.scale` of a ternary weight): the
+    // GEMM epilogue takes the scale by value, so graph_compute needs no device read-back.  Guarded by dev->io_mutex.
+    std::unordered_map<const void *, float> scalars;
+};
+
+// call with dev->io_mutex held: bytes [lo, hi) of the buffer are being rewritten
+void forget_scalars(buffer_ctx *bc, const void *lo_, size_t n) {
+    const char *lo = (const char *) lo_, *hi = lo + n;
+    for (auto it = bc->scalars.begin(); it != bc->scalars.end();) {
+        const char *p = (const char *) it->first;
+        it = (p >= lo && p < hi) ? bc->scalars.erase(it) : std::next(it);
+    }
+}
+
+// The activations last quantised into the backend's workspace: consecutive MUL_MATs that share src1 (Q/K/V on one
+// attention input, up/gate on one FFN input) quantise once.  Valid inside one graph_compute call only.
+struct act_cache {
+    const ggml_tensor *src1 = nullptr;
+    const char *lo = nullptr, *hi = nullptr;  // byte range of the slice that was quantised
+    int64_t K = 0, T = 0;
+    bool i1_family = false;  // K-group 640 (I1*) vs 512 (I2*)
 };
 
 struct backend_ctx {
     device_ctx *dev = nullptr;
     vlut_ctx *ctx = nullptr;
     std::string name;
+    act_cache act;
+    // counters behind the "vlut_b200_backend_stats" proc address (tests)
+    int64_t n_mul_mat = 0, n_quantize = 0, n_fused_scale = 0, n_scale_rows = 0;
 };
+
+bool is_i1_family(enum ggml_type t) { return t == GGML_TYPE_I1_V || t == GGML_TYPE_I1_V_2; }
+
+// GGML_OP_MUL of an f32 matrix by a one-element f32 tensor in our buffer type: the per-tensor `.scale` that follows a
+// ternary MUL_MAT (src/models/bitnet.cpp:33-34, src/llama-graph.cpp:780-783).  Returns the scalar operand's index.
+int scalar_mul_operand(const ggml_tensor *op) {
+    if (op->op != GGML_OP_MUL || op->type != GGML_TYPE_F32) return -1;
+    for (int j = 1; j >= 0; j--) {
+        const ggml_tensor *s = op->src[j], *x = op->src[1 - j];
+        if (!s || !x) continue;
+        if (s->type != GGML_TYPE_F32 || ggml_nelements(s) != 1) continue;
+        if (x->type != GGML_TYPE_F32 || !ggml_are_same_shape(x, op)) continue;
+        if (x->nb[0] != sizeof(float) || op->nb[0] != sizeof(float)) continue;
+        return j;
+    }
+    return -1;
+}
 
 vlut_ctx *io_ctx(device_ctx *d) {
     if (!d->io_ctx) {
@@ -82,6 +124,7 @@ void *buffer_get_base(ggml_backend_buffer_t buffer) { return ((buffer_ctx *) buf
 void buffer_memset_tensor(ggml_backend_buffer_t buffer, ggml_tensor *tensor, uint8_t value, size_t offset, size_t size) {
     buffer_ctx *b = (buffer_ctx *) buffer->context;
     std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    forget_scalars(b, (char *) tensor->data + offset, size);
     vlut_dev_memset(io_ctx(b->dev), (char *) tensor->data + offset, value, size);
 }
 
@@ -94,12 +137,20 @@ void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor *tensor, const 
     if (is_vlut_type(tensor->type)) {
         GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "vlut weights must be uploaded whole (they are repacked)");
         GGML_ASSERT(ggml_n_dims(tensor) <= 2);
+        forget_scalars(b, tensor->data, vlut_repacked_nbytes((int) tensor->type, tensor->ne[0], tensor->ne[1]));
         const int rc = vlut_upload_weights(c, (int) tensor->type, tensor->ne[0], tensor->ne[1], data, tensor->data);
         if (rc != VLUT_OK) GGML_ABORT("vlut_upload_weights failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
         return;
     }
     const int rc = vlut_dev_memcpy_h2d(c, (char *) tensor->data + offset, data, size);
     if (rc != VLUT_OK) GGML_ABORT("H2D copy failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
+    if (tensor->type == GGML_TYPE_F32 && ggml_nelements(tensor) == 1 && offset == 0 && size == sizeof(float)) {
+        float v;
+        memcpy(&v, data, sizeof(float));
+        b->scalars[tensor->data] = v;
+    } else {
+        forget_scalars(b, (char *) tensor->data + offset, size);
+    }
 }
 
 void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor *tensor, void *data, size_t offset, size_t size) {
@@ -113,6 +164,7 @@ void buffer_get_tensor(ggml_backend_buffer_t buffer, const ggml_tensor *tensor, 
 void buffer_clear(ggml_backend_buffer_t buffer, uint8_t value) {
     buffer_ctx *b = (buffer_ctx *) buffer->context;
     std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    b->scalars.clear();
     vlut_dev_memset(io_ctx(b->dev), b->base, value, buffer->size);
 }
 
@@ -183,37 +235,134 @@ void backend_free(ggml_backend_t backend) {
 
 void backend_synchronize(ggml_backend_t backend) { vlut_ctx_sync(((backend_ctx *) backend->context)->ctx); }
 
+// value of a one-element f32 tensor living in one of our buffers: the host copy kept by set_tensor, else one 4-byte
+// read-back (after which it is cached too)
+bool scalar_value(backend_ctx *b, const ggml_tensor *s, float *out) {
+    const ggml_tensor *base = s->view_src ? s->view_src : s;
+    if (!base->buffer || base->buffer->buft != &b->dev->buft) return false;
+    buffer_ctx *bc = (buffer_ctx *) base->buffer->context;
+    std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+    auto it = bc->scalars.find(s->data);
+    if (it != bc->scalars.end()) {
+        *out = it->second;
+        return true;
+    }
+    if (vlut_ctx_sync(b->ctx) != VLUT_OK) return false;  // the scalar may have been produced on our stream
+    if (vlut_dev_memcpy_d2h(io_ctx(b->dev), out, s->data, sizeof(float)) != VLUT_OK) return false;
+    bc->scalars[s->data] = *out;
+    return true;
+}
+
+// a node of ours is about to write [lo, hi): forget cached state that lives there
+void note_write(backend_ctx *b, const ggml_tensor *dst) {
+    const char *lo = (const char *) dst->data, *hi = lo + ggml_nbytes(dst);
+    if (b->act.src1 && lo < b->act.hi && b->act.lo < hi) b->act = act_cache{};
+    const ggml_tensor *base = dst->view_src ? dst->view_src : dst;
+    if (base->buffer && base->buffer->buft == &b->dev->buft) {
+        buffer_ctx *bc = (buffer_ctx *) base->buffer->context;
+        std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+        forget_scalars(bc, lo, (size_t) (hi - lo));
+    }
+}
+
 // GGML_OP_MUL_MAT(vlut weight [K,N], f32 [K,T,...]) -> f32 [N,T,...]: the Vec-LUT branch of
 // ggml_compute_forward_mul_mat (ggml-cpu.c:1372-1421): quantise activations per token, Vec-LUT GEMM, fp32 epilogue.
-ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst) {
+// `out_t` is where the result goes (the MUL_MAT node itself, or the trailing MUL node when its scale is folded into
+// the epilogue as w_scale: ((float) acc * s_t) * w_scale, the same two roundings as MUL_MAT followed by MUL).
+ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst, const ggml_tensor *out_t, float w_scale) {
     const ggml_tensor *src0 = dst->src[0];
     const ggml_tensor *src1 = dst->src[1];
     const int64_t K = src0->ne[0], N = src0->ne[1], T = src1->ne[1];
     GGML_ASSERT(src1->ne[0] == K && dst->ne[0] == N && dst->ne[1] == T);
-    GGML_ASSERT(src1->nb[0] == sizeof(float) && dst->nb[0] == sizeof(float));
+    GGML_ASSERT(src1->nb[0] == sizeof(float) && out_t->nb[0] == sizeof(float));
+    const bool batched = src1->ne[2] * src1->ne[3] > 1;
     for (int64_t i3 = 0; i3 < src1->ne[3]; i3++) {
         for (int64_t i2 = 0; i2 < src1->ne[2]; i2++) {
             const float *x = (const float *) ((const char *) src1->data + i2 * src1->nb[2] + i3 * src1->nb[3]);
-            float *out = (float *) ((char *) dst->data + i2 * dst->nb[2] + i3 * dst->nb[3]);
-            const int rc = vlut_mul_mat(b->ctx, (int) src0->type, K, N, T, src0->data, x, (int64_t) (src1->nb[1] / sizeof(float)),
-                                        out, (int64_t) (dst->nb[1] / sizeof(float)), 1.0f, VLUT_ALGO_AUTO);
+            float *out = (float *) ((char *) out_t->data + i2 * out_t->nb[2] + i3 * out_t->nb[3]);
+            const int64_t ldx = (int64_t) (src1->nb[1] / sizeof(float)), ldo = (int64_t) (out_t->nb[1] / sizeof(float));
+            int rc = VLUT_OK;
+            const bool reuse = !batched && b->act.src1 == src1 && b->act.K == K && b->act.T == T &&
+                               b->act.i1_family == is_i1_family(src0->type);
+            if (!reuse) {
+                rc = vlut_quantize_act(b->ctx, (int) src0->type, x, ldx, K, T);
+                b->n_quantize++;
+                b->act = act_cache{};
+                if (rc == VLUT_OK && !batched) {
+                    b->act.src1 = src1;
+                    b->act.lo = (const char *) x;
+                    b->act.hi = (const char *) x + (size_t) (T - 1) * src1->nb[1] + (size_t) K * sizeof(float);
+                    b->act.K = K;
+                    b->act.T = T;
+                    b->act.i1_family = is_i1_family(src0->type);
+                }
+            }
+            if (rc == VLUT_OK) rc = vlut_gemm(b->ctx, (int) src0->type, K, N, T, src0->data, out, ldo, w_scale, VLUT_ALGO_AUTO);
             if (rc != VLUT_OK) {
+                b->act = act_cache{};
                 GGML_LOG_ERROR("%s: vlut_mul_mat(%s) failed: %s (%s)\n", __func__, dst->name, vlut_error_string(rc),
                                vlut_last_cuda_error());
                 return rc == VLUT_ERR_NOMEM ? GGML_STATUS_ALLOC_FAILED : GGML_STATUS_FAILED;
             }
+            b->n_mul_mat++;
         }
     }
+    note_write(b, out_t);
+    return GGML_STATUS_SUCCESS;
+}
+
+// stand-alone MUL by a one-element tensor (the product had other consumers, or did not directly follow its MUL_MAT)
+ggml_status compute_scalar_mul(backend_ctx *b, const ggml_tensor *dst) {
+    const int j = scalar_mul_operand(dst);
+    GGML_ASSERT(j >= 0);
+    const ggml_tensor *x = dst->src[1 - j];
+    float sc = 1.0f;
+    if (!scalar_value(b, dst->src[j], &sc)) return GGML_STATUS_FAILED;
+    for (int64_t i3 = 0; i3 < dst->ne[3]; i3++) {
+        for (int64_t i2 = 0; i2 < dst->ne[2]; i2++) {
+            const float *xi = (const float *) ((const char *) x->data + i2 * x->nb[2] + i3 * x->nb[3]);
+            float *oi = (float *) ((char *) dst->data + i2 * dst->nb[2] + i3 * dst->nb[3]);
+            const int rc = vlut_scale_rows(b->ctx, xi, (int64_t) (x->nb[1] / sizeof(float)), oi,
+                                           (int64_t) (dst->nb[1] / sizeof(float)), dst->ne[0], dst->ne[1], sc);
+            if (rc != VLUT_OK) {
+                GGML_LOG_ERROR("%s: vlut_scale_rows(%s) failed: %s\n", __func__, dst->name, vlut_error_string(rc));
+                return GGML_STATUS_FAILED;
+            }
+        }
+    }
+    b->n_scale_rows++;
+    note_write(b, dst);
     return GGML_STATUS_SUCCESS;
 }
 
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
     backend_ctx *b = (backend_ctx *) backend->context;
+    static const bool no_fuse = getenv("VLUT_B200_NO_FUSE") != nullptr;
+    b->act = act_cache{};  // inputs may have been rewritten since the last graph
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor *node = cgraph->nodes[i];
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
-                const ggml_status st = compute_mul_mat(b, node);
+                // look ahead: MUL_MAT -> MUL by the weight's {1} scale folds into the epilogue (same-shape, single
+                // use, not a graph output: ggml_can_fuse, ggml-impl.h:604-643)
+                static const enum ggml_op fuse_ops[2] = {GGML_OP_MUL_MAT, GGML_OP_MUL};
+                float sc = 1.0f;
+                if (!no_fuse && ggml_can_fuse(cgraph, i, fuse_ops, 2)) {
+                    const ggml_tensor *mul = cgraph->nodes[i + 1];
+                    const int j = scalar_mul_operand(mul);
+                    if (j >= 0 && mul->src[1 - j] == node && scalar_value(b, mul->src[j], &sc)) {
+                        const ggml_status st = compute_mul_mat(b, node, mul, sc);
+                        if (st != GGML_STATUS_SUCCESS) return st;
+                        b->n_fused_scale++;
+                        i++;  // the MUL is done
+                        break;
+                    }
+                }
+                const ggml_status st = compute_mul_mat(b, node, node, 1.0f);
+                if (st != GGML_STATUS_SUCCESS) return st;
+            } break;
+            case GGML_OP_MUL: {
+                const ggml_status st = compute_scalar_mul(b, node);
                 if (st != GGML_STATUS_SUCCESS) return st;
             } break;
             case GGML_OP_NONE:
@@ -227,6 +376,7 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
                 return GGML_STATUS_FAILED;
         }
     }
+    b->act = act_cache{};
     // results are read back through get_tensor (which synchronises its own stream): make them visible first
     if (vlut_ctx_sync(b->ctx) != VLUT_OK) return GGML_STATUS_FAILED;
     return GGML_STATUS_SUCCESS;
@@ -323,6 +473,13 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor *op) {
             if (src0->buffer && src0->buffer->buft != &d->buft) return false;
             return true;
         }
+        case GGML_OP_MUL: {
+            // only the per-tensor `.scale` multiply: f32 matrix x one-element f32 tensor that lives in our buffer type
+            const int j = scalar_mul_operand(op);
+            if (j < 0) return false;
+            const ggml_tensor *sc = op->src[j]->view_src ? op->src[j]->view_src : op->src[j];
+            return sc->buffer && sc->buffer->buft == &d->buft;
+        }
         default:
             return false;
     }
@@ -365,7 +522,20 @@ ggml_backend_dev_t reg_get_device(ggml_backend_reg_t reg, size_t index) {
     GGML_ASSERT(index < r->handles.size());
     return &r->handles[index];
 }
-void *reg_get_proc_address(ggml_backend_reg_t, const char *) { return nullptr; }
+// "vlut_b200_backend_stats": void(ggml_backend_t, int64_t out[4]) -> {GEMMs, quantise passes, folded scales, stand-alone
+// scale kernels} since the backend was created (how tests and llama-bench runs see that the fusions engaged)
+void backend_stats(ggml_backend_t backend, int64_t *out) {
+    backend_ctx *b = (backend_ctx *) backend->context;
+    out[0] = b->n_mul_mat;
+    out[1] = b->n_quantize;
+    out[2] = b->n_fused_scale;
+    out[3] = b->n_scale_rows;
+}
+
+void *reg_get_proc_address(ggml_backend_reg_t, const char *name) {
+    if (name && strcmp(name, "vlut_b200_backend_stats") == 0) return (void *) backend_stats;
+    return nullptr;
+}
 
 const ggml_backend_reg_i reg_iface = {
     /* .get_name         = */ reg_get_name,

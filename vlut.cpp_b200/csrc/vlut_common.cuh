@@ -135,6 +135,8 @@ cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w,
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s);
 cudaError_t launch_relayout(const ActView &a, cudaStream_t s);  // rewrite q_sw from q_rm for a.sw_tile
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
+cudaError_t launch_scale_rows(const float *x, int64_t ldx, float *out, int64_t ldo, int64_t N, int64_t T, float sc,
+                              cudaStream_t s);
 cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);   // single pipeline (TS or SS)
 bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_tc3(const GemmArgs &g, cudaStream_t s, int *launches);  // 256 rows / CTA, shared act stages
