@@ -31,6 +31,6 @@ for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "16,128,512").s
 
     if os.environ.get("TIMELINE"):
         names = ["producer", "mma", "decode0", "epilogue"]
-        kinds = {0: "w0", 1: "w1", 2: "st-issued", 3: "fetched", 4: "st-done", 5: "fenced", 6: "chunk", 7: "drained", 8: "mma-issued", 9: "A-ready"}
+        kinds = {0: "w0", 1: "w1", 2: "st-issued", 3: "fetched", 4: "st-done", 5: "fenced", 6: "chunk", 7: "drained", 8: "mma-issued", 9: "A-ready", 10: "parked", 11: "counted", 12: "fixed-up"}
         for r in range(4):
             print("  timeline", names[r], " ".join(f"{int(t)}:{kinds.get(int(k), k)}" for t, k in ev[r] if t > 0))

@@ -295,6 +295,27 @@ def test_streamk_split_tiles_and_ring_wrap(ctx, orc, monkeypatch, grid, stages, 
 
 
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
+@pytest.mark.parametrize("grid", [4, 10, 14, 22, 148])
+@pytest.mark.parametrize("T", [65, 300, 600])
+def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, monkeypatch, grid, T, fast):
+    """VLUT_TC_WHOLE=2: every CTA pair walks its share of the split units first (tiles shared with other pairs; pairs
+    with no split unit, ranges crossing a tile boundary, last-arriver fix-up skipping empty pairs) and then its whole
+    tiles.  Forced grids make floor(tiles / pairs) and the remainder take many values."""
+    a = api()
+    monkeypatch.setenv("VLUT_TC_GRID", str(grid))
+    monkeypatch.setenv("VLUT_TC_WHOLE", "2")
+    monkeypatch.setenv("VLUT_TC_FAST", str(fast))
+    for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I1_V_2, 3200, 900), (O.I2_V_4, 4096, 1800)]:
+        w = O.make_ternary(N, K, seed=grid)
+        x = O.make_acts(T, K, seed=T, kind="uniform" if grid % 4 else "normal")
+        packed = orc.pack(type_, w)
+        ref = orc.mul_mat(type_, packed, x, N)
+        for rep in range(2):
+            out = run(ctx, type_, packed, x, N, a.ALGO_TCP)
+            assert np.array_equal(bits(out), bits(ref)), f"{O.TYPE_NAMES[type_]} K={K} N={N} rep={rep}"
+
+
+@pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("split", [1, 2, 3, 5, 8])
 @pytest.mark.parametrize("T", [1, 9, 16, 31, 64])
 def test_tcs_cluster_split_k(ctx, orc, monkeypatch, split, T, fast):

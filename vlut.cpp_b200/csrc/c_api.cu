@@ -55,7 +55,7 @@ struct vlut_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_unsafe, part, counters, stage_x, stage_out, stage_w;
+    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_unsafe, part, counters, acc, stage_x, stage_out, stage_w;
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
@@ -154,7 +154,7 @@ void vlut_ctx_destroy(vlut_ctx *c) {
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     DevBuf *bufs[] = {&c->q_rm, &c->q_sw,     &c->scales,  &c->gpre,      &c->nowrap, &c->tile_unsafe,
-                      &c->part, &c->counters, &c->stage_x, &c->stage_out, &c->stage_w};
+                      &c->part, &c->counters, &c->acc, &c->stage_x, &c->stage_out, &c->stage_w};
     for (DevBuf *b : bufs) b->release();
     for (cudaEvent_t e : c->ev_in) cudaEventDestroy(e);
     for (cudaEvent_t e : c->ev_done) cudaEventDestroy(e);
@@ -396,6 +396,10 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
         const size_t cb = (size_t) ((g.Npad / TILE_ROWS + 1) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));
+        const size_t ab = (size_t) c->sm_count * 128 * 128 * sizeof(int32_t);
+        if (c->acc.reserve(ab, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+        if (grew) CK(cudaMemsetAsync(c->acc.p, 0, c->acc.cap, c->stream));
+        g.acc = (int32_t *) c->acc.p;
         g.part = (int32_t *) c->part.p;
         g.counters = (int32_t *) c->counters.p;
     }

@@ -58,7 +58,7 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
 }
 
 // One 16-column chunk of a fast-path drain: subtract the u8-code offset correction, then store (fp32 output or partial slot).
-template <int OUT, bool TO_SLOT>
+template <int OUT, int TO_SLOT>  // TO_SLOT: 0 fp32 output, 1 store the int32 partial, 2 red.add it into an accumulation tile
 __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, const int32_t *s_gs, const float *s_sc, bool ws,
                                            float w_scale, float *out0, float *const *outs, int n_out, int64_t idx0,
                                            int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m) {
@@ -71,7 +71,10 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
         x[4 * j + 2] = (int32_t) v[4 * j + 2] - g.z;
         x[4 * j + 3] = (int32_t) v[4 * j + 3] - g.w;
     }
-    if (TO_SLOT) {
+    if (TO_SLOT == 2) {
+#pragma unroll
+        for (int i = 0; i < 16; i++) atomicAdd(slot_m + (c0 + i) * 128, x[i]);  // result unused: RED, resolved in L2
+    } else if (TO_SLOT == 1) {
 #pragma unroll
         for (int i = 0; i < 16; i++) __stcg(slot_m + (c0 + i) * 128, x[i]);
     } else if (nvalid) {
@@ -82,7 +85,7 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
 // Fast-path drain of one accumulator (NT columns of this thread's TMEM lane).  `ta` = TMEM address of column 0 for this
 // warp's lane quadrant; s_gs / s_sc = per-token correction and scale (shared memory, 16-byte aligned); idx0 = t0 * ldo + n;
 // tvalid = T - t0; slot_m = partial slot + m (TO_SLOT).  Warp-collective: every lane must call it.
-template <int NT, int OUT, bool TO_SLOT>
+template <int NT, int OUT, int TO_SLOT>
 __device__ __forceinline__ void drain_fast(uint32_t ta, const int32_t *s_gs, const float *s_sc, float w_scale, float *out0,
                                            float *const *outs, int n_out, int64_t idx0, int64_t ldo, int tvalid, bool nvalid,
                                            int32_t *slot_m) {

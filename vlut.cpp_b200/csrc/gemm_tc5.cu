@@ -39,7 +39,8 @@ struct Params {
     int KB, G, gsub, RT, RP, TT, U;
     int nstages, stage_bytes;
     int allow_fast, pdl;
-    int whole;  // 1: every pair gets whole output tiles (no split tiles, no fix-up); 0: stream-K over (tile, K-group) units
+    int split_last;  // experiment: walk the whole tiles before the split units
+    int whole;  // 1: whole output tiles only (no fix-up); 0: stream-K over (tile, K-group) units; 2: hybrid (whole tiles + split remainder)
     int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores, 16 no drain
     long long *dbg;
     int dbg_skip;
@@ -59,12 +60,24 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {
     return (2u << 4) | (0u << 7) | (1u << 10) | ((uint32_t) (n >> 3) << 17) | ((uint32_t) (256 >> 4) << 24);
 }
 
-// units of this PAIR: unit = (row-pair tile rp, token tile tt, K-group g), ordered [rp][tt][g]
+// units of this PAIR: unit = (row-pair tile rp, token tile tt, K-group g), ordered [rp][tt][g].  A pair walks up to two
+// unit ranges: first its share [b0, b1) of the SPLIT units (tiles shared with other pairs, fixed up through the workspace),
+// then its WHOLE tiles [a0, a1).  Split units go first so that the last arriver's fix-up runs under the following tiles' MMAs.
+struct Ranges {
+    int a0, a1, b0, b1;
+};
 struct Walk {
-    int u, u0, u1, G, TT, gsub, KB;
+    int u, u1, n0, n1, G, TT, gsub, KB;
     int tile, g, rp, tt, kb0, nsub;
-    __device__ __forceinline__ void init(const Params &p, int u0_, int u1_) {
-        u = u0 = u0_; u1 = u1_; G = p.G; TT = p.TT; gsub = p.gsub; KB = p.KB;
+    __device__ __forceinline__ void init(const Params &p, const Ranges &r) {
+        G = p.G; TT = p.TT; gsub = p.gsub; KB = p.KB;
+        int f0 = r.b0, f1 = r.b1, s0 = r.a0, s1 = r.a1;
+        if (p.split_last) { f0 = r.a0; f1 = r.a1; s0 = r.b0; s1 = r.b1; }
+        if (f0 < f1) { u = f0; u1 = f1; n0 = s0; n1 = s1; }
+        else         { u = s0; u1 = s1; n0 = n1 = 0; }
+        locate();
+    }
+    __device__ __forceinline__ void locate() {
         tile = u / G; g = u - tile * G;
         rp = tile / TT; tt = tile - rp * TT;
         refresh();
@@ -74,6 +87,11 @@ struct Walk {
     __device__ __forceinline__ int run_last() const { return min(u1 - 1, u - g + G - 1); }
     __device__ __forceinline__ void next() {
         ++u;
+        if (u == u1 && n0 < n1) {  // on to the second range
+            u = n0; u1 = n1; n0 = n1;
+            locate();
+            return;
+        }
         if (++g == G) { g = 0; ++tile; if (++tt == TT) { tt = 0; ++rp; } }
         refresh();
     }
@@ -140,8 +158,22 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
 
     const int ntiles = p.RP * p.TT;
-    const int u0 = p.whole ? (int) (((int64_t) pair * ntiles) / npairs) * p.G : (int) (((int64_t) pair * p.U) / npairs);
-    const int u1 = p.whole ? (int) (((int64_t) (pair + 1) * ntiles) / npairs) * p.G : (int) (((int64_t) (pair + 1) * p.U) / npairs);
+    // p.whole: 1 = whole tiles only (uneven tile counts per pair), 0 = stream-K (every unit is a split unit),
+    // 2 = hybrid: floor(ntiles / npairs) whole tiles per pair, the units of the remaining tiles split evenly over all pairs
+    const int full = (p.whole == 2) ? ntiles / npairs : 0;
+    const int sbase = npairs * full * p.G;   // first split unit
+    const int SU = p.U - sbase;              // split units
+    Ranges rg;
+    if (p.whole == 1) {
+        rg.a0 = (int) (((int64_t) pair * ntiles) / npairs) * p.G;
+        rg.a1 = (int) (((int64_t) (pair + 1) * ntiles) / npairs) * p.G;
+        rg.b0 = rg.b1 = 0;
+    } else {
+        rg.a0 = pair * full * p.G;
+        rg.a1 = (pair + 1) * full * p.G;
+        rg.b0 = sbase + (int) (((int64_t) pair * SU) / npairs);
+        rg.b1 = sbase + (int) (((int64_t) (pair + 1) * SU) / npairs);
+    }
     auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
     const bool dbg_on = p.dbg != nullptr && blockIdx.x == 0 && lane == 0;
@@ -166,7 +198,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         const bool is_w = (warp == 14);
         const uint64_t pol = is_w ? ptx::policy_evict_first() : ptx::policy_evict_last();
         Walk w;
-        w.init(p, u0, u1);
+        w.init(p, rg);
         Ring st;
         st.init(S);
         // weights are static: with PDL their stream starts while the predecessor (quantise) kernel is still running;
@@ -206,7 +238,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         if (rank == 0) {
             constexpr uint32_t idesc = make_idesc(NT);
             Walk w;
-            w.init(p, u0, u1);
+            w.init(p, rg);
             Ring st, ar;
             st.init(S);
             ar.init(2);
@@ -281,7 +313,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         const uint32_t afull_leader0 = ptx::mapa(ptx::smem_u32(&s_afull[0]), 0);
         const uint32_t afull_leader1 = ptx::mapa(ptx::smem_u32(&s_afull[1]), 0);
         Walk w;
-        w.init(p, u0, u1);
+        w.init(p, rg);
         Ring st, ar;
         st.init(S);
         ar.init(2);
@@ -358,18 +390,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         // exact-path running totals: this CTA's scratch tile in the (L2-resident) workspace
         int32_t *const tots = p.g.part + ((int64_t) gridDim.x * 2 + blockIdx.x) * (NT * 128);
         Walk w;
-        w.init(p, u0, u1);
+        w.init(p, rg);
         while (w.valid()) {
             // ---- one tile run: units [ra, rb] of one output tile ----
             const int ra = w.u, rb = w.run_last();
             const int g_begin = w.g, g_end = w.g + (rb - ra);
             const bool fast = tile_fast(w.tt);
             const bool complete = (g_begin == 0) && (g_end == p.G - 1);
-            const int run_slot = (ra == u0) ? 0 : 1;
             const int tile = w.tile;
             const int64_t n = ((int64_t) 2 * w.rp + rank) * TILE_ROWS + m;
             const int64_t t0 = (int64_t) w.tt * NT;
-            int32_t *const slot = p.g.part + ((int64_t) blockIdx.x * 2 + run_slot) * (NT * 128);
+            // Split tile: every contributor red.adds its int32 partial into ONE accumulation tile (resolved in L2, fire
+            // and forget), indexed by the first pair that owns a unit of the tile (unique among split tiles: a pair that
+            // owned the first unit of two tiles would own all of the first).  The last arriver reads the sum back with
+            // 64 loads in flight per thread and leaves zeros behind.  (Private slots summed by the last arriver made it
+            // walk contributors x NT/16 dependent L2 round trips of ~2000 clk each under the main loop's traffic.)
+            int32_t *slot = nullptr;
+            if (!complete) {
+                const long long x = (long long) tile * p.G - sbase;
+                const int b_first = (int) (((x + 1) * npairs - 1) / SU);
+                slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * 128);
+            }
             if (et < NT) s_sc[et] = __ldg(p.g.act.scales + t0 + et);
 
             auto emit = [&](int c0, const int32_t (&vals)[16]) {
@@ -386,7 +427,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     }
                 } else {
 #pragma unroll
-                    for (int i = 0; i < 16; i++) __stcg(slot + (c0 + i) * 128 + m, vals[i]);
+                    for (int i = 0; i < 16; i++) atomicAdd(slot + (c0 + i) * 128 + m, vals[i]);  // RED
                 }
             };
 
@@ -406,10 +447,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     const int64_t idx0 = t0 * p.g.ldo + n;
                     const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
                     if (complete)
-                        epi::drain_fast<NT, OUT, false>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                        epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                         p.g.ldo, tvalid, n < p.g.N, nullptr);
                     else
-                        epi::drain_fast<NT, OUT, true>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
+                        epi::drain_fast<NT, OUT, 2>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                        p.g.ldo, tvalid, n < p.g.N, slot + m);
                 } else {
                     // exact path: int16 wrap per K-group, running totals in the scratch tile
@@ -442,6 +483,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
 
             if (!complete) {
                 // split tile (stream-K): partial parked above; the last CTA to arrive sums all slots and finishes
+                mark(10);
                 __threadfence();
                 ptx::bar_sync(1, 128);
                 int32_t *const counter = p.g.counters + tile * 2 + rank;
@@ -451,31 +493,30 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     s_last = (old + ndone == p.G);
                 }
                 ptx::bar_sync(1, 128);
+                mark(11);
                 if (s_last) {
                     __threadfence();
-                    const long long ua = (long long) tile * p.G, ub = ua + p.G - 1;
-                    const int b_lo = (int) (((ua + 1) * npairs - 1) / p.U);
-                    const int b_hi = (int) (((ub + 1) * npairs - 1) / p.U);
+                    constexpr int CB = (NT >= 64) ? 4 : NT / 16;  // 16-column chunks per round trip
 #pragma unroll 1
-                    for (int c0 = 0; c0 < NT; c0 += 16) {
-                        int32_t acc[16];
+                    for (int c0 = 0; c0 < NT; c0 += 16 * CB) {
+                        int32_t a[CB][16];
 #pragma unroll
-                        for (int i = 0; i < 16; i++) acc[i] = 0;
-                        for (int b = b_lo; b <= b_hi; b++) {
-                            const int b_u0 = (int) (((long long) b * p.U) / npairs);
-                            const int b_slot = (b_u0 / p.G == tile) ? 0 : 1;
-                            const int32_t *ps = p.g.part + ((int64_t) (2 * b + rank) * 2 + b_slot) * (NT * 128) + m;
-                            int32_t a[16];
+                        for (int j = 0; j < CB; j++)
 #pragma unroll
-                            for (int i = 0; i < 16; i++) a[i] = __ldcg(ps + (c0 + i) * 128);
+                            for (int i = 0; i < 16; i++) a[j][i] = __ldcg(slot + (c0 + 16 * j + i) * 128 + m);
 #pragma unroll
-                            for (int i = 0; i < 16; i++) acc[i] += a[i];
-                        }
-                        if (n < p.g.N)
-                            epi::store16<OUT>(acc, s_sc + c0, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs, p.g.n_out,
-                                              (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0));
+                        for (int j = 0; j < CB; j++)
+#pragma unroll
+                            for (int i = 0; i < 16; i++) __stcg(slot + (c0 + 16 * j + i) * 128 + m, 0);
+#pragma unroll
+                        for (int j = 0; j < CB; j++)
+                            if (n < p.g.N)
+                                epi::store16<OUT>(a[j], s_sc + c0 + 16 * j, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs,
+                                                  p.g.n_out, (t0 + c0 + 16 * j) * p.g.ldo + n, p.g.ldo,
+                                                  (int) min((int64_t) 16, p.g.T - t0 - c0 - 16 * j));
                     }
                     if (et == 0) *counter = 0;
+                    mark(12);
                 }
             }
             ptx::bar_sync(1, 128);  // s_sc / s_last are reused by the next run
@@ -537,20 +578,32 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
         cached = n;
     }
     if (npairs > cached) npairs = cached;
-    // Work split.  Stream-K (equal units per pair, tiles split across pairs and fixed up through the workspace) balances
-    // perfectly but every split tile costs about ten A blocks of time at the tail (slot write, fence, counter, the last
-    // arriver's reduction: measured T=512: 39.6 us split vs 33.9 us with whole tiles on only 56 of the 74 pairs).  So whole
-    // tiles unless the rounding loss is larger than that: rounds * G  vs  U / npairs + FIXUP_UNITS.
+    // Work split, in K-group units of pair time:
+    //   whole (1)   rounds * G                         whole tiles only; pairs beyond ptiles / rounds stay idle
+    //   hybrid (2)  full * G + 2 ceil(SU / npairs) + 3  floor(ptiles / npairs) whole tiles per pair; the SU units of the
+    //                                                  remaining tiles are split over all pairs and done FIRST, so the
+    //                                                  fix-up (slot write, fence, counter, the last arriver's reduction)
+    //                                                  runs in the epilogue warps under the MMAs of the whole tiles
+    //   stream-K (0) ceil(U / npairs) + 10             every pair ends on a split tile: the fix-up is exposed at the tail
+    //                                                  (measured T=512: 39.6 us vs 33.9 us whole on 56 of the 74 pairs)
     const int ptiles = p.RP * p.TT;
-    constexpr int FIXUP_UNITS = 10;
+    constexpr int FIXUP_UNITS = 10, HYBRID_UNITS = 3;
     const int rounds = (ptiles + npairs - 1) / npairs;
-    p.whole = (rounds * p.G <= (p.U + npairs - 1) / npairs + FIXUP_UNITS) ? 1 : 0;
-    const int forced_grid = env_int("VLUT_TC_GRID", 0);  // tests: force a grid (and with it the stream-K split paths)
+    const int full = ptiles / npairs, su = (ptiles - full * npairs) * p.G;
+    const int cost_whole = rounds * p.G;
+    const int cost_hybrid = full * p.G + (su ? 2 * ((su + npairs - 1) / npairs) + HYBRID_UNITS : 0);  // split units cost ~2x (measured)
+    const int cost_sk = (p.U + npairs - 1) / npairs + FIXUP_UNITS;
+    p.whole = 1;
+    if (full >= 1 && cost_hybrid < cost_whole && cost_hybrid <= cost_sk) p.whole = 2;
+    else if (cost_sk < cost_whole) p.whole = 0;
+    const int forced_grid = env_int("VLUT_TC_GRID", 0);  // tests: force a grid (and with it the split paths)
     if (forced_grid > 0) p.whole = 0;
     p.whole = env_int("VLUT_TC_WHOLE", p.whole);
+    p.split_last = env_int("VLUT_TC_SPLIT_LAST", 0);
     if (forced_grid > 0) npairs = forced_grid / 2;
-    else if (p.whole) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
+    else if (p.whole == 1) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;
+    if (2 * npairs > sm_count) npairs = sm_count / 2;  // one accumulation tile per CTA of a resident grid (GemmArgs.acc)
     if (npairs < 1) npairs = 1;
     cfg.gridDim = dim3((unsigned) (2 * npairs));
     return cudaLaunchKernelEx(&cfg, kern, p);

@@ -112,6 +112,8 @@ struct GemmArgs {
     float w_scale;
     int32_t *part;      // int32 [CTAs][4 slots + 2 scratch][NT][128] stream-K partial tiles (no initialisation needed)
     int32_t *counters;  // per output-tile arrival counters (self-cleaning)
+    int32_t *acc;       // int32 [CTAs][128][128] accumulation tiles of split output tiles (TCP): contributors red.add their
+                        // partials, the last arriver reads the sum and writes zeros back (zeroed at allocation, self-cleaning)
     int sm_count;
 };
 
