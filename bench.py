@@ -196,7 +196,7 @@ def main() -> None:
     torch.cuda.set_stream(stream)
     ctx = api.Context(dev, stream=stream)
 
-    def graph_time_us(fn, iters):
+    def graph_time_us(fn, iters, finish=None):
         """GPU time per call of fn(i), i in [0, iters): one CUDA graph of the whole loop, best of 3 replays, CUDA events
         on the launch stream.  Falls back to an eager loop if the capture fails."""
         for i in range(5):
@@ -207,6 +207,8 @@ def main() -> None:
             with torch.cuda.graph(g, stream=stream):
                 for i in range(iters):
                     fn(i)
+                if finish:
+                    finish()
             g.replay()
             torch.cuda.synchronize()
             best = None
@@ -227,6 +229,8 @@ def main() -> None:
             e0.record()
             for i in range(iters):
                 fn(i)
+            if finish:
+                finish()
             e1.record()
             torch.cuda.synchronize()
             return e0.elapsed_time(e1) / iters * 1e3, "eager"
@@ -251,6 +255,7 @@ def main() -> None:
     xs = make_x(T)
     n_total = N * world
     gather_mode = "none"
+    use_mc = False
     if world == 1:
         outs = [torch.empty((T, n_total), dtype=torch.float32, device=dev) for _ in range(n_x)]
     else:
@@ -265,7 +270,12 @@ def main() -> None:
                 buf = symm_mem.empty((T, n_total), dtype=torch.float32, device=dev)
                 hdls.append(symm_mem.rendezvous(buf, dist.group.WORLD))
                 outs.append(buf)
-            gather_mode = "fused-multimem" if int(getattr(hdls[0], "multicast_ptr", 0) or 0) else "fused-p2p"
+            # multicast sends one copy to the switch, which also returns the rank's OWN slice over its ingress link: the
+            # right trade from 4 ranks up ((N-1)/N of the ingress is needed anyway, egress is 1 slice instead of N-1), the
+            # wrong one at 2 ranks (ingress doubles): there the epilogue stores to the local and the peer buffer directly
+            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and \
+                (world > 2 or os.environ.get("VLUT_BENCH_MULTICAST") == "1") and os.environ.get("VLUT_BENCH_MULTICAST") != "0"
+            gather_mode = "fused-multimem" if use_mc else "fused-p2p"
         except Exception as e:  # noqa: BLE001
             if rank == 0:
                 print(f"[bench] symmetric memory unavailable ({e}); using the NCCL all-gather", file=sys.stderr)
@@ -284,7 +294,7 @@ def main() -> None:
             # the result buffers rotate: the cross-rank barrier that publishes step i-1 is issued after step i's GEMM
             # has been launched, so the NVLink transfer of one step overlaps the compute of the next
             h = hdls[i % n_x]
-            ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs], multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0),
+            ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs], multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0) if use_mc else 0,
                                 ldo=n_total, col0=rank * N)
             if pending:
                 pending.pop().barrier()
@@ -323,6 +333,21 @@ def main() -> None:
     if world == 1:
         # single GPU: the K steps are one CUDA graph (same kernels, same order, same rotating buffers)
         us, timing_mode = graph_time_us(step, args.steps)
+        launches = (ctx.launch_count - launches0) * args.steps // (args.steps + 5) if timing_mode == "cuda-graph" else \
+            (ctx.launch_count - launches0) * args.steps // (2 * args.steps + 5)
+        total_ms = us * args.steps / 1e3
+        per_step = [us / 1e3] * args.steps
+    elif hdls and os.environ.get("VLUT_BENCH_GRAPH", "1") != "0":
+        # fused gather: the K steps (GEMM with scatter epilogue + the symmetric-memory barrier that publishes each step)
+        # are one CUDA graph per rank; the in-graph barriers keep the ranks in lockstep, time = max over ranks
+        def flush():
+            while pending:
+                pending.pop().barrier()
+        flush()
+        dist.barrier()
+        torch.cuda.synchronize()
+        us, timing_mode = graph_time_us(step, args.steps, finish=flush)
+        barrier()
         launches = (ctx.launch_count - launches0) * args.steps // (args.steps + 5) if timing_mode == "cuda-graph" else \
             (ctx.launch_count - launches0) * args.steps // (2 * args.steps + 5)
         total_ms = us * args.steps / 1e3
