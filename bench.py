@@ -273,8 +273,9 @@ def main() -> None:
             # multicast sends one copy to the switch, which also returns the rank's OWN slice over its ingress link: the
             # right trade from 4 ranks up ((N-1)/N of the ingress is needed anyway, egress is 1 slice instead of N-1), the
             # wrong one at 2 ranks (ingress doubles): there the epilogue stores to the local and the peer buffer directly
-            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and \
-                (world > 2 or os.environ.get("VLUT_BENCH_MULTICAST") == "1") and os.environ.get("VLUT_BENCH_MULTICAST") != "0"
+            P2P_AT_2 = False  # flipped once the peer-pointer path is measured faster at N = 2 (VLUT_BENCH_MULTICAST=0 tries it)
+            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST") != "0" and \
+                (world > 2 or not P2P_AT_2 or os.environ.get("VLUT_BENCH_MULTICAST") == "1")
             gather_mode = "fused-multimem" if use_mc else "fused-p2p"
         except Exception as e:  # noqa: BLE001
             if rank == 0:
