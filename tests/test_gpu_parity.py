@@ -249,6 +249,24 @@ def test_mul_mat_host_pipeline_chunks(ctx, orc, T):
         assert (oh[:, N:] == -3.0).all()
 
 
+def test_scale_rows_matches_fp32_multiply(ctx):
+    """vlut_scale_rows = ggml's MUL by a one-element f32 tensor: one fp32 rounding per element, strided rows, in place."""
+    rng = np.random.Generator(np.random.PCG64(5))
+    for T, N, s in [(1, 7, 0.37), (33, 1000, -1.9), (300, 4097, 3.0e-3)]:
+        x = (rng.standard_normal((T, N + 5)) * 100).astype(np.float32)
+        xd = torch.from_numpy(x).cuda()
+        out = torch.full((T, N + 3), -7.0, device="cuda")
+        ctx.scale_rows(xd[:, :N], s, out=out[:, :N])
+        torch.cuda.synchronize()
+        expect = x[:, :N] * np.float32(s)
+        assert np.array_equal(bits(out[:, :N].cpu().numpy()), bits(expect))
+        assert (out[:, N:] == -7.0).all()
+        ctx.scale_rows(xd[:, :N], s, out=xd[:, :N])  # in place
+        torch.cuda.synchronize()
+        assert np.array_equal(bits(xd[:, :N].cpu().numpy()), bits(expect))
+        assert np.array_equal(bits(xd[:, N:].cpu().numpy()), bits(x[:, N:]))
+
+
 def test_strided_output_and_errors(ctx, orc):
     a = api()
     type_, K, N, T = O.I1_V_2, 1280, 100, 5

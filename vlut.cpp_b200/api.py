@@ -174,6 +174,18 @@ class Context:
                                               len(ptrs), 1 if multicast_ptr else 0, ldo, w_scale, algo),
               "vlut_mul_mat_scatter")
 
+    def scale_rows(self, x: torch.Tensor, scale: float, out: torch.Tensor | None = None) -> torch.Tensor:
+        """out[t][n] = x[t][n] * scale (one fp32 rounding): GGML_OP_MUL by a one-element tensor, the weight's `.scale`
+        (ggml-cpu/binary-ops.cpp:152), for when it is not folded into the GEMM epilogue.  In place when out is x."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+        T, N = x.shape
+        if out is None:
+            out = torch.empty((T, N), dtype=torch.float32, device=x.device)
+        assert out.is_cuda and out.dtype == torch.float32 and out.shape == (T, N) and out.stride(1) == 1
+        check(_lib.lib().vlut_scale_rows(self._h, x.data_ptr(), x.stride(0), out.data_ptr(), out.stride(0), N, T, scale),
+              "vlut_scale_rows")
+        return out
+
     def mul_mat_host(self, w: Weight, x_host: torch.Tensor, out_host: torch.Tensor, w_scale: float = 1.0,
                      algo: int = ALGO_AUTO) -> torch.Tensor:
         """The op on HOST buffers (pinned for asynchronous copies): H2D(x) + op + D2H(out) + sync."""

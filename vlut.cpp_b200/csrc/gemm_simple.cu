@@ -46,7 +46,7 @@ cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s) {
 // out[t][n] = x[t][n] * s: GGML_OP_MUL by a one-element f32 tensor (the `.scale` of a ternary weight,
 // src/models/bitnet.cpp:33-34; ggml_compute_forward_mul, ggml-cpu/binary-ops.cpp:152) when it could not be folded
 // into the GEMM epilogue.  One fp32 rounding, as on the CPU.
-__global__ void __launch_bounds__(256) scale_rows_kernel(const float *__restrict__ x, int64_t ldx, float *__restrict__ out,
+__global__ void __launch_bounds__(256) scale_rows_kernel(const float *x, int64_t ldx, float *out,
                                                          int64_t ldo, int64_t N, int64_t T, float s) {
     const int64_t t = blockIdx.y;
     for (int64_t n = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; n < N; n += (int64_t) gridDim.x * blockDim.x)
