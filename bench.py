@@ -270,12 +270,9 @@ def main() -> None:
                 buf = symm_mem.empty((T, n_total), dtype=torch.float32, device=dev)
                 hdls.append(symm_mem.rendezvous(buf, dist.group.WORLD))
                 outs.append(buf)
-            # multicast sends one copy to the switch, which also returns the rank's OWN slice over its ingress link: the
-            # right trade from 4 ranks up ((N-1)/N of the ingress is needed anyway, egress is 1 slice instead of N-1), the
-            # wrong one at 2 ranks (ingress doubles): there the epilogue stores to the local and the peer buffer directly
-            P2P_AT_2 = False  # flipped once the peer-pointer path is measured faster at N = 2 (VLUT_BENCH_MULTICAST=0 tries it)
-            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST") != "0" and \
-                (world > 2 or not P2P_AT_2 or os.environ.get("VLUT_BENCH_MULTICAST") == "1")
+            # multicast (one multimem.st per element, replicated by the switch) is the default wherever it exists; plain
+            # peer-pointer stores measured 185 us against 105 us per step on 2 x B200 (VLUT_BENCH_MULTICAST=0 selects them)
+            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST") != "0"
             gather_mode = "fused-multimem" if use_mc else "fused-p2p"
         except Exception as e:  # noqa: BLE001
             if rank == 0:

@@ -63,6 +63,7 @@ struct vlut_ctx {
     int last_algo = 0;
     uint32_t epoch = 0;  // quantisation call counter (ActView.epoch)
     // vlut_mul_mat_host pipeline: one copy stream per PCIe direction and one event pair per token chunk
+    const char *last_out_lo = nullptr, *last_out_hi = nullptr;  // output range of the GEMM launched last (nullptr: unknown)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_done;
 };
@@ -244,6 +245,7 @@ int vlut_repack_weights(vlut_ctx *c, int type, int64_t K, int64_t N, const void 
     int rc = check_shape(type, K, N);
     if (rc) return rc;
     CK(cudaSetDevice(c->device));
+    c->last_out_lo = c->last_out_hi = nullptr;
     CK(launch_repack(type, K, N, (const uint8_t *) gguf_dev, (uint8_t *) t2_dev, c->stream));
     c->launches++;
     return VLUT_OK;
@@ -333,7 +335,11 @@ static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx,
     if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, 1, T);
     int rc = prepare_act(c, type, K, T, algo);
     if (rc) return rc;
-    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream));
+    // the last kernel this context launched was a GEMM whose output range is known and does not meet x
+    const char *xl = (const char *) x_dev, *xh = xl + ((size_t) (T - 1) * ldx + K) * sizeof(float);
+    const bool untouched = c->last_out_lo && (xh <= c->last_out_lo || xl >= c->last_out_hi);
+    c->last_out_lo = c->last_out_hi = nullptr;
+    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, untouched));
     c->launches++;
     return VLUT_OK;
 }
@@ -457,6 +463,11 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
     c->launches += launches;
     c->last_algo = algo;
+    c->last_out_lo = c->last_out_hi = nullptr;
+    if (out_dev && n_out == 0) {
+        c->last_out_lo = (const char *) out_dev;
+        c->last_out_hi = c->last_out_lo + ((size_t) (T - 1) * ldo + N) * sizeof(float);
+    }
     return VLUT_OK;
 }
 
@@ -485,6 +496,7 @@ int vlut_scale_rows(vlut_ctx *c, const float *x_dev, int64_t ldx, float *out_dev
                     float scale) {
     if (!c || !x_dev || !out_dev || N <= 0 || T <= 0 || ldx < N || ldo < N) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
+    c->last_out_lo = c->last_out_hi = nullptr;  // this kernel's output may be the next quantise's input
     cudaError_t e = launch_scale_rows(x_dev, ldx, out_dev, ldo, N, T, scale, c->stream);
     if (e != cudaSuccess) return cuda_fail(e, "scale_rows launch");
     c->launches += (T + 65534) / 65535;

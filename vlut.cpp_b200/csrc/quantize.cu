@@ -154,7 +154,7 @@ __device__ __forceinline__ int quant1(float x, double is, float isf) {
 
 template <int CH>
 __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
-                                                          ActView a) {
+                                                          ActView a, int early) {
     const int t = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -165,7 +165,10 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
     const int64_t Kpad = a.Kpad;
     const bool live = t < T;
     const float *xr = x + (int64_t) t * ldx;
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // `early` (the host knows the preceding kernel on the stream does not write x): the row is loaded, reduced and its
+    // scale computed while the previous GEMM is still running; only the stores below wait for it (they overwrite the
+    // workspace that GEMM reads)
+    if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
 
     float4 v[CH][4];
     float mx = -INFINITY;
@@ -194,6 +197,7 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
     const double sd = dm / 127;
     const double is = 1e0 / (sd > 1e-5 ? sd : 1e-5);
     const float isf = (float) is;
+    if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
     if (tid == 0) a.scales[t] = live ? (float) sd : 0.0f;
 
     const int gsize = a.gsize;
@@ -310,7 +314,8 @@ cudaError_t launch_relayout(const ActView &a, cudaStream_t s) {
 }
 
 template <int CH>
-static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl) {
+static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
+                              int early) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) a.Tpad);
     cfg.blockDim = dim3(QT);
@@ -321,22 +326,26 @@ static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T,
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a);
+    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a, early);
 }
 
-cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s) {
+cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
+                            bool x_untouched_by_predecessor) {
     if (a.G > 64) return cudaErrorInvalidValue;
     const char *e2 = getenv("VLUT_QUANT_2PASS"), *ep = getenv("VLUT_PDL");
     const bool two_pass = e2 && atoi(e2) != 0;
     // programmatic launch of the quantiser itself (behind the previous GEMM): measured on the quantise + GEMM chain at
     // 4096 -> 14336 it gains 0.1-0.5 us for T <= 64 and from T = 1024 up, and loses 1.6-2 us in between (scripts/time_op.py)
     const char *eq = getenv("VLUT_QUANT_PDL");
-    const bool pdl = (ep ? atoi(ep) != 0 : true) && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512));
+    // VLUT_QUANT_EARLY=1 (experiment, default off): programmatic launch at every T with the loads ahead of the dependency wait
+    const char *ee = getenv("VLUT_QUANT_EARLY");
+    const int early = (ee && atoi(ee) != 0 && x_untouched_by_predecessor && (ep ? atoi(ep) != 0 : true)) ? 1 : 0;
+    const bool pdl = early || ((ep ? atoi(ep) != 0 : true) && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512)));
     const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
     if (!two_pass && aligned && a.Kpad <= 16384) {
-        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl);
-        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl);
-        return launch_reg<4>(x, ldx, K, T, a, s, pdl);
+        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl, early);
+        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl, early);
+        return launch_reg<4>(x, ldx, K, T, a, s, pdl, early);
     }
     quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a);
     return cudaGetLastError();
