@@ -195,6 +195,8 @@ def main() -> None:
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     ctx = api.Context(dev, stream=stream)
+    # the activations of every step are resident tensors written (and synchronised with) before the timed region
+    ctx.set_option(api.Context.OPT_INPUTS_VISIBLE, 1)
 
     def graph_time_us(fn, iters, finish=None):
         """GPU time per call of fn(i), i in [0, iters): one CUDA graph of the whole loop, best of 3 replays, CUDA events

@@ -68,6 +68,14 @@ int   vlut_ctx_create(int device, void *stream, vlut_ctx **out);
 void  vlut_ctx_destroy(vlut_ctx *ctx);
 void *vlut_ctx_stream(vlut_ctx *ctx);
 int   vlut_ctx_sync(vlut_ctx *ctx);
+/* Context options.  VLUT_OPT_INPUTS_VISIBLE = 1: the caller promises that the activations it passes are already
+ * visible on the device when the call is made -- they were written by a copy, by a kernel that has been synchronised
+ * with, or by this context's own kernels -- never by a foreign kernel launched immediately before on the context's
+ * stream.  The quantise kernel may then read them ahead of its programmatic-launch dependency wait (i.e. while the
+ * previous GEMM of this context is still running).  True for the ggml plugin (src1 arrives through a synchronous
+ * set_tensor or from the plugin's own kernels).  Default 0. */
+#define VLUT_OPT_INPUTS_VISIBLE 1
+int   vlut_ctx_set_option(vlut_ctx *ctx, int option, int value);
 /* number of this library's kernels launched through ctx so far (bench.py's gpu_launches) */
 int64_t vlut_ctx_launch_count(const vlut_ctx *ctx);
 

@@ -249,6 +249,37 @@ def test_mul_mat_host_pipeline_chunks(ctx, orc, T):
         assert (oh[:, N:] == -3.0).all()
 
 
+@pytest.mark.parametrize("T", [8, 64, 512, 700])
+def test_inputs_visible_option_and_chained_matmuls(orc, T):
+    """VLUT_OPT_INPUTS_VISIBLE lets the quantise kernel read x ahead of its dependency wait while the previous GEMM of
+    the context still runs -- except when that GEMM's output IS the next x (chained matmuls), which the library must
+    detect.  Back-to-back ops without host synchronisation, K == N so that outputs can feed the next op."""
+    a = api()
+    c = a.Context(0)
+    c.set_option(a.Context.OPT_INPUTS_VISIBLE, 1)
+    type_, K = O.I2_V_4, 1024
+    ws = [O.make_ternary(K, K, seed=s) for s in (1, 2)]
+    packed = [orc.pack(type_, w) for w in ws]
+    W = [c.upload(type_, K, K, p) for p in packed]
+    x0 = O.make_acts(T, K, seed=3)
+    xd = torch.from_numpy(x0).cuda()
+    y1 = torch.empty((T, K), device="cuda")
+    y2 = torch.empty((T, K), device="cuda")
+    outs = []
+    for rep in range(3):  # independent x (early allowed), then chained: y1 -> y2 (early must be refused)
+        c.mul_mat(W[0], xd, out=y1)
+        c.mul_mat(W[1], y1, out=y2)
+        c.mul_mat(W[0], xd, out=y1)  # overwrites y1 while nothing reads it any more
+        outs.append((y1.clone(), y2.clone()))
+    torch.cuda.synchronize()
+    r1 = orc.mul_mat(type_, packed[0], x0, K)
+    r2 = orc.mul_mat(type_, packed[1], r1, K)
+    for y1c, y2c in outs:
+        assert np.array_equal(bits(y1c.cpu().numpy()), bits(r1))
+        assert np.array_equal(bits(y2c.cpu().numpy()), bits(r2))
+    c.close()
+
+
 def test_scale_rows_matches_fp32_multiply(ctx):
     """vlut_scale_rows = ggml's MUL by a one-element f32 tensor: one fp32 rounding per element, strided rows, in place."""
     rng = np.random.Generator(np.random.PCG64(5))

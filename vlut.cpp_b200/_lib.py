@@ -31,6 +31,7 @@ _SIGNATURES = {
     "vlut_ctx_destroy": (None, [vp]),
     "vlut_ctx_stream": (vp, [vp]),
     "vlut_ctx_sync": (cint, [vp]),
+    "vlut_ctx_set_option": (cint, [vp, cint, cint]),
     "vlut_ctx_launch_count": (i64, [vp]),
     "vlut_ctx_last_algo": (cint, [vp]),
     "vlut_dev_malloc": (cint, [cint, C.c_size_t, C.POINTER(vp)]),

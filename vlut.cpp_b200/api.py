@@ -89,6 +89,13 @@ class Context:
         check(_lib.lib().vlut_ctx_create(self.device.index, C.c_void_p(handle), C.byref(h)), "vlut_ctx_create")
         self._h = h
 
+    OPT_INPUTS_VISIBLE = 1
+
+    def set_option(self, option: int, value: int) -> None:
+        """vlut_ctx_set_option.  OPT_INPUTS_VISIBLE: the caller promises that activations are already visible on the
+        device when passed in (not written by a foreign kernel launched just before on this stream)."""
+        check(_lib.lib().vlut_ctx_set_option(self._h, option, value), "vlut_ctx_set_option")
+
     def close(self) -> None:
         if getattr(self, "_h", None):
             _lib.lib().vlut_ctx_destroy(self._h)

@@ -63,6 +63,7 @@ struct vlut_ctx {
     int last_algo = 0;
     uint32_t epoch = 0;  // quantisation call counter (ActView.epoch)
     // vlut_mul_mat_host pipeline: one copy stream per PCIe direction and one event pair per token chunk
+    int inputs_visible = 0;  // VLUT_OPT_INPUTS_VISIBLE
     const char *last_out_lo = nullptr, *last_out_hi = nullptr;  // output range of the GEMM launched last (nullptr: unknown)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_done;
@@ -339,7 +340,7 @@ static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx,
     const char *xl = (const char *) x_dev, *xh = xl + ((size_t) (T - 1) * ldx + K) * sizeof(float);
     const bool untouched = c->last_out_lo && (xh <= c->last_out_lo || xl >= c->last_out_hi);
     c->last_out_lo = c->last_out_hi = nullptr;
-    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, untouched));
+    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, untouched ? (c->inputs_visible ? 1 : 2) : 0));
     c->launches++;
     return VLUT_OK;
 }
@@ -490,6 +491,14 @@ int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const v
     int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo);
     if (rc) return rc;
     return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
+}
+
+int vlut_ctx_set_option(vlut_ctx *c, int option, int value) {
+    if (!c) return VLUT_ERR_INVALID;
+    switch (option) {
+        case VLUT_OPT_INPUTS_VISIBLE: c->inputs_visible = value != 0; return VLUT_OK;
+        default: return VLUT_ERR_INVALID;
+    }
 }
 
 int vlut_scale_rows(vlut_ctx *c, const float *x_dev, int64_t ldx, float *out_dev, int64_t ldo, int64_t N, int64_t T,

@@ -439,6 +439,9 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char * /*params*/)
         delete b;
         return nullptr;
     }
+    // src1 reaches this backend through a synchronous set_tensor or from the backend's own kernels (no cpy_tensor, no
+    // foreign kernels on the context's private stream): the quantise kernel may read it ahead of its dependency wait
+    vlut_ctx_set_option(b->ctx, VLUT_OPT_INPUTS_VISIBLE, 1);
     return new ggml_backend{
         /* .guid    = */ backend_guid(),
         /* .iface   = */ backend_iface,

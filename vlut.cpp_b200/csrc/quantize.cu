@@ -330,17 +330,25 @@ static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T,
 }
 
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
-                            bool x_untouched_by_predecessor) {
+                            int early_ok) {
     if (a.G > 64) return cudaErrorInvalidValue;
     const char *e2 = getenv("VLUT_QUANT_2PASS"), *ep = getenv("VLUT_PDL");
     const bool two_pass = e2 && atoi(e2) != 0;
     // programmatic launch of the quantiser itself (behind the previous GEMM): measured on the quantise + GEMM chain at
     // 4096 -> 14336 it gains 0.1-0.5 us for T <= 64 and from T = 1024 up, and loses 1.6-2 us in between (scripts/time_op.py)
     const char *eq = getenv("VLUT_QUANT_PDL");
-    // VLUT_QUANT_EARLY=1 (experiment, default off): programmatic launch at every T with the loads ahead of the dependency wait
+    // Early mode: programmatic launch with the loads ahead of the dependency wait.  early_ok: 0 = the host cannot rule out
+    // that the preceding kernel writes x; 1 = it can (vlut_ctx_set_option(VLUT_OPT_INPUTS_VISIBLE) + the last launch was a
+    // GEMM that does not write x): used where it measured faster (scripts/time_op.py).
+    // VLUT_QUANT_EARLY=0 never, =1 at every T (needs the same host-side proof about the last launch).
     const char *ee = getenv("VLUT_QUANT_EARLY");
-    const int early = (ee && atoi(ee) != 0 && x_untouched_by_predecessor && (ep ? atoi(ep) != 0 : true)) ? 1 : 0;
-    const bool pdl = early || ((ep ? atoi(ep) != 0 : true) && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512)));
+    const bool pdl_on = ep ? atoi(ep) != 0 : true;
+    int early = 0;
+    if (pdl_on && early_ok) {
+        if (ee) early = atoi(ee) != 0;
+        else early = (early_ok == 1) && (T <= 64 || (T >= 512 && T <= 1024));
+    }
+    const bool pdl = early || (pdl_on && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512)));
     const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
     if (!two_pass && aligned && a.Kpad <= 16384) {
         if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl, early);

@@ -135,7 +135,7 @@ inline __device__ int32_t wrap16(int32_t v) { return (int32_t) (int16_t) (uint16
 cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, uint8_t *t2, cudaStream_t s);
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
-                            bool x_untouched_by_predecessor);
+                            int early_ok);  // early_ok: 1 = policy, 2 = VLUT_QUANT_EARLY=1 experiment without the option
 cudaError_t launch_relayout(const ActView &a, cudaStream_t s);  // rewrite q_sw from q_rm for a.sw_tile
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
 cudaError_t launch_scale_rows(const float *x, int64_t ldx, float *out, int64_t ldo, int64_t N, int64_t T, float sc,
