@@ -2,22 +2,33 @@
 """bench.py -- the headline benchmark of the Vec-LUT MUL_MAT path on B200 (driver contract in the task statement).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--type I2_V_4] [--tokens 512]
+                    [--no-sweep] [--no-configs] [--no-cpu]
 
 Workload (BASELINE.json `metric`): ternary GEMM int-op/s (+ HBM GB/s) at K=4096 x N=14336 (Llama3-8B FFN up/gate
 shape), I2_V_4 weights, synthetic random ternary weights and N(0,1) activations.
   * one *step* = one GGML_OP_MUL_MAT(vlut weight [K,N], f32 [K,T]) at T = 512 tokens (the pp512 regime):
     activation quantisation + Vec-LUT GEMM + fp32 epilogue;  value = 2*K*N*T / time  (zeros counted, like the
-    reference's own test, tests/test-vlut-gemm.cpp:595-598), in Tint-op/s.
-  * `sweep` = the same op at T in {1,2,4,...,2048}: per-T time, Tint-op/s, algorithmic HBM GB/s and both roofline
-    fractions, measured in the same run with CUDA events.
+    reference's own test, tests/test-vlut-gemm.cpp:595-598), in Tint-op/s.  The headline runs in the library's DEFAULT
+    mode (no VLUT_OPT_INPUTS_VISIBLE promise); the opt-in figure is reported beside it (`step_inputs_visible_us`).
+  * `sweep` = the same op at T in {1,2,4,...,2048}: per-T GEMM / op (graph replay) / op (eager launches) time, Tint-op/s,
+    algorithmic HBM GB/s and both roofline fractions, measured in the same run with CUDA events.
+  * `configs` = every BASELINE.json config (shapes: tests/test-vlut-gemm.cpp:665-692 of the reference): (1) I2_V_4
+    4096x4096 T=256, (2) BitNet-3B I1_V_2 3200/8640 sweep, (3) Llama3-8B I2_V_4 at T=512, (4) Falcon3-1B at T=32..256,
+    (5) TriLM-3.9B 3072/9216 at T in {16, 512} -- plus `exact` rows (uniform activations: the per-K-group int16-wrap
+    path) and `batch` rows (Q/K/V and up/gate in one launch, vlut_mul_mat_batch).
+  * the int8 tensor peak is MEASURED in the run (vlut_measure_int8_peak: a tcgen05.mma kind::i8 issue loop on every SM);
+    `frac_int8` divides by it, `frac_int8_vs_2x_bf16` by twice the driver-measured bf16 burst (round-1 convention).
   * inputs are resident in HBM for `value`; `e2e` is the same op through the C-ABI host-buffer entry
     (vlut_mul_mat_host: H2D of x from pinned memory, the op, D2H of the result, stream sync) -- what a
     ggml_backend_sched split costs.
-  * L2: the timed loop rotates over enough distinct weight buffers (and activation/output buffers) that the working
+  * L2: the timed loops rotate over enough distinct weight buffers (and activation/output buffers) that the working
     set exceeds the 126 MB L2 (`config.l2`).
   * N > 1 (torchrun): output-row tensor parallelism, weak scaling: every rank holds its own [K, 14336] row shard
-    of a [K, 14336*N] matrix, quantises the (replicated) activations, computes its slice and all-gathers the f32
-    output slices over NCCL/NVLink; value = 2*K*(14336*N)*T / max-over-ranks time.
+    of a [K, 14336*N] matrix, quantises the (replicated) activations, computes its slice and the GEMM epilogue stores it
+    into EVERY rank's [T][14336*N] buffer (16-byte NVSwitch multicast stores), followed by the library's own barrier
+    kernel.  The gathered buffer is checked bit-for-bit against an NCCL all-gather of the ranks' local results
+    (`checks.gather_bit_exact`; the run fails if false).  `multi_gpu` reports GEMM-only, GEMM+gather, ingress GB/s and
+    the fraction of the NVLink bound, and config 5 (TriLM shapes) strong-scaled over the ranks.
   * --impl reference: the reference's OWN CPU kernels (oracle/_ref, compiled from /root/reference in place) on the
     box's host cores, same op, same metric.
 """
@@ -39,6 +50,7 @@ sys.path.insert(0, str(ROOT))
 K_DIM, N_DIM = 4096, 14336
 SWEEP_T = [1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048]
 L2_BYTES = 126 * 1024 * 1024
+NVLINK_GBS = 900.0  # per direction per GPU (NVLink 5 / NVSwitch), the bound of the all-gather's ingress
 
 
 def load_peaks() -> dict:
@@ -60,7 +72,6 @@ class ClockSampler:
         self.index = index
         self.rows = []
         self.proc = None
-        self.marks = []
 
     def start(self):
         try:
@@ -107,6 +118,10 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+def host_threads() -> int:
+    return len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+
+
 def run_reference(args) -> None:
     """--impl reference: the reference's own CPU kernels on the host cores (rank 0 only)."""
     rank = int(os.environ.get("RANK", "0"))
@@ -117,8 +132,7 @@ def run_reference(args) -> None:
     ref = O.RefLib()
     type_ = O.__dict__[args.type]
     T, K, N = args.tokens, K_DIM, N_DIM * args.gpus
-    # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
-    nth = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    nth = host_threads()  # all host cores, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1)
     rng = np.random.Generator(np.random.PCG64(1234))
     packed = rng.integers(0, 81 if type_ in (O.I2_V, O.I2_V_4, O.I2_V_8) else 243, size=O.row_size(type_, K) * N,
                           dtype=np.uint8)
@@ -136,15 +150,38 @@ def run_reference(args) -> None:
     line = {
         "impl": "reference", "metric": "ternary_gemm_int_ops_per_s", "value": value, "unit": "Tint-op/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total / len(times) * 1e3,
+        "median_ms_per_step": statistics.median(times) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8xternary->int32->f32",
         "data": "synthetic",
-        "config": {"workload": f"vlut MUL_MAT {args.type} K={K} N={N} T={T} (reference CPU kernels, correct tile layout)",
-                   "K": K, "N": N, "T": T, "type": args.type},
+        "config": {"workload": workload_name(args.type, K, N, T, args.gpus), "K": K, "N": N, "T": T, "type": args.type,
+                   "arm": "reference CPU kernels (oracle/_ref), correct tile layout"},
         "cpu_baseline": {"value": value, "unit": "Tint-op/s", "cores": nth, "kind": "reference",
                          "sample": f"full op, {len(times)} reps, isa build {ref.isa}"},
         "e2e": {"value": value, "unit": "Tint-op/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+def workload_name(type_name: str, K: int, N: int, T: int, world: int) -> str:
+    """The same string in both arms (`config.workload`)."""
+    return (f"vlut MUL_MAT {type_name} K={K} N={N} T={T} (quantise + Vec-LUT GEMM + fp32 epilogue"
+            f"{', row-sharded + all-gather of output slices' if world > 1 else ''})")
+
+
+# BASELINE.json configs (SURVEY.md section 8d); shapes from the reference's tests/test-vlut-gemm.cpp:665-692
+CONFIGS = [
+    ("1:vlut-gemm-test", "I2_V_4", [(4096, 4096)], [256]),
+    ("2:bitnet-3b", "I1_V_2", [(3200, 3200), (3200, 8640), (8640, 3200)], [1, 4, 16, 64, 128, 256, 512, 1024, 2048]),
+    ("3:llama3-8b", "I2_V_4", [(4096, 4096), (4096, 1024), (4096, 14336), (14336, 4096)], [512]),
+    ("4:falcon3-1b", "I2_V_4", [(2048, 2048), (2048, 1024), (2048, 8192), (8192, 2048)], [32, 64, 128, 256]),
+    ("5:trilm-3.9b", "I2_V_4", [(3072, 3072), (3072, 9216), (9216, 3072)], [16, 512]),
+]
+BATCHES = [  # (name, type, K, [N...], Ts): weights that share one activation tensor
+    ("llama3-8b up+gate", "I2_V_4", 4096, [14336, 14336], [1, 4, 16, 64]),
+    ("llama3-8b q+k+v", "I2_V_4", 4096, [4096, 1024, 1024], [1, 4, 16, 64]),
+    ("falcon3-1b q+k+v", "I2_V_4", 2048, [2048, 1024, 1024], [32, 64]),
+    ("bitnet-3b up+gate", "I1_V_2", 3200, [8640, 8640], [1, 16]),
+]
 
 
 def main() -> None:
@@ -156,8 +193,10 @@ def main() -> None:
     ap.add_argument("--type", default="I2_V_4", choices=["I2_V", "I2_V_4", "I2_V_8", "I1_V", "I1_V_2"])
     ap.add_argument("--tokens", type=int, default=512)
     ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-configs", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sweep-iters", type=int, default=60)
+    ap.add_argument("--replays", type=int, default=7)
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -184,26 +223,29 @@ def main() -> None:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     dev = torch.device("cuda", local_rank)
     peaks = load_peaks()
-    int8_peak_tops = 2.0 * peaks["bf16_tflops"]  # dense int8 = 2x dense bf16 on sm_100a; no int8 figure is measured
     type_ = api.TYPE_BY_NAME[args.type]
     K, N, T = K_DIM, N_DIM, args.tokens
-    nb_gguf = api.nbytes(type_, K, N)
-    is_i2 = type_ in (api.I2_V, api.I2_V_4, api.I2_V_8)
 
     # a capturable (non-default) stream: launch-bound loops (two ~5 us kernels per op at small T against ~6 us of
     # Python/ctypes launch overhead per call) are captured once into CUDA graphs and replayed
     stream = torch.cuda.Stream(device=dev)
     torch.cuda.set_stream(stream)
     ctx = api.Context(dev, stream=stream)
-    # the activations of every step are resident tensors written (and synchronised with) before the timed region
-    ctx.set_option(api.Context.OPT_INPUTS_VISIBLE, 1)
 
-    def graph_time_us(fn, iters, finish=None):
-        """GPU time per call of fn(i), i in [0, iters): one CUDA graph of the whole loop, best of 3 replays, CUDA events
-        on the launch stream.  Falls back to an eager loop if the capture fails."""
+    # ---- the int8 tensor peak of this GPU, measured --------------------------------
+    int8_peak_tops, clk_per_mma = ctx.measure_int8_peak()
+    int8_peak_2xbf16 = 2.0 * peaks["bf16_tflops"]
+
+    def replay_times_us(fn, iters, replays, finish=None):
+        """GPU time per call of fn(i), i in [0, iters): ONE CUDA graph of the whole loop, replayed `replays` times, each
+        replay timed with CUDA events on the launch stream.  Returns (list of per-call us, mode).  Falls back to eager
+        loops if the capture fails."""
         for i in range(5):
             fn(i)
+        if finish:
+            finish()
         torch.cuda.synchronize()
+        out = []
         try:
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g, stream=stream):
@@ -213,19 +255,23 @@ def main() -> None:
                     finish()
             g.replay()
             torch.cuda.synchronize()
-            best = None
-            for _ in range(3):
+            for _ in range(replays):
                 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 e0.record()
                 g.replay()
                 e1.record()
                 torch.cuda.synchronize()
-                t = e0.elapsed_time(e1) / iters * 1e3
-                best = t if best is None else min(best, t)
+                out.append(e0.elapsed_time(e1) / iters * 1e3)
             del g
-            return best, "cuda-graph"
+            return out, "cuda-graph"
         except Exception as e:  # noqa: BLE001
-            print(f"[bench] graph capture failed ({e}); timing an eager loop", file=sys.stderr)
+            print(f"[bench] graph capture failed ({e}); timing eager loops", file=sys.stderr)
+            torch.cuda.synchronize()
+            return eager_times_us(fn, iters, replays, finish), "eager"
+
+    def eager_times_us(fn, iters, replays, finish=None):
+        out = []
+        for _ in range(replays):
             torch.cuda.synchronize()
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()
@@ -235,35 +281,87 @@ def main() -> None:
                 finish()
             e1.record()
             torch.cuda.synchronize()
-            return e0.elapsed_time(e1) / iters * 1e3, "eager"
+            out.append(e0.elapsed_time(e1) / iters * 1e3)
+        return out
+
+    def med(xs):
+        return float(statistics.median(xs))
+
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
 
-    # ---- resident inputs: enough distinct weight copies to exceed L2 -------------------------------------
-    n_w = max(2, -(-int(1.25 * L2_BYTES) // nb_gguf))
-    weights = []
-    for i in range(n_w):
-        # uniform bytes in [0, 81) (resp. [0, 243)) are iid uniform ternary digits: a valid GGUF I2/I1 tensor
-        gg = torch.randint(0, 81 if is_i2 else 243, (nb_gguf,), dtype=torch.uint8, device=dev, generator=gen)
-        weights.append(ctx.upload(type_, K, N, gg))
-        del gg
+    class Shape:
+        """Resident inputs of one (type, K, N): enough distinct weight copies that a rotation exceeds L2."""
+
+        def __init__(self, tname, K_, N_, max_copies=400):
+            self.tname, self.type, self.K, self.N = tname, api.TYPE_BY_NAME[tname], K_, N_
+            self.nb = api.nbytes(self.type, K_, N_)
+            self.is_i2 = self.type in (api.I2_V, api.I2_V_4, api.I2_V_8)
+            self.n_w = min(max_copies, max(2, -(-int(1.25 * L2_BYTES) // self.nb)))
+            self.weights = []
+            for _ in range(self.n_w):
+                # uniform bytes in [0, 81) (resp. [0, 243)) are iid uniform ternary digits: a valid GGUF I2/I1 tensor
+                gg = torch.randint(0, 81 if self.is_i2 else 243, (self.nb,), dtype=torch.uint8, device=dev, generator=gen)
+                if not self.is_i2 and K_ % 20:   # the 4-trit tail bytes of an I1 row hold values < 81
+                    nb5 = K_ // 20 * 4 * N_
+                    gg[nb5:] = torch.randint(0, 81, (self.nb - nb5,), dtype=torch.uint8, device=dev, generator=gen)
+                self.weights.append(ctx.upload(self.type, K_, N_, gg))
+                del gg
+
+        def alg_bytes(self, t):  # SURVEY.md section 8d: W (GGUF packed size) + A (f32 in) + O (f32 out)
+            return self.nb + 4 * t * self.K + 4 * t * self.N
+
     n_x = 4
 
-    def make_x(t):
+    def make_x(t, k, kind="normal"):
         g2 = torch.Generator(device=dev)
         g2.manual_seed(4321)  # activations are replicated across ranks
-        return [torch.randn((t, K), dtype=torch.float32, device=dev, generator=g2) for _ in range(n_x)]
+        if kind == "uniform":   # sum |q| > 32767 inside a K-group: the per-group int16-wrap (exact) path
+            return [torch.rand((t, k), dtype=torch.float32, device=dev, generator=g2) * 2 - 1 for _ in range(n_x)]
+        return [torch.randn((t, k), dtype=torch.float32, device=dev, generator=g2) for _ in range(n_x)]
 
-    xs = make_x(T)
+    def measure(shape: Shape, t: int, iters: int, kind="normal", eager=True) -> dict:
+        """GEMM alone (pre-quantised activations), the whole op (graph replay) and the whole op launched eagerly."""
+        xl = make_x(t, shape.K, kind)
+        o = torch.empty((t, shape.N), dtype=torch.float32, device=dev)
+        ws, nw = shape.weights, shape.n_w
+        algo = api.pick_algo(shape.type, shape.K, shape.N, t)
+        row = {"type": shape.tname, "K": shape.K, "N": shape.N, "T": t, "algo": api.ALGO_NAMES.get(algo, str(algo))}
+        if algo != api.ALGO_GEMV:   # the GEMV kernel is the whole op (quantisation fused): no stage-2-only figure
+            ctx.quantize_act(shape.type, xl[0])
+            g_us = med(replay_times_us(lambda i: ctx.gemm(ws[i % nw], t, out=o), iters, 3)[0])
+        else:
+            g_us = None
+        op_us = med(replay_times_us(lambda i: ctx.mul_mat(ws[i % nw], xl[i % n_x], out=o), iters, 3)[0])
+        k_us = g_us if g_us is not None else op_us
+        tops = 2.0 * shape.K * shape.N * t / (k_us * 1e-6) / 1e12
+        gbs = shape.alg_bytes(t) / (k_us * 1e-6) / 1e9
+        row.update({"gemm_us": None if g_us is None else round(g_us, 3), "op_us": round(op_us, 3),
+                    "tint_ops": round(tops, 3), "alg_gbs": round(gbs, 1),
+                    "frac_hbm": round(gbs / peaks["hbm_gbs"], 4), "frac_int8": round(tops / int8_peak_tops, 4),
+                    "frac_hbm_op": round(shape.alg_bytes(t) / (op_us * 1e-6) / 1e9 / peaks["hbm_gbs"], 4),
+                    "tok_s": round(t / (op_us * 1e-6), 1)})
+        if eager:
+            row["op_eager_us"] = round(med(eager_times_us(lambda i: ctx.mul_mat(ws[i % nw], xl[i % n_x], out=o), iters, 3)), 3)
+        if kind != "normal":
+            row["acts"] = kind
+        return row
+
+    # ---- resident inputs of the headline shape --------------------------------------------------------------
+    main_shape = Shape(args.type, K, N)
+    weights, n_w, nb_gguf = main_shape.weights, main_shape.n_w, main_shape.nb
+    xs = make_x(T, K)
     n_total = N * world
     gather_mode = "none"
     use_mc = False
+    hdls, flags = [], []
     if world == 1:
         outs = [torch.empty((T, n_total), dtype=torch.float32, device=dev) for _ in range(n_x)]
     else:
         # fused all-gather: the GEMM epilogue stores into every rank's [T][N_total] symmetric-memory buffer (NVSwitch
         # multicast when available, peer pointers otherwise); NCCL all-gather + permute as the fallback / comparison
-        outs, hdls = [], []
+        from vlut_b200 import shard
+        outs = []
         try:
             if os.environ.get("VLUT_BENCH_GATHER", "fused") != "fused":
                 raise RuntimeError("nccl gather requested")
@@ -272,10 +370,11 @@ def main() -> None:
                 buf = symm_mem.empty((T, n_total), dtype=torch.float32, device=dev)
                 hdls.append(symm_mem.rendezvous(buf, dist.group.WORLD))
                 outs.append(buf)
-            # multicast (one multimem.st per element, replicated by the switch) is the default wherever it exists; plain
-            # peer-pointer stores measured 185 us against 105 us per step on 2 x B200 (VLUT_BENCH_MULTICAST=0 selects them)
+            flags = shard.RowShardedWeight.flag_ptrs(hdls[0])
             use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST") != "0"
-            gather_mode = "fused-multimem" if use_mc else "fused-p2p"
+            gather_mode = "fused-multimem-v4" if use_mc else "fused-p2p-v4"
+            if os.environ.get("VLUT_SCATTER_VEC") == "0":
+                gather_mode = gather_mode.replace("-v4", "-scalar")
         except Exception as e:  # noqa: BLE001
             if rank == 0:
                 print(f"[bench] symmetric memory unavailable ({e}); using the NCCL all-gather", file=sys.stderr)
@@ -285,112 +384,110 @@ def main() -> None:
         gather_buf = torch.empty((world * T, N), dtype=torch.float32, device=dev)
         local_out = [torch.empty((T, N), dtype=torch.float32, device=dev) for _ in range(n_x)]
 
+    def fused_scatter(h, w, x, n_tot, col0):
+        ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs],
+                            multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0) if use_mc else 0, ldo=n_tot, col0=col0)
+
     def step(i: int):
         w = weights[i % n_w]
         x = xs[i % n_x]
         if world == 1:
             ctx.mul_mat(w, x, out=outs[i % n_x])
         elif hdls:
-            # the result buffers rotate: the cross-rank barrier that publishes step i-1 is issued after step i's GEMM
-            # has been launched, so the NVLink transfer of one step overlaps the compute of the next
-            h = hdls[i % n_x]
-            ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs], multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0) if use_mc else 0,
-                                ldo=n_total, col0=rank * N)
-            if pending:
-                pending.pop().barrier()
-            pending.append(h)
+            # the result buffers rotate (n_x = 4); the library's barrier kernel publishes every step
+            fused_scatter(hdls[i % n_x], w, x, n_total, rank * N)
+            ctx.barrier(flags, rank)
         else:
             lo = local_out[i % n_x]
             ctx.mul_mat(w, x, out=lo)
             dist.all_gather_into_tensor(gather_buf, lo)
             outs[i % n_x].view(T, world, N).copy_(gather_buf.view(world, T, N).permute(1, 0, 2))
 
-    pending = []  # symmetric-memory handles whose publishing barrier is still owed
-
     def barrier():
-        while pending:
-            pending.pop().barrier()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # quick in-run sanity: AUTO agrees with the scalar anchor kernel at the bench size (both on the GPU)
+    # ---- in-run checks ---------------------------------------------------------------------------------------
+    checks = {}
     torch.cuda.synchronize()
     chk_a = ctx.mul_mat(weights[0], xs[0]).clone()
     chk_b = ctx.mul_mat(weights[0], xs[0], algo=api.ALGO_SIMPLE)
-    auto_equals_simple = bool(torch.equal(chk_a, chk_b))
+    checks["auto_equals_simple_kernel"] = bool(torch.equal(chk_a, chk_b))
+    if world > 1:
+        # the gathered [T][N*G] buffer of the FUSED path == an NCCL all-gather of every rank's local result, bit for bit
+        ok = True
+        for rep in range(2):
+            if hdls:
+                outs[rep].fill_(float("nan"))
+                barrier()
+                fused_scatter(hdls[rep], weights[0], xs[0], n_total, rank * N)
+                ctx.barrier(flags, rank)
+            else:
+                step(rep)
+            torch.cuda.synchronize()
+            lst = [torch.empty_like(chk_a) for _ in range(world)]
+            dist.all_gather(lst, chk_a)
+            expect = torch.cat(lst, dim=1)
+            ok = ok and bool(torch.equal(outs[rep].view(torch.int32), expect.view(torch.int32)))
+            del lst, expect
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        checks["gather_bit_exact"] = bool(flag.item() == 1)
     del chk_a, chk_b
 
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
 
+    # ---- the headline: K steps, default mode -------------------------------------------------------------------
     for i in range(args.warmup):
         step(i)
     barrier()
     launches0 = ctx.launch_count
-    timing_mode = "eager"
-    if world == 1:
-        # single GPU: the K steps are one CUDA graph (same kernels, same order, same rotating buffers)
-        us, timing_mode = graph_time_us(step, args.steps)
-        launches = (ctx.launch_count - launches0) * args.steps // (args.steps + 5) if timing_mode == "cuda-graph" else \
-            (ctx.launch_count - launches0) * args.steps // (2 * args.steps + 5)
-        total_ms = us * args.steps / 1e3
-        per_step = [us / 1e3] * args.steps
-    elif hdls and os.environ.get("VLUT_BENCH_GRAPH", "1") != "0":
-        # fused gather: the K steps (GEMM with scatter epilogue + the symmetric-memory barrier that publishes each step)
-        # are one CUDA graph per rank; the in-graph barriers keep the ranks in lockstep, time = max over ranks
-        def flush():
-            while pending:
-                pending.pop().barrier()
-        flush()
-        dist.barrier()
-        torch.cuda.synchronize()
-        us, timing_mode = graph_time_us(step, args.steps, finish=flush)
-        barrier()
-        launches = (ctx.launch_count - launches0) * args.steps // (args.steps + 5) if timing_mode == "cuda-graph" else \
-            (ctx.launch_count - launches0) * args.steps // (2 * args.steps + 5)
-        total_ms = us * args.steps / 1e3
-        per_step = [us / 1e3] * args.steps
+    if world == 1 or (hdls and os.environ.get("VLUT_BENCH_GRAPH", "1") != "0"):
+        # the K steps are ONE CUDA graph (same kernels, same order, same rotating buffers); at N > 1 the in-graph
+        # barrier kernels keep the ranks in lockstep; time = max over ranks
+        us_list, timing_mode = replay_times_us(step, args.steps, args.replays)
+        per_replay_ms = [u * args.steps / 1e3 for u in us_list]
+        n_calls = 5 + args.steps * (1 if timing_mode == "cuda-graph" else 1 + args.replays)
+        launches = (ctx.launch_count - launches0) * args.steps // n_calls
     else:
-        ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
-        ev[0].record()
-        for i in range(args.steps):
-            step(i)
-            ev[i + 1].record()
-        barrier()
-        launches = ctx.launch_count - launches0
-        total_ms = ev[0].elapsed_time(ev[-1])
-        per_step = [ev[i].elapsed_time(ev[i + 1]) for i in range(args.steps)]
+        timing_mode = "eager"
+        per_replay_ms = []
+        for _ in range(args.replays):
+            barrier()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for i in range(args.steps):
+                step(i)
+            e1.record()
+            barrier()
+            per_replay_ms.append(e0.elapsed_time(e1))
+        launches = (ctx.launch_count - launches0) // args.replays
+    barrier()
     if world > 1:
-        tt = torch.tensor([total_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        total_ms = float(tt.item())
+        tt = torch.tensor(per_replay_ms, dtype=torch.float64, device=dev)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)   # every replay: max over ranks
+        per_replay_ms = [float(v) for v in tt.tolist()]
+    total_ms = med(per_replay_ms)                  # the K timed steps = the median replay
     ms_per_step = total_ms / args.steps
     ops_step = 2.0 * K * n_total * T
     value = ops_step / (ms_per_step * 1e-3) / 1e12
     algo_used = api.ALGO_NAMES[ctx.last_algo]
 
-    # ---- dominant kernel alone (GEMM+epilogue on pre-quantised activations), CUDA events on the launch stream ----
-    def time_gemm(t, iters, x_list):
-        ctx.quantize_act(type_, x_list[0])
-        o = torch.empty((t, N), dtype=torch.float32, device=dev)
-        us, _ = graph_time_us(lambda i: ctx.gemm(weights[i % n_w], t, out=o), iters)
-        return us, api.ALGO_NAMES[ctx.last_algo]
+    # opt-in best case: the caller promises resident, already visible inputs (VLUT_OPT_INPUTS_VISIBLE)
+    step_visible_us = None
+    if world == 1:
+        ctx.set_option(api.Context.OPT_INPUTS_VISIBLE, 1)
+        step_visible_us = med(replay_times_us(step, args.steps, 3)[0])
+        ctx.set_option(api.Context.OPT_INPUTS_VISIBLE, 0)
 
-    def time_op(t, iters, x_list):
-        o = torch.empty((t, N), dtype=torch.float32, device=dev)
-        us, _ = graph_time_us(lambda i: ctx.mul_mat(weights[i % n_w], x_list[i % n_x], out=o), iters)
-        return us
-
-    def alg_bytes(t):  # W (GGUF packed size) + A (f32 in) + O (f32 out)
-        return nb_gguf + 4 * t * K + 4 * t * N
-
-    gemm_us, gemm_algo = time_gemm(T, max(20, args.steps // 2), xs)
-    gemm_tops = 2.0 * K * N * T / (gemm_us * 1e-6) / 1e12
-    gemm_gbs = alg_bytes(T) / (gemm_us * 1e-6) / 1e9
-    frac_tensor = gemm_tops / int8_peak_tops
-    frac_hbm = gemm_gbs / peaks["hbm_gbs"]
+    # ---- dominant kernel alone (GEMM + epilogue on pre-quantised activations) ---------------------------------
+    head = measure(main_shape, T, max(20, args.steps // 2), eager=False)
+    gemm_us, gemm_algo = head["gemm_us"] or head["op_us"], head["algo"]
+    gemm_tops, gemm_gbs = head["tint_ops"], head["alg_gbs"]
+    frac_tensor, frac_hbm = gemm_tops / int8_peak_tops, gemm_gbs / peaks["hbm_gbs"]
     if frac_hbm >= frac_tensor:
         roofline = {"bound": "hbm", "achieved": gemm_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": frac_hbm}
     else:
@@ -398,49 +495,175 @@ def main() -> None:
                     "frac": frac_tensor}
     traffic = None
     try:
-        tj = json.loads((ROOT / "profiles" / "r1_traffic.json").read_text())
+        tj = json.loads((ROOT / "profiles" / "traffic.json").read_text())
         traffic = tj.get(f"{gemm_algo}_T{T}_{args.type}")
     except Exception:  # noqa: BLE001
         pass
     roofline.update({"traffic": traffic, "kernel": f"vlut gemm ({gemm_algo}) T={T}", "kernel_us": gemm_us,
-                     "peak_source": f"{peaks['source']} (MEASURED_PEAKS.json); int8 tensor peak taken as 2 x measured "
-                                    f"bf16 burst (no int8 figure is measured)",
-                     "algorithmic_bytes": alg_bytes(T), "algorithmic_ops": 2 * K * N * T})
+                     "peak_source": f"HBM: {peaks['source']} (MEASURED_PEAKS.json); int8 tensor peak MEASURED in this run: "
+                                    f"tcgen05.mma kind::i8 issue loop on every SM = {int8_peak_tops:.0f} TOP/s "
+                                    f"({clk_per_mma:.1f} clk per M128 N256 K32 MMA)",
+                     "frac_vs_2x_bf16_burst": gemm_tops / int8_peak_2xbf16,
+                     "int8_peak_measured_tops": int8_peak_tops, "int8_peak_2x_bf16_tops": int8_peak_2xbf16,
+                     "algorithmic_bytes": main_shape.alg_bytes(T), "algorithmic_ops": 2 * K * N * T})
 
-    sweep = []
+    sweep, configs, batches = [], [], []
     if not args.no_sweep and world == 1:
         for t in SWEEP_T:
-            xl = make_x(t)
             it = args.sweep_iters if t <= 256 else max(10, args.sweep_iters // 4)
-            g_us, g_algo = time_gemm(t, it, xl)
-            op_us = time_op(t, it, xl)
-            tops = 2.0 * K * N * t / (g_us * 1e-6) / 1e12
-            gbs = alg_bytes(t) / (g_us * 1e-6) / 1e9
-            sweep.append({"T": t, "algo": g_algo, "gemm_us": round(g_us, 3), "op_us": round(op_us, 3),
-                          "tint_ops": round(tops, 3), "alg_gbs": round(gbs, 1),
-                          "frac_hbm": round(gbs / peaks["hbm_gbs"], 4), "frac_int8": round(tops / int8_peak_tops, 4),
-                          "tok_s": round(t / (op_us * 1e-6), 1)})
-            del xl
+            sweep.append(measure(main_shape, t, it))
+        for t in (16, 512):   # the exact (per-K-group drain, int16 wrap) path: one row per regime
+            r = measure(main_shape, t, 20, kind="uniform", eager=False)
+            r["path"] = "exact"
+            sweep.append(r)
+    if not args.no_configs and world == 1:
+        shapes_cache = {}
+        for cname, tname, shapes, ts in CONFIGS:
+            for (k_, n_) in shapes:
+                key = (tname, k_, n_)
+                if key == (args.type, K, N):
+                    shp = main_shape
+                else:
+                    shp = shapes_cache.get(key) or Shape(tname, k_, n_)
+                    shapes_cache[key] = shp
+                for t in ts:
+                    r = measure(shp, t, 30 if t <= 256 else 12, eager=False)
+                    r["config"] = cname
+                    configs.append(r)
+            if cname.startswith("2:"):   # the I1 exact path, one row
+                r = measure(shapes_cache[("I1_V_2", 3200, 8640)], 512, 12, kind="uniform", eager=False)
+                r.update({"config": cname, "path": "exact"})
+                configs.append(r)
+            shapes_cache = {}   # free the copies
+            torch.cuda.empty_cache()
+        # several weights on one activation tensor: ONE quantisation + ONE launch (vlut_mul_mat_batch) vs separate ops
+        for bname, tname, k_, ns, ts in BATCHES:
+            shps = [main_shape if (tname, k_, n_) == (args.type, K, N) else Shape(tname, k_, n_, max_copies=24) for n_ in ns]
+            for t in ts:
+                xl = make_x(t, k_)
+                os_ = [torch.empty((t, n_), dtype=torch.float32, device=dev) for n_ in ns]
+                nbytes_alg = sum(s.nb for s in shps) + 4 * t * k_ + sum(4 * t * n_ for n_ in ns)
 
-    # ---- e2e through the C-ABI host-buffer entry ----------------------------------------------------------
-    xh = [x.cpu().pin_memory() for x in xs[:2]]
-    oh = [torch.empty((T, N), dtype=torch.float32).pin_memory() for _ in range(2)]
-    e2e_steps = max(5, min(args.steps, 50))
-    for i in range(3):
-        ctx.mul_mat_host(weights[i % n_w], xh[i % 2], oh[i % 2])
-    barrier()
-    t0 = time.perf_counter()
-    for i in range(e2e_steps):
-        ctx.mul_mat_host(weights[i % n_w], xh[i % 2], oh[i % 2])
-    torch.cuda.synchronize()
-    e2e_s = (time.perf_counter() - t0) / e2e_steps
+                def f_batch(i):
+                    ctx.mul_mat_batch([s.weights[(i + j) % s.n_w] for j, s in enumerate(shps)], xl[i % n_x], outs=os_)
+
+                def f_sep(i):
+                    for j, s in enumerate(shps):
+                        ctx.mul_mat(s.weights[(i + j) % s.n_w], xl[i % n_x], out=os_[j])
+
+                b_us = med(replay_times_us(f_batch, 30, 3)[0])
+                s_us = med(replay_times_us(f_sep, 30, 3)[0])
+                batches.append({"batch": bname, "type": tname, "K": k_, "Ns": ns, "T": t, "algo": api.ALGO_NAMES[ctx.last_algo],
+                                "batch_us": round(b_us, 3), "separate_us": round(s_us, 3),
+                                "alg_gbs": round(nbytes_alg / (b_us * 1e-6) / 1e9, 1),
+                                "frac_hbm_op": round(nbytes_alg / (b_us * 1e-6) / 1e9 / peaks["hbm_gbs"], 4)})
+            del shps
+            torch.cuda.empty_cache()
+
+    # ---- multi-GPU detail: GEMM-only vs GEMM+gather, link fraction, config 5 strong-scaled --------------------
+    multi = None
     if world > 1:
+        def max_over_ranks(v):
+            t_ = torch.tensor([v], dtype=torch.float64, device=dev)
+            dist.all_reduce(t_, op=dist.ReduceOp.MAX)
+            return float(t_.item())
+
+        lo = torch.empty((T, N), dtype=torch.float32, device=dev)
+        gemm_only_us = max_over_ranks(med(replay_times_us(lambda i: ctx.mul_mat(weights[i % n_w], xs[i % n_x], out=lo), 50, 3)[0]))
+        step_us = ms_per_step * 1e3
+        ingress = (world - 1) * T * N * 4        # bytes every rank must RECEIVE per step
+        multi = {"gemm_only_us": round(gemm_only_us, 2), "gemm_plus_gather_us": round(step_us, 2),
+                 "ingress_bytes_per_rank": ingress, "ingress_gbs": round(ingress / (step_us * 1e-6) / 1e9, 1),
+                 "nvlink_bound_us": round(ingress / (NVLINK_GBS * 1e9) * 1e6, 2),
+                 "frac_of_nvlink_bound": round(ingress / (step_us * 1e-6) / 1e9 / NVLINK_GBS, 4),
+                 "efficiency_ceiling_weak": round(min(1.0, gemm_only_us / max(gemm_only_us, ingress / (NVLINK_GBS * 1e9) * 1e6)), 4),
+                 "gather": gather_mode, "strong_scaling_config5": []}
+        if hdls:
+            import torch.distributed._symmetric_memory as symm_mem
+            for (k_, n_) in [(3072, 3072), (3072, 9216), (9216, 3072)]:
+                rows = n_ // world // 128 * 128
+                if rows == 0:
+                    continue
+                shp = Shape("I2_V_4", k_, rows, max_copies=max(2, 24 // world))
+                for t in (16, 512):
+                    xl = make_x(t, k_)
+                    bufs, hs = [], []
+                    for _ in range(2):
+                        b_ = symm_mem.empty((t, rows * world), dtype=torch.float32, device=dev)
+                        hs.append(symm_mem.rendezvous(b_, dist.group.WORLD))
+                        bufs.append(b_)
+                    fl = shard.RowShardedWeight.flag_ptrs(hs[0])
+
+                    def f(i):
+                        fused_scatter(hs[i % 2], shp.weights[i % shp.n_w], xl[i % n_x], rows * world, rank * rows)
+                        ctx.barrier(fl, rank)
+
+                    barrier()
+                    us = max_over_ranks(med(replay_times_us(f, 40, 3)[0]))
+                    barrier()
+                    o1 = torch.empty((t, rows), dtype=torch.float32, device=dev)
+                    us_local = max_over_ranks(med(replay_times_us(
+                        lambda i: ctx.mul_mat(shp.weights[i % shp.n_w], xl[i % n_x], out=o1), 40, 3)[0]))
+                    multi["strong_scaling_config5"].append(
+                        {"type": "I2_V_4", "K": k_, "N_total": rows * world, "rows_per_rank": rows, "T": t,
+                         "gemm_plus_gather_us": round(us, 2), "gemm_only_us": round(us_local, 2),
+                         "tint_ops": round(2.0 * k_ * rows * world * t / (us * 1e-6) / 1e12, 2),
+                         "tok_s": round(t / (us * 1e-6), 1)})
+                    del bufs, hs
+                del shp
+                torch.cuda.empty_cache()
+
+    # ---- e2e through the reference-facing C-ABI call with HOST buffers ---------------------------------------
+    xh = [x.cpu().pin_memory() for x in xs[:2]]
+    e2e_steps = max(5, min(args.steps, 50))
+    if world == 1:
+        oh = [torch.empty((T, N), dtype=torch.float32).pin_memory() for _ in range(2)]
+        for i in range(3):
+            ctx.mul_mat_host(weights[i % n_w], xh[i % 2], oh[i % 2])
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            ctx.mul_mat_host(weights[i % n_w], xh[i % 2], oh[i % 2])
+        torch.cuda.synchronize()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
+        e2e = {"value": 2.0 * K * n_total * T / e2e_s / 1e12, "unit": "Tint-op/s", "h2d_bytes_per_step": 4 * T * K,
+               "d2h_bytes_per_step": 4 * T * N, "ms_per_step": e2e_s * 1e3,
+               "note": "vlut_mul_mat_host: pinned H2D of x + quantise + GEMM + D2H of out + stream sync"}
+    else:
+        # the SHARDED path end to end: every rank uploads the (replicated) activations from pinned host memory, runs its
+        # shard with the fused gather, and reads back its 1/G share of the gathered token rows -- the ranks together
+        # return the whole [T][N*G] result to the host once, over G PCIe links
+        t_lo, t_hi = rank * T // world, (rank + 1) * T // world
+        xd = [torch.empty((T, K), dtype=torch.float32, device=dev) for _ in range(2)]
+        ohs = [torch.empty((t_hi - t_lo, n_total), dtype=torch.float32).pin_memory() for _ in range(2)]
+
+        def e2e_step(i):
+            xd[i % 2].copy_(xh[i % 2], non_blocking=True)
+            if hdls:
+                fused_scatter(hdls[i % n_x], weights[i % n_w], xd[i % 2], n_total, rank * N)
+                ctx.barrier(flags, rank)
+            else:
+                ctx.mul_mat(weights[i % n_w], xd[i % 2], out=local_out[i % n_x])
+                dist.all_gather_into_tensor(gather_buf, local_out[i % n_x])
+                outs[i % n_x].view(T, world, N).copy_(gather_buf.view(world, T, N).permute(1, 0, 2))
+            ohs[i % 2].copy_(outs[i % n_x][t_lo:t_hi], non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+        for i in range(3):
+            e2e_step(i)
+        barrier()
+        t0 = time.perf_counter()
+        for i in range(e2e_steps):
+            e2e_step(i)
+        torch.cuda.synchronize()
+        e2e_s = (time.perf_counter() - t0) / e2e_steps
         tt = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
         e2e_s = float(tt.item())
-    e2e = {"value": 2.0 * K * n_total * T / e2e_s / 1e12, "unit": "Tint-op/s", "h2d_bytes_per_step": 4 * T * K,
-           "d2h_bytes_per_step": 4 * T * N, "ms_per_step": e2e_s * 1e3,
-           "note": "vlut_mul_mat_host: pinned H2D of x + quantise + GEMM + D2H of out + stream sync, per rank"}
+        e2e = {"value": 2.0 * K * n_total * T / e2e_s / 1e12, "unit": "Tint-op/s", "h2d_bytes_per_step": 4 * T * K,
+               "d2h_bytes_per_step": 4 * (t_hi - t_lo) * n_total, "ms_per_step": e2e_s * 1e3,
+               "note": "per rank: pinned H2D of x, row-shard GEMM with fused all-gather, barrier, D2H of this rank's 1/G "
+                       "share of the gathered token rows, stream sync (max over ranks)"}
 
     clocks = sampler.stop() if rank == 0 else None
 
@@ -450,11 +673,9 @@ def main() -> None:
         from oracle import oracle as O
         try:
             ref = O.RefLib()
-            kind = "reference"
-            nth = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
-            pk = weights[0]  # regenerate the same distribution on the host: timing is data independent
-            rng = np.random.Generator(np.random.PCG64(1234))
-            packed = rng.integers(0, 81 if is_i2 else 243, size=nb_gguf, dtype=np.uint8)
+            nth = host_threads()
+            rng = np.random.Generator(np.random.PCG64(1234))   # same distribution on the host: timing is data independent
+            packed = rng.integers(0, 81 if main_shape.is_i2 else 243, size=nb_gguf, dtype=np.uint8)
             xc = xs[0].cpu().numpy()
             ref.mul_mat(type_, packed, xc, N, nth=nth)
             reps, t_acc = 0, 0.0
@@ -463,7 +684,7 @@ def main() -> None:
                 ref.mul_mat(type_, packed, xc, N, nth=nth)
                 t_acc += time.perf_counter() - t0
                 reps += 1
-            cpu = {"value": 2.0 * K * N * T * reps / t_acc / 1e12, "unit": "Tint-op/s", "cores": nth, "kind": kind,
+            cpu = {"value": 2.0 * K * N * T * reps / t_acc / 1e12, "unit": "Tint-op/s", "cores": nth, "kind": "reference",
                    "sample": f"full op K={K} N={N} T={T}, {reps} reps, {t_acc / reps * 1e3:.1f} ms each, "
                              f"build {ref.isa}", "ms_per_op": t_acc / reps * 1e3}
         except Exception as e:  # noqa: BLE001
@@ -475,27 +696,36 @@ def main() -> None:
             "metric": "ternary_gemm_int_ops_per_s", "value": value, "unit": "Tint-op/s", "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int8xternary->int32->f32", "data": "synthetic",
-            "config": {"workload": f"vlut MUL_MAT {args.type} K={K} N={n_total} T={T} "
-                                   f"(quantise + Vec-LUT GEMM + fp32 epilogue"
-                                   f"{', row-sharded + all-gather of output slices' if world > 1 else ''})",
+            "config": {"workload": workload_name(args.type, K, n_total, T, world),
                        "K": K, "N": n_total, "T": T, "type": args.type, "algo": algo_used,
+                       "mode": "library defaults (no VLUT_OPT_INPUTS_VISIBLE promise)",
                        "l2": f"rotating {n_w} weight buffers + {n_x} activation/output buffers, working set "
                              f"{ws_mb:.0f} MB > 126 MB L2",
-                       "parallelism": f"row-shard x{world}, gather={gather_mode}" if world > 1 else "single GPU"},
-            "median_ms_per_step": statistics.median(per_step),
-            "timing": f"{timing_mode}: K steps timed with CUDA events on the launch stream",
+                       "parallelism": f"row-shard x{world}, gather={gather_mode}, barrier=vlut_barrier" if world > 1 else "single GPU"},
+            "median_ms_per_step": ms_per_step,
+            "min_ms_per_step": min(per_replay_ms) / args.steps, "max_ms_per_step": max(per_replay_ms) / args.steps,
+            "replays_ms_per_step": [round(v / args.steps, 6) for v in per_replay_ms],
+            "timing": f"{timing_mode}: the K steps timed with CUDA events on the launch stream, {len(per_replay_ms)} "
+                      f"repetitions, ms_per_step = the median repetition / K",
+            "step_inputs_visible_us": step_visible_us,
             "gpu_launches": int(launches),
             "roofline": roofline,
             "cpu_baseline": cpu,
             "e2e": e2e,
             "clocks": clocks,
             "sweep": sweep,
-            "checks": {"auto_equals_simple_kernel": auto_equals_simple},
+            "configs": configs,
+            "batches": batches,
+            "multi_gpu": multi,
+            "checks": checks,
         }
         print(json.dumps(line), flush=True)
+    ok = all(bool(v) for v in checks.values())
     if world > 1:
         dist.destroy_process_group()
     ctx.close()
+    if not ok:
+        raise SystemExit(f"bench.py: an in-run check failed: {checks}")
 
 
 if __name__ == "__main__":

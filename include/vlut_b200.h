@@ -42,12 +42,10 @@ extern "C" {
 /* GEMM algorithms (stage 2).  AUTO picks per token count from the measured crossover table. */
 #define VLUT_ALGO_AUTO    0
 #define VLUT_ALGO_SIMPLE  1   /* one thread per output, scalar: the in-library correctness anchor            */
-#define VLUT_ALGO_TC      3   /* stream-K tcgen05 kind::i8: TMA weight stream, 8-warp register unpack into TMEM, PDL     */
-#define VLUT_ALGO_TC1     5   /* first generation: 4 decode warps; A operand in TMEM or (VLUT_TC_TS=0) shared memory    */
-#define VLUT_ALGO_TC2     6   /* 256 weight rows per CTA, two pipelines sharing every activation stage                  */
-#define VLUT_ALGO_TCP     7   /* CTA pairs (cluster of 2, cta_group::2, M = 256): each CTA stages half the token tile, T > 32 */
-#define VLUT_ALGO_TCS     8   /* T <= 64: per-thread cp.async weight stream, K split over a thread-block cluster (DSMEM reduce)    */
-#define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate, T <= 16 (measured candidate)     */
+#define VLUT_ALGO_LUT     4   /* faithful shared-memory vector-LUT lookup-accumulate, T <= 16 (measured candidate)                  */
+#define VLUT_ALGO_TCP     7   /* tcgen05 kind::i8 on CTA pairs (cluster of 2, cta_group::2, M = 256), T > 32: the tensor-bound regime */
+#define VLUT_ALGO_TCS     8   /* tcgen05, T <= 64: per-thread cp.async weight stream, K split over a thread-block cluster (DSMEM)    */
+#define VLUT_ALGO_GEMV    9   /* CUDA cores, T <= 8: register decode + dp4a, split-K, activation quantisation fused (one launch)     */
 
 typedef struct vlut_ctx vlut_ctx;
 
@@ -76,6 +74,9 @@ int   vlut_ctx_sync(vlut_ctx *ctx);
  * set_tensor or from the plugin's own kernels).  Default 0. */
 #define VLUT_OPT_INPUTS_VISIBLE 1
 int   vlut_ctx_set_option(vlut_ctx *ctx, int option, int value);
+/* Re-read the VLUT_* environment knobs (they are read once, at the first call / every vlut_ctx_create -- never on the
+ * launch path).  Test hook. */
+int   vlut_reload_env(void);
 /* number of this library's kernels launched through ctx so far (bench.py's gpu_launches) */
 int64_t vlut_ctx_launch_count(const vlut_ctx *ctx);
 
@@ -134,14 +135,43 @@ int vlut_scale_rows(vlut_ctx *ctx, const float *x_dev, int64_t ldx, float *out_d
 int vlut_mul_mat_scatter(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                          int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
                          int algo);
+/* The cross-rank barrier that publishes a fused all-gather.  flags_dev[i] = rank i's flag array as seen from this device:
+ * >= 16 uint32, peer-visible (a symmetric-memory signal pad or a vlut_group allocation), zero-initialised.  Rank `rank`
+ * advances its epoch (kept in word [8] of its own array, so the call is CUDA-graph capturable), stores it into slot [rank]
+ * of every rank's array (st.release.sys behind a system-scope fence) and waits until all slots of its own array have
+ * reached it.  Every rank must call it the same number of times.  Enqueued on the context's stream after the scatter GEMM;
+ * replaces the synchronisation of the baseline's separate collective (ncclAllGather). */
+int vlut_barrier(vlut_ctx *ctx, void *const *flags_dev, int n_ranks, int rank);
 /* the whole op on HOST buffers: H2D of x, the op, D2H of out, stream sync -- what a ggml_backend_sched split
  * costs (ggml/src/ggml-backend.cpp:1443-1460).  Pinned host memory makes the copies asynchronous. */
 int vlut_mul_mat_host(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev,
                       const float *x_host, int64_t ldx, float *out_host, int64_t ldo, float w_scale, int algo);
 
+/* Several weights that share ONE activation tensor -- Q/K/V on an attention input, up/gate on an FFN input: consecutive
+ * build_lora_mm calls on one tensor (src/models/bitnet.cpp:28-60, src/llama-graph.cpp:668-671, :780-783).  One
+ * quantisation and, in the small-token regime (T <= 64), ONE kernel launch that streams all n weights; otherwise the GEMMs
+ * run back to back on the one quantisation.  All weights have the same K and the same K-group family (I2* or I1*).
+ * Bit-identical to n separate vlut_mul_mat calls. */
+int vlut_mul_mat_batch(vlut_ctx *ctx, int n, const int *types, int64_t K, const int64_t *Ns, int64_t T,
+                       const void *const *t2_dev, const float *x_dev, int64_t ldx, float *const *outs_dev,
+                       const int64_t *ldos, const float *w_scales /* NULL: all 1.0f */, int algo);
+/* same, on the activations last quantised into ctx (stage 2+3 only) */
+int vlut_gemm_batch(vlut_ctx *ctx, int n, const int *types, int64_t K, const int64_t *Ns, int64_t T,
+                    const void *const *t2_dev, float *const *outs_dev, const int64_t *ldos, const float *w_scales, int algo);
+
+/* 1 if vlut_mul_mat handles this op (valid vlut type and packing constraints, at most 64 K-groups), else 0: what the ggml
+ * plugin's supports_op asks (ggml_backend_device_i.supports_op, ggml/src/ggml-backend-impl.h:166) */
+int vlut_op_supported(int type, int64_t K, int64_t N, int64_t T);
+
 /* which algorithm AUTO resolves to for this shape (also what the last vlut_gemm on ctx used) */
 int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T);
 int vlut_ctx_last_algo(const vlut_ctx *ctx);
+
+/* ---- measurement ------------------------------------------------------------------------------------- */
+/* The int8 tensor-pipe peak of the context's device, measured: one CTA per SM issuing tcgen05.mma kind::i8 (M128 N256 K32,
+ * A in TMEM like the GEMM kernels) back to back, timed with CUDA events.  *tops = 2 * MAC / s over the whole device in
+ * TOP/s, *clk_per_mma (optional) = SM clocks per MMA.  bench.py's int8 roofline denominator. */
+int vlut_measure_int8_peak(vlut_ctx *ctx, double *tops, double *clk_per_mma);
 
 /* ---- test hooks ---------------------------------------------------------------------------------------- */
 /* copy the quantised activations of the last vlut_quantize_act back: q_host int8 [T][K], scales_host [T] */

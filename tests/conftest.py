@@ -39,3 +39,28 @@ def ctx():
     c = api.Context(0)
     yield c
     c.close()
+
+
+@pytest.fixture
+def knobs():
+    """Set VLUT_* environment knobs for one test.  The library resolves its knobs once (never on the launch path), so the
+    fixture makes it re-read them after every change and again after restoring the environment."""
+    import os
+    import vlut_b200  # noqa: F401
+    from vlut_b200 import api
+    saved = {}
+
+    def set_(**kv):
+        for k, v in kv.items():
+            if k not in saved:
+                saved[k] = os.environ.get(k)
+            os.environ[k] = str(v)
+        api.reload_env()
+
+    yield set_
+    for k, v in saved.items():
+        if v is None:
+            os.environ.pop(k, None)
+        else:
+            os.environ[k] = v
+    api.reload_env()

@@ -119,5 +119,7 @@ def test_scale_fusion_and_shared_activations(tmp_path, orc, type_, K, N, T, fuse
     expect = [base * np.float32(0.37), base * np.float32(-1.9), base, base * np.float32(0.37), base + np.float32(1.0)]
     for i, e in enumerate(expect):
         assert np.array_equal(bits(out[i]), bits(e)), f"output {i} differs"
-    want = "gemm=4 quantize=1 fused_scale=2 scale_rows=1" if fuse else "gemm=4 quantize=1 fused_scale=0 scale_rows=3"
+    # fused: the four MUL_MATs on one input (two of them with their scale folded in) run as ONE batched group
+    want = ("gemm=4 quantize=1 fused_scale=2 scale_rows=1 batched=4" if fuse
+            else "gemm=4 quantize=1 fused_scale=0 scale_rows=3 batched=0")
     assert want in r.stdout, r.stdout

@@ -32,9 +32,10 @@ def api():
 
 def algos_for(T):
     a = api()
-    return ([a.ALGO_SIMPLE, a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_LUT] if T <= 16 else []) +
-            ([a.ALGO_TCP] if T > 32 else []) +  # CTA-pair kernel: token tiles of 64 / 128
-            ([a.ALGO_TCS] if T <= 64 else []))  # small-T streaming kernel
+    return ([a.ALGO_AUTO, a.ALGO_SIMPLE] + ([a.ALGO_LUT] if T <= 16 else []) +
+            ([a.ALGO_GEMV] if T <= 8 else []) +   # CUDA-core split-K GEMV with fused quantisation
+            ([a.ALGO_TCP] if T > 32 else []) +    # CTA-pair kernel: token tiles of 64 / 128 / 256
+            ([a.ALGO_TCS] if T <= 64 else []))    # small-T streaming kernel
 
 
 def run(ctx, type_, packed, x, N, algo, w_scale=1.0):
@@ -81,10 +82,10 @@ def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
 
 
 @pytest.mark.parametrize("two_pass", [0, 1], ids=["register-kernel", "two-pass-kernel"])
-def test_quantize_ties_and_saturation(ctx, orc, monkeypatch, two_pass):
+def test_quantize_ties_and_saturation(ctx, orc, knobs, two_pass):
     """round() is half AWAY from zero and the clamp is asymmetric: exact .5 products (row max 127 -> scale 1), values far
     outside the int8 range, and a row whose signed max is negative (everything saturates to -128)."""
-    monkeypatch.setenv("VLUT_QUANT_2PASS", str(two_pass))
+    knobs(VLUT_QUANT_2PASS=two_pass)
     K = 1024
     x = np.zeros((3, K), dtype=np.float32)
     ties = np.array([0.5, -0.5, 1.5, -1.5, 2.5, -2.5, 126.5, -126.5, -127.5, -128.5, -129.0, -1000.0, 127.0, 0.49999997,
@@ -177,7 +178,7 @@ def test_full_size_known_answers(ctx):
             pytest.skip("numpy RNG stream differs from the one the fixtures were made with")
         packed = O.Oracle().pack(k["type"], w)
         assert hashlib.sha256(packed.tobytes()).hexdigest() == k["sha256_packed"]
-        for algo in [api().ALGO_TC, api().ALGO_AUTO] + ([api().ALGO_TCS] if k["T"] <= 64 else []):
+        for algo in [api().ALGO_AUTO] + ([api().ALGO_TCS] if k["T"] <= 64 else [api().ALGO_TCP]):
             out = run(ctx, k["type"], packed, x, k["N"], algo)
             assert hashlib.sha256(out.tobytes()).hexdigest() == k["sha256_out"], f"{name} algo={algo}"
 
@@ -317,43 +318,35 @@ def test_strided_output_and_errors(ctx, orc):
         ctx.upload(O.I2_V_4, 1000, 8, np.zeros(10, dtype=np.uint8))  # K % 16 != 0
 
 
-@pytest.mark.parametrize("ts", [1, 0], ids=["A-in-TMEM", "A-in-smem"])
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
-@pytest.mark.parametrize("grid,stages", [(3, 0), (7, 2), (20, 3), (148, 0)])
-@pytest.mark.parametrize("T", [5, 16, 33, 64, 130, 300])
-def test_streamk_split_tiles_and_ring_wrap(ctx, orc, monkeypatch, grid, stages, T, fast, ts):
-    """Force few persistent CTAs / few pipeline stages so that every CTA walks several (tile, K-group) units:
-    exercises the shared-memory ring wrap-around, tiles completed by a single CTA (direct store), tiles split
-    across CTAs (int32 partials + last-arriver epilogue), the self-cleaning workspace, both A-operand paths
-    (TMEM / shared memory) and both drain policies (single drain when no int16 wrap is possible / per K-group)."""
+@pytest.mark.parametrize("grid,stages", [(4, 0), (6, 2), (20, 3), (148, 0)])
+@pytest.mark.parametrize("T", [33, 64, 130, 300, 520])
+def test_streamk_split_tiles_and_ring_wrap(ctx, orc, knobs, grid, stages, T, fast):
+    """Force few persistent CTA pairs / few pipeline stages so that every pair walks several (tile, K-group) units:
+    exercises the shared-memory ring wrap-around, tiles completed by a single pair (direct store), tiles split
+    across pairs (int32 partials + last-arriver epilogue), the self-cleaning workspace and both drain policies (single
+    drain when no int16 wrap is possible / per K-group)."""
     a = api()
-    monkeypatch.setenv("VLUT_TC_GRID", str(grid))
-    monkeypatch.setenv("VLUT_TC_STAGES", str(stages))
-    monkeypatch.setenv("VLUT_TC_FAST", str(fast))
-    monkeypatch.setenv("VLUT_TC_TS", str(ts))
+    knobs(VLUT_TC_GRID=grid, VLUT_TC_STAGES=stages, VLUT_TC_FAST=fast)
     for type_, K, N in [(O.I2_V_4, 4096, 640), (O.I1_V_2, 3200, 520)]:
         w = O.make_ternary(N, K, seed=grid)
         x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "normal")  # uniform: sum|q| often > 32767
         packed = orc.pack(type_, w)
         ref = orc.mul_mat(type_, packed, x, N)
-        algos = [a.ALGO_TC, a.ALGO_TC1, a.ALGO_TC2] + ([a.ALGO_TCP] if T > 32 else [])
-        for algo in (algos if ts else [a.ALGO_TC1]):  # shared-memory A path: TC1 only
-            for rep in range(2):  # second run sees the workspace the first one left behind
-                out = run(ctx, type_, packed, x, N, algo)
-                assert np.array_equal(bits(out), bits(ref)), f"algo={algo} rep={rep}"
+        for rep in range(2):  # second run sees the workspace the first one left behind
+            out = run(ctx, type_, packed, x, N, a.ALGO_TCP)
+            assert np.array_equal(bits(out), bits(ref)), f"rep={rep}"
 
 
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("grid", [4, 10, 14, 22, 148])
 @pytest.mark.parametrize("T", [65, 300, 600])
-def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, monkeypatch, grid, T, fast):
+def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, knobs, grid, T, fast):
     """VLUT_TC_WHOLE=2: every CTA pair walks its share of the split units first (tiles shared with other pairs; pairs
     with no split unit, ranges crossing a tile boundary, last-arriver fix-up skipping empty pairs) and then its whole
     tiles.  Forced grids make floor(tiles / pairs) and the remainder take many values."""
     a = api()
-    monkeypatch.setenv("VLUT_TC_GRID", str(grid))
-    monkeypatch.setenv("VLUT_TC_WHOLE", "2")
-    monkeypatch.setenv("VLUT_TC_FAST", str(fast))
+    knobs(VLUT_TC_GRID=grid, VLUT_TC_WHOLE=2, VLUT_TC_FAST=fast)
     for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I1_V_2, 3200, 900), (O.I2_V_4, 4096, 1800)]:
         w = O.make_ternary(N, K, seed=grid)
         x = O.make_acts(T, K, seed=T, kind="uniform" if grid % 4 else "normal")
@@ -367,14 +360,12 @@ def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, monkeypatch, grid, T, fast)
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("split", [1, 2, 3, 5, 8])
 @pytest.mark.parametrize("T", [1, 9, 16, 31, 64])
-def test_tcs_cluster_split_k(ctx, orc, monkeypatch, split, T, fast):
+def test_tcs_cluster_split_k(ctx, orc, knobs, split, T, fast):
     """VLUT_ALGO_TCS with the K-groups of every strip forced onto `split` CTAs of a thread-block cluster (capped at the
     number of K-groups): distributed-shared-memory reduction, uneven group and token slices, activation-ring wrap-around
     (VLUT_TCS_NAS=2), both drain policies, I2 (512-k groups) and I1 (640-k groups, odd sub-block count, 4-weight tail)."""
     a = api()
-    monkeypatch.setenv("VLUT_TCS_SPLIT", str(split))
-    monkeypatch.setenv("VLUT_TCS_NAS", "2" if split % 2 else "0")
-    monkeypatch.setenv("VLUT_TC_FAST", str(fast))
+    knobs(VLUT_TCS_SPLIT=split, VLUT_TCS_NAS=2 if split % 2 else 0, VLUT_TC_FAST=fast)
     for type_, K, N in [(O.I2_V_4, 4096, 640), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 129), (O.I1_V, 3072, 72),
                         (O.I2_V_4, 14336, 256)]:
         w = O.make_ternary(N, K, seed=split)
@@ -399,14 +390,15 @@ def test_gemm_on_a_workspace_quantised_for_another_kernel(ctx, orc, T):
     ref = orc.mul_mat(type_, packed, x, N)
     W = ctx.upload(type_, K, N, packed)
     xd = torch.from_numpy(x).cuda()
-    for algo in [a.ALGO_TC, a.ALGO_TCS, a.ALGO_SIMPLE, a.ALGO_TCS, a.ALGO_TC1, a.ALGO_AUTO]:
+    other = a.ALGO_TCP if T > 32 else a.ALGO_SIMPLE
+    for algo in [other, a.ALGO_TCS, a.ALGO_SIMPLE, a.ALGO_TCS, a.ALGO_AUTO]:
         ctx.quantize_act(type_, xd)
         out = ctx.gemm(W, T, algo=algo)
         torch.cuda.synchronize()
         assert np.array_equal(bits(out.cpu().numpy()), bits(ref)), f"algo={algo}"
-        out2 = ctx.gemm(W, T, algo=a.ALGO_TC)   # and back, on the same quantisation
+        out2 = ctx.gemm(W, T, algo=other)   # and back, on the same quantisation
         torch.cuda.synchronize()
-        assert np.array_equal(bits(out2.cpu().numpy()), bits(ref)), f"algo={algo} then tc"
+        assert np.array_equal(bits(out2.cpu().numpy()), bits(ref)), f"algo={algo} then {other}"
 
 
 def test_fused_scatter_epilogue_single_gpu_emulation(ctx, orc):
@@ -428,3 +420,146 @@ def test_fused_scatter_epilogue_single_gpu_emulation(ctx, orc):
     torch.cuda.synchronize()
     for b in bufs:
         assert np.array_equal(bits(b.cpu().numpy()), bits(ref))
+
+
+@pytest.mark.parametrize("T", [4, 16, 64])
+def test_inputs_visible_with_an_unrelated_matmul_in_between(orc, T):
+    """Programmatic-launch chains nest: in G1(->y1), Q2, G2(->y3), Q3(x = y1) the early-reading Q3 only orders itself after
+    G2's CTAs have STARTED, so it must not read y1 ahead of its dependency wait while G1 may still be storing it.  The
+    library remembers the output ranges of every GEMM in flight (not just the last one).  Small shape: G1 and G2 fit on
+    the GPU together."""
+    a = api()
+    c = a.Context(0)
+    c.set_option(a.Context.OPT_INPUTS_VISIBLE, 1)
+    type_, K = O.I2_V_4, 1024
+    packed = [orc.pack(type_, O.make_ternary(K, K, seed=s)) for s in (5, 6, 7)]
+    W = [c.upload(type_, K, K, p) for p in packed]
+    x0, x1 = O.make_acts(T, K, seed=8), O.make_acts(T, K, seed=9)
+    xd0, xd1 = torch.from_numpy(x0).cuda(), torch.from_numpy(x1).cuda()
+    y1, y2, y3 = (torch.empty((T, K), device="cuda") for _ in range(3))
+    r1 = orc.mul_mat(type_, packed[0], x0, K)
+    r3 = orc.mul_mat(type_, packed[1], x1, K)
+    r2 = orc.mul_mat(type_, packed[2], r1, K)
+    for rep in range(20):
+        y1.zero_()
+        torch.cuda.synchronize()
+        c.mul_mat(W[0], xd0, out=y1)      # G1 -> y1
+        c.mul_mat(W[1], xd1, out=y3)      # unrelated: Q2 (early), G2 -> y3
+        c.mul_mat(W[2], y1, out=y2)       # Q3 reads y1: early mode must be refused
+        torch.cuda.synchronize()
+        assert np.array_equal(bits(y2.cpu().numpy()), bits(r2)), f"rep {rep}"
+        assert np.array_equal(bits(y3.cpu().numpy()), bits(r3)), f"rep {rep}"
+    c.close()
+
+
+@pytest.mark.parametrize("T", [1, 3, 16, 40, 64, 200])
+@pytest.mark.parametrize("type_,K,Ns", [(O.I2_V_4, 4096, [256, 128, 128]), (O.I1_V_2, 3200, [520, 520]),
+                                        (O.I2_V, 1040, [129, 77, 300, 64, 130])])
+def test_mul_mat_batch_equals_separate_ops(ctx, orc, type_, K, Ns, T):
+    """vlut_mul_mat_batch: several weights on ONE activation tensor (Q/K/V, up/gate) -- one quantisation and, at T <= 64,
+    one launch of the streaming kernel over all strips -- is bit-identical to separate MUL_MATs (and to the oracle)."""
+    x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "normal")
+    xd = torch.from_numpy(x).cuda()
+    packed = [orc.pack(type_, O.make_ternary(n, K, seed=n)) for n in Ns]
+    W = [ctx.upload(type_, K, n, p) for n, p in zip(Ns, packed)]
+    scales = [1.0, 0.5, 1.25, 1.0, 3.0][: len(Ns)]
+    l0 = ctx.launch_count
+    outs = ctx.mul_mat_batch(W, xd, w_scales=scales)
+    n_launch = ctx.launch_count - l0
+    torch.cuda.synchronize()
+    for n, p, o, sc in zip(Ns, packed, outs, scales):
+        ref = orc.mul_mat(type_, p, x, n)
+        if sc != 1.0:
+            ref = ref * np.float32(sc)
+        assert np.array_equal(bits(o.cpu().numpy()), bits(ref)), f"N={n}"
+    if T <= 64 and len(Ns) <= 4:
+        assert n_launch <= 2, f"{n_launch} launches for one batch"   # quantise + one GEMM (or one fused kernel)
+
+
+@pytest.mark.parametrize("split", [0, 1, 2, 5])
+@pytest.mark.parametrize("T", [1, 2, 3, 4, 7, 8])
+def test_gemv_fused_quantise_kernel(ctx, orc, knobs, split, T):
+    """VLUT_ALGO_GEMV: the whole op in one launch on the CUDA cores (quantisation fused, K split over a cluster).  Forced
+    cluster sizes, ragged N, I1 tails (K % 20 != 0, K % 640 != 0), strided x, batch of weights."""
+    a = api()
+    knobs(VLUT_GEMV_SPLIT=split)
+    for type_, K, N in [(O.I2_V_4, 4096, 300), (O.I1_V_2, 3200, 130), (O.I2_V, 1040, 129), (O.I1_V, 3072, 72),
+                        (O.I2_V_4, 14336, 128), (O.I1_V_2, 8640, 64)]:
+        w = O.make_ternary(N, K, seed=K + split)
+        x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "outlier")
+        packed = orc.pack(type_, w)
+        ref = orc.mul_mat(type_, packed, x, N)
+        W = ctx.upload(type_, K, N, packed)
+        buf = torch.zeros((T, K + 64), device="cuda")
+        buf[:, :K] = torch.from_numpy(x).cuda()
+        out = ctx.mul_mat(W, buf[:, :K], algo=a.ALGO_GEMV)
+        torch.cuda.synchronize()
+        assert a.ALGO_NAMES[ctx.last_algo] == "gemv"
+        bad = bits(out.cpu().numpy()) != bits(ref)
+        assert not bad.any(), f"type={type_} K={K}: {bad.sum()} of {bad.size} differ, first at {np.argwhere(bad)[0]}"
+    # int16 wrap inside every K-group
+    K, N = 2048, 144
+    wv = np.ones((N, K), dtype=np.float32)
+    wv[::3] = -1.0
+    xv = O.make_acts(T, K, kind="ones")
+    xv[1::2] *= -1.0
+    pk = orc.pack(O.I2_V_4, wv)
+    out = ctx.mul_mat(ctx.upload(O.I2_V_4, K, N, pk), torch.from_numpy(xv).cuda(), algo=a.ALGO_GEMV)
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(out.cpu().numpy()), bits(orc.mul_mat(O.I2_V_4, pk, xv, N)))
+
+
+def test_op_supported_mirrors_the_launch_path(ctx):
+    a = api()
+    assert a.op_supported(O.I2_V_4, 4096, 14336, 512)
+    assert a.op_supported(O.I1_V_2, 3200, 8640, 1)
+    assert not a.op_supported(O.I2_V_4, 4104, 16, 1)          # K % 16 != 0 (the reference packer would overrun)
+    assert not a.op_supported(O.I2_V_4, 65536, 16, 1)         # more than 64 K-groups
+    assert not a.op_supported(7, 4096, 16, 1)                 # not a vlut type
+    assert a.op_supported(O.I2_V_4, 32768, 16, 1)
+
+
+def test_barrier_kernel_two_ranks_emulated_on_one_gpu():
+    """vlut_barrier with the two 'ranks' as two contexts (two streams) on ONE GPU: each waits for the other's flag; the
+    epoch lives on the device, so repeated calls (and graph replays) stay in step."""
+    a = api()
+    s0, s1 = torch.cuda.Stream(), torch.cuda.Stream()
+    c0, c1 = a.Context(0, stream=s0), a.Context(0, stream=s1)
+    flags = [torch.zeros(16, dtype=torch.int32, device="cuda") for _ in range(2)]
+    ptrs = [f.data_ptr() for f in flags]
+    torch.cuda.synchronize()
+    for rep in range(5):
+        c0.barrier(ptrs, 0)
+        c1.barrier(ptrs, 1)
+    torch.cuda.synchronize()
+    for r, f in enumerate(flags):
+        h = f.cpu().numpy()
+        assert h[0] == 5 and h[1] == 5 and h[8] == 5, (r, h)
+    c0.close()
+    c1.close()
+
+
+@pytest.mark.parametrize("vec", [1, 0])
+@pytest.mark.parametrize("T,N,bounds", [(40, 640, [0, 384, 640]), (130, 1000, [0, 512, 1000]), (16, 262, [0, 128, 262]),
+                                        (200, 390, [0, 130, 390])])
+def test_fused_scatter_vector_stores(ctx, orc, knobs, vec, T, N, bounds):
+    """The scatter epilogue with 16-byte stores (four rows per lane after a 4 x 4 lane transpose): aligned shards, ragged
+    row tails (N % 4 != 0), a shard whose first column is not 16-byte aligned (scalar fallback), and VLUT_SCATTER_VEC=0."""
+    a = api()
+    knobs(VLUT_SCATTER_VEC=vec)
+    type_, K = O.I2_V_4, 2048
+    w = O.make_ternary(N, K, seed=N)
+    x = O.make_acts(T, K, seed=T)
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    xd = torch.from_numpy(x).cuda()
+    ld = (N + 3) // 4 * 4
+    bufs = [torch.zeros((T, ld), device="cuda") for _ in range(2)]
+    for g in range(2):
+        r0, rows = bounds[g], bounds[g + 1] - bounds[g]
+        Wg = ctx.upload(type_, K, rows, a.shard_rows(type_, K, N, r0, rows, packed))
+        ctx.mul_mat_scatter(Wg, xd, peers=[b.data_ptr() for b in bufs], multicast_ptr=0, ldo=ld, col0=r0)
+    torch.cuda.synchronize()
+    for b in bufs:
+        assert np.array_equal(bits(b[:, :N].cpu().numpy()), bits(ref))
+        assert (b[:, N:] == 0).all()

@@ -48,9 +48,15 @@ _SIGNATURES = {
     "vlut_gemm": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, f32, cint]),
     "vlut_mul_mat": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_mul_mat_scatter": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, cint, cint, i64, f32, cint]),
+    "vlut_barrier": (cint, [vp, vp, cint, cint]),
     "vlut_mul_mat_host": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_scale_rows": (cint, [vp, vp, i64, vp, i64, i64, i64, f32]),
     "vlut_pick_algo": (cint, [cint, i64, i64, i64]),
+    "vlut_op_supported": (cint, [cint, i64, i64, i64]),
+    "vlut_reload_env": (cint, []),
+    "vlut_measure_int8_peak": (cint, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "vlut_mul_mat_batch": (cint, [vp, cint, vp, i64, vp, i64, vp, vp, i64, vp, vp, vp, cint]),
+    "vlut_gemm_batch": (cint, [vp, cint, vp, i64, vp, i64, vp, vp, vp, vp, cint]),
     "vlut_debug_get_act": (cint, [vp, i64, i64, vp, vp]),
     "vlut_debug_unpack_t2": (cint, [vp, cint, i64, i64, vp, vp]),
     "vlut_debug_tc_counters": (cint, [vp, cint]),

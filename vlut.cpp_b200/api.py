@@ -23,8 +23,17 @@ I2_V, I2_V_4, I2_V_8, I1_V, I1_V_2 = 40, 42, 43, 45, 46
 TYPE_NAMES = {I2_V: "I2_V", I2_V_4: "I2_V_4", I2_V_8: "I2_V_8", I1_V: "I1_V", I1_V_2: "I1_V_2"}
 TYPE_BY_NAME = {v: k for k, v in TYPE_NAMES.items()}
 
-ALGO_AUTO, ALGO_SIMPLE, ALGO_TC, ALGO_LUT, ALGO_TC1, ALGO_TC2, ALGO_TCP, ALGO_TCS = 0, 1, 3, 4, 5, 6, 7, 8
-ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_TC: "tc", ALGO_LUT: "lut", ALGO_TC1: "tc1", ALGO_TC2: "tc2", ALGO_TCP: "tcp", ALGO_TCS: "tcs"}
+ALGO_AUTO, ALGO_SIMPLE, ALGO_LUT, ALGO_TCP, ALGO_TCS, ALGO_GEMV = 0, 1, 4, 7, 8, 9
+ALGO_NAMES = {ALGO_AUTO: "auto", ALGO_SIMPLE: "simple", ALGO_LUT: "lut", ALGO_TCP: "tcp", ALGO_TCS: "tcs", ALGO_GEMV: "gemv"}
+
+
+def reload_env() -> None:
+    """Make the library re-read its VLUT_* environment knobs (they are resolved once, never on the launch path)."""
+    check(_lib.lib().vlut_reload_env(), "vlut_reload_env")
+
+
+def op_supported(type_: int, K: int, N: int, T: int) -> bool:
+    return bool(_lib.lib().vlut_op_supported(type_, K, N, T))
 
 
 def nbytes(type_: int, K: int, N: int) -> int:
@@ -165,6 +174,25 @@ class Context:
                                       out.data_ptr(), out.stride(0), w_scale, algo), "vlut_mul_mat")
         return out
 
+    def mul_mat_batch(self, ws: list[Weight], x: torch.Tensor, outs: list[torch.Tensor] | None = None,
+                      w_scales: list[float] | None = None, algo: int = ALGO_AUTO) -> list[torch.Tensor]:
+        """Several weights on ONE activation tensor (Q/K/V, up/gate): one quantisation, one launch at small T."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1
+        T, K = x.shape
+        n = len(ws)
+        assert n >= 1 and all(w.K == K for w in ws)
+        if outs is None:
+            outs = [torch.empty((T, w.N), dtype=torch.float32, device=self.device) for w in ws]
+        types = (C.c_int * n)(*[w.type for w in ws])
+        Ns = (C.c_int64 * n)(*[w.N for w in ws])
+        t2 = (C.c_void_p * n)(*[w.t2.data_ptr() for w in ws])
+        op = (C.c_void_p * n)(*[o.data_ptr() for o in outs])
+        ldos = (C.c_int64 * n)(*[o.stride(0) for o in outs])
+        sc = (C.c_float * n)(*(w_scales or [1.0] * n))
+        check(_lib.lib().vlut_mul_mat_batch(self._h, n, types, K, Ns, T, t2, x.data_ptr(), x.stride(0), op, ldos, sc, algo),
+              "vlut_mul_mat_batch")
+        return outs
+
     def mul_mat_scatter(self, w: Weight, x: torch.Tensor, peers: list[int], multicast_ptr: int, ldo: int, col0: int,
                         w_scale: float = 1.0, algo: int = ALGO_AUTO) -> None:
         """Row-sharded op with the all-gather fused into the epilogue: this rank's [T][w.N] slice is stored at column
@@ -180,6 +208,11 @@ class Context:
         check(_lib.lib().vlut_mul_mat_scatter(self._h, w.type, w.K, w.N, T, w.t2.data_ptr(), x.data_ptr(), x.stride(0), arr,
                                               len(ptrs), 1 if multicast_ptr else 0, ldo, w_scale, algo),
               "vlut_mul_mat_scatter")
+
+    def barrier(self, flag_ptrs: list[int], rank: int) -> None:
+        """vlut_barrier: publish a fused all-gather across ranks (flag_ptrs[i] = rank i's peer-visible flag array)."""
+        arr = (C.c_void_p * len(flag_ptrs))(*flag_ptrs)
+        check(_lib.lib().vlut_barrier(self._h, arr, len(flag_ptrs), rank), "vlut_barrier")
 
     def scale_rows(self, x: torch.Tensor, scale: float, out: torch.Tensor | None = None) -> torch.Tensor:
         """out[t][n] = x[t][n] * scale (one fp32 rounding): GGML_OP_MUL by a one-element tensor, the weight's `.scale`
@@ -203,6 +236,12 @@ class Context:
                                            x_host.stride(0), out_host.data_ptr(), out_host.stride(0), w_scale, algo),
               "vlut_mul_mat_host")
         return out_host
+
+    def measure_int8_peak(self) -> tuple[float, float]:
+        """(TOP/s over the device, SM clocks per M128 N256 K32 MMA) of a tcgen05.mma kind::i8 issue loop on every SM."""
+        tops, clk = C.c_double(0), C.c_double(0)
+        check(_lib.lib().vlut_measure_int8_peak(self._h, C.byref(tops), C.byref(clk)), "vlut_measure_int8_peak")
+        return tops.value, clk.value
 
     def sync(self) -> None:
         check(_lib.lib().vlut_ctx_sync(self._h), "vlut_ctx_sync")

@@ -26,6 +26,63 @@ static int cuda_fail(cudaError_t e, const char *what) {
         if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
     } while (0)
 
+// ---- run-time knobs: the environment is read here and nowhere else -------------------------------------------------
+static int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+static Knobs g_knobs;
+static bool g_knobs_loaded = false;
+namespace vlut {
+void knobs_reload() {
+    Knobs k{};
+    k.algo = env_int("VLUT_B200_ALGO", 0);
+    k.host_chunk = env_int("VLUT_HOST_CHUNK", 128);
+    if (k.host_chunk < 0) k.host_chunk = 0;
+    k.pdl = env_int("VLUT_PDL", 1);
+    k.tc_fast = env_int("VLUT_TC_FAST", 1);
+    k.tc_smem_kb = env_int("VLUT_TC_SMEM_KB", 200);
+    k.tc_stages = env_int("VLUT_TC_STAGES", 0);
+    k.tc_grid = env_int("VLUT_TC_GRID", 0);
+    k.tc_whole = env_int("VLUT_TC_WHOLE", -1);
+    k.tc_split_last = env_int("VLUT_TC_SPLIT_LAST", 0);
+    k.tc_abl = env_int("VLUT_TC_ABL", 0);
+    k.tc_debug = env_int("VLUT_TC_DEBUG", 0);
+    k.tc_debug_skip = env_int("VLUT_TC_DEBUG_SKIP", 0);
+    k.tc_nt = env_int("VLUT_TC_NT", 0);
+    k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
+    k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
+    k.tcs_issuers = env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
+    k.tcs_depth = env_int("VLUT_TCS_DEPTH", 3);
+    k.tcs_dbg_cta = env_int("VLUT_TCS_DBG_CTA", 0);
+    k.tcs_dbg_mask = env_int("VLUT_TCS_DBG_MASK", 15);
+    k.quant_2pass = env_int("VLUT_QUANT_2PASS", 0);
+    k.quant_pdl = env_int("VLUT_QUANT_PDL", -1);
+    k.quant_early = env_int("VLUT_QUANT_EARLY", -1);
+    k.quant_tpc = env_int("VLUT_QUANT_TPC", 0);
+    k.scatter_vec = env_int("VLUT_SCATTER_VEC", 1);
+    k.gemv_split = env_int("VLUT_GEMV_SPLIT", 0);
+    k.gemv_max_t = env_int("VLUT_GEMV_MAX_T", -1);
+    g_knobs = k;
+    g_knobs_loaded = true;
+}
+const Knobs &knobs() {
+    if (!g_knobs_loaded) knobs_reload();
+    return g_knobs;
+}
+
+// zeroed debug buffer shared by the kernels' optional instrumentation (VLUT_TC_DEBUG=1); word 0 = events to skip
+constexpr int DBG_WORDS = 256 * 4 * 8 + 4 * 24 * 2;
+static long long *g_dbg_buf = nullptr;
+long long *debug_buffer(cudaStream_t s, int skip) {
+    if (!g_dbg_buf && cudaMalloc(&g_dbg_buf, DBG_WORDS * sizeof(long long)) != cudaSuccess) return nullptr;
+    cudaMemsetAsync(g_dbg_buf, 0, DBG_WORDS * sizeof(long long), s);
+    const long long sk = skip;
+    cudaMemcpyAsync(g_dbg_buf, &sk, sizeof(sk), cudaMemcpyHostToDevice, s);
+    return g_dbg_buf;
+}
+}  // namespace vlut
+
 struct DevBuf {
     void *p = nullptr;
     size_t cap = 0;
@@ -59,12 +116,21 @@ struct vlut_ctx {
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
+    bool act_rm_valid = false;  // q_rm holds the current quantisation (written by the quantiser or materialised from q_sw)
     int64_t launches = 0;
     int last_algo = 0;
     uint32_t epoch = 0;  // quantisation call counter (ActView.epoch)
     // vlut_mul_mat_host pipeline: one copy stream per PCIe direction and one event pair per token chunk
     int inputs_visible = 0;  // VLUT_OPT_INPUTS_VISIBLE
-    const char *last_out_lo = nullptr, *last_out_hi = nullptr;  // output range of the GEMM launched last (nullptr: unknown)
+    // Early-read bookkeeping (VLUT_OPT_INPUTS_VISIBLE).  Every kernel of this library signals launch_dependents at its
+    // first instruction, so programmatic-launch chains NEST: a quantise kernel that reads x ahead of its dependency wait
+    // may run while ANY kernel launched since the last fully serialising launch (one without the programmatic attribute,
+    // or a stream sync) is still storing.  `inflight` holds the output ranges of the GEMMs launched since that point;
+    // `inflight_unknown` says some launch since then wrote a range we do not know (scatter epilogue, scale_rows, ...).
+    struct Range { const char *lo, *hi; };
+    std::vector<Range> inflight;
+    bool inflight_unknown = true;
+    bool last_was_gemm = false;
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_done;
 };
@@ -119,9 +185,15 @@ int vlut_device_info(int device, char *name, size_t name_len, size_t *free_bytes
     return VLUT_OK;
 }
 
+int vlut_reload_env(void) {
+    knobs_reload();
+    return VLUT_OK;
+}
+
 int vlut_ctx_create(int device, void *stream, vlut_ctx **out) {
     if (!out) return VLUT_ERR_INVALID;
     *out = nullptr;
+    knobs_reload();
     int n = 0;
     CK(cudaGetDeviceCount(&n));
     if (device < 0 || device >= n) return VLUT_ERR_INVALID;
@@ -171,6 +243,8 @@ void *vlut_ctx_stream(vlut_ctx *c) { return c ? (void *) c->stream : nullptr; }
 int vlut_ctx_sync(vlut_ctx *c) {
     if (!c) return VLUT_ERR_INVALID;
     CK(cudaStreamSynchronize(c->stream));
+    c->inflight.clear();
+    c->inflight_unknown = false;
     return VLUT_OK;
 }
 
@@ -222,6 +296,11 @@ int vlut_dev_memset(vlut_ctx *c, void *dst_dev, int value, size_t nbytes) {
 }
 
 static int check_shape(int type, int64_t K, int64_t N);
+// a kernel of ours that writes memory the early-read bookkeeping does not track was just launched
+static void note_foreign_write(vlut_ctx *c) {
+    c->inflight_unknown = true;
+    c->last_was_gemm = false;
+}
 
 size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N) {
     if (check_shape(type, K, N) != VLUT_OK) return 0;
@@ -246,7 +325,7 @@ int vlut_repack_weights(vlut_ctx *c, int type, int64_t K, int64_t N, const void 
     int rc = check_shape(type, K, N);
     if (rc) return rc;
     CK(cudaSetDevice(c->device));
-    c->last_out_lo = c->last_out_hi = nullptr;
+    note_foreign_write(c);
     CK(launch_repack(type, K, N, (const uint8_t *) gguf_dev, (uint8_t *) t2_dev, c->stream));
     c->launches++;
     return VLUT_OK;
@@ -328,82 +407,176 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo) {
     return VLUT_OK;
 }
 
+// Launch policy of the quantise kernel (measured on the quantise + GEMM chain at 4096 -> 14336, scripts/time_op.py):
+//   pdl    programmatic launch behind the previous GEMM: gains 0.1-0.5 us for T <= 64 and from T = 1024 up, loses 1.6-2 us
+//          in between
+//   early  programmatic launch with the row loads, maximum and scale AHEAD of the dependency wait: only where the host can
+//          prove that no kernel still in flight writes x (early_ok) and where it measured faster (T <= 64, 512 <= T <= 1024)
+struct QuantPolicy { bool pdl, early; };
+static QuantPolicy quant_policy(int64_t T, bool early_ok, bool opted_in) {
+    const Knobs &k = knobs();
+    QuantPolicy q{false, false};
+    if (!k.pdl) return q;
+    if (early_ok) {
+        if (k.quant_early >= 0) q.early = k.quant_early != 0;    // VLUT_QUANT_EARLY=1: experiment without the option
+        else q.early = opted_in && (T <= 64 || (T >= 512 && T <= 1024));
+    }
+    q.pdl = q.early || (k.quant_pdl >= 0 ? k.quant_pdl != 0 : (T <= 64 || T > 512));
+    return q;
+}
+
 // quantise for the kernel `algo` resolves to (the CTA-pair kernel wants half-height swizzled tiles)
-static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T, int algo) {
+static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T, int algo, int64_t N_hint) {
     if (!c || !x_dev || T <= 0 || ldx < K) return VLUT_ERR_INVALID;
     if (!type_valid(type) || K <= 0 || K % 4) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
-    if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, 1, T);
+    if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, N_hint, T);
     int rc = prepare_act(c, type, K, T, algo);
     if (rc) return rc;
-    // the last kernel this context launched was a GEMM whose output range is known and does not meet x
+    // x is not written by any kernel of this context that may still be running: the last launch was a GEMM and the
+    // output ranges of every GEMM launched since the last fully serialising launch are known and do not meet x
     const char *xl = (const char *) x_dev, *xh = xl + ((size_t) (T - 1) * ldx + K) * sizeof(float);
-    const bool untouched = c->last_out_lo && (xh <= c->last_out_lo || xl >= c->last_out_hi);
-    c->last_out_lo = c->last_out_hi = nullptr;
-    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, untouched ? (c->inputs_visible ? 1 : 2) : 0));
+    bool untouched = c->last_was_gemm && !c->inflight_unknown;
+    for (const vlut_ctx::Range &r : c->inflight) untouched = untouched && (xh <= r.lo || xl >= r.hi);
+    const QuantPolicy qp = quant_policy(T, untouched, c->inputs_visible != 0);
+    // q_rm (row-major copy) is only written for the kernels that read it; otherwise it is materialised on demand
+    const bool want_rm = (algo == VLUT_ALGO_SIMPLE || algo == VLUT_ALGO_LUT);
+    CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, qp.pdl, qp.early, want_rm));
+    c->act_rm_valid = want_rm;
     c->launches++;
+    c->last_was_gemm = false;
+    if (!qp.pdl) {   // launched without the programmatic attribute: starts after everything before it has completed
+        c->inflight.clear();
+        c->inflight_unknown = false;
+    }
+    return VLUT_OK;
+}
+
+// the row-major copy of the quantised activations (anchor kernel, LUT candidate, re-tiling, test read-back)
+static int ensure_q_rm(vlut_ctx *c) {
+    if (c->act_rm_valid) return VLUT_OK;
+    CK(launch_unswizzle(c->act, c->stream));
+    c->launches++;
+    c->act_rm_valid = true;
+    c->inflight.clear();           // plain launch: serialises the stream
+    c->inflight_unknown = false;
+    c->last_was_gemm = false;
     return VLUT_OK;
 }
 
 int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
-    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO);
+    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO, 1);
 }
 
+int vlut_op_supported(int type, int64_t K, int64_t N, int64_t T) {
+    if (check_shape(type, K, N) != VLUT_OK || T <= 0) return 0;
+    if (ceil_div(K, group_size(type)) > 64) return 0;   // prepare_act: at most 64 K-groups (K <= 32768 I2*, 40960 I1*)
+    return 1;
+}
+
+// AUTO runs the CUDA-core GEMV (quantisation fused, one launch) up to this many tokens (measured crossover)
+constexpr int GEMV_MAX_T_DEFAULT = 0;
+
 int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T) {
-    // crossover table from measurements on B200 (profiles/, DESIGN.md section "crossover")
-    const char *v = getenv("VLUT_B200_ALGO");
-    const int forced = v ? atoi(v) : 0;
+    const int forced = knobs().algo;
     if (forced > 0) return forced;
     // crossover table from B200 measurements (profiles/):
+    //   T <= 4    GEMV (CUDA cores: register decode + dp4a, split-K, quantisation fused) where it measured faster
     //   T <= 64   TCS  (per-thread cp.async weight stream, 16 decode warps, two MMA issuers, cluster split-K)
-    //   T  > 64   TCP  (CTA pairs, cta_group::2: each CTA stages half of the 128-token tile -> half the activation fill)
-    // TC (one CTA per strip, TMA weight stream), TC1 / TC2 (earlier generations) stay selectable for comparison.
+    //   T  > 64   TCP  (CTA pairs, cta_group::2: each CTA stages half of the token tile -> half the activation fill)
+    const int gemv_max = knobs().gemv_max_t >= 0 ? knobs().gemv_max_t : GEMV_MAX_T_DEFAULT;
+    if (T <= gemv_max && T <= 8 && vlut_op_supported(type, K, N, T)) return VLUT_ALGO_GEMV;
     if (T <= 64 && gemm_tcs_supported(type, K, N, T)) return VLUT_ALGO_TCS;
     if (T > 64 && gemm_tc5_supported(type, K, N, T)) return VLUT_ALGO_TCP;
-    if (gemm_tc4_supported(type, K, N, T)) return VLUT_ALGO_TC;
-    if (gemm_tc_supported(type, K, N, T)) return VLUT_ALGO_TC1;
     return VLUT_ALGO_SIMPLE;
 }
 
-static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev,
-                     float *const *outs, int n_out, int multicast, int64_t ldo, float w_scale, int algo) {
-    if (!c || !t2_dev || (!out_dev && n_out <= 0) || T <= 0 || ldo < N || n_out > 8) return VLUT_ERR_INVALID;
-    int rc = check_shape(type, K, N);
-    if (rc) return rc;
-    if (c->act_K != K || c->act_T != T || group_size(c->act_type) != group_size(type)) return VLUT_ERR_INVALID;
+// One launch over up to MAX_BATCH weights that share the quantised activations (Q/K/V on one attention input, up/gate on
+// one FFN input: consecutive build_lora_mm calls on one tensor, src/models/bitnet.cpp:28-60, src/llama-graph.cpp:668-671).
+struct GemmCall {
+    int type;
+    int64_t N;
+    const void *t2;
+    float *out;
+    int64_t ldo;
+    float w_scale;
+};
+
+static int gemm_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, int ncalls, float *const *outs, int n_out,
+                     int multicast, int algo) {
+    if (!c || !calls || ncalls < 1 || ncalls > MAX_BATCH || T <= 0 || n_out > 8) return VLUT_ERR_INVALID;
+    if (ncalls > 1 && n_out > 0) return VLUT_ERR_UNSUPPORTED;
+    int64_t Nsum = 0;
+    for (int i = 0; i < ncalls; i++) {
+        const GemmCall &q = calls[i];
+        if (!q.t2 || (!q.out && n_out <= 0) || q.ldo < q.N) return VLUT_ERR_INVALID;
+        int rc = check_shape(q.type, K, q.N);
+        if (rc) return rc;
+        if (group_size(c->act_type) != group_size(q.type)) return VLUT_ERR_INVALID;
+        Nsum += round_up(q.N, TILE_ROWS);
+    }
+    if (c->act_K != K || c->act_T != T) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
     if (algo == VLUT_ALGO_AUTO) {
-        algo = vlut_pick_algo(type, K, N, T);
-        if (n_out > 0 && algo == VLUT_ALGO_TC1) algo = VLUT_ALGO_TC;  // TC1 has no scatter epilogue
+        algo = vlut_pick_algo(calls[0].type, K, Nsum, T);
+        if (algo == VLUT_ALGO_GEMV) algo = VLUT_ALGO_TCS;   // stage 2 alone: the GEMV kernel is the whole op (it quantises x itself)
+    }
+    if (algo == VLUT_ALGO_GEMV) return VLUT_ERR_UNSUPPORTED;
+    // only the small-T streaming kernel walks several weights in one launch; everything else runs them back to back
+    if (ncalls > 1 && algo != VLUT_ALGO_TCS) {
+        for (int i = 0; i < ncalls; i++) {
+            int rc = gemm_impl(c, K, T, calls + i, 1, nullptr, 0, 0, algo);
+            if (rc) return rc;
+        }
+        return VLUT_OK;
     }
 
     GemmArgs g{};
-    g.w = (const uint8_t *) t2_dev;
     g.act = c->act;
-    g.out = out_dev;
     g.n_out = n_out > 0 ? n_out : 0;
     g.multicast = multicast;
-    for (int i = 0; i < g.n_out; i++) g.outs[i] = outs[i];
-    g.ldo = ldo;
+    g.vec_ok = (g.n_out > 0 && calls[0].ldo % 4 == 0) ? 1 : 0;
+    for (int i = 0; i < g.n_out; i++) {
+        g.outs[i] = outs[i];
+        if (reinterpret_cast<uintptr_t>(outs[i]) & 15) g.vec_ok = 0;
+    }
+    if (knobs().scatter_vec == 0) g.vec_ok = 0;
     g.K = K;
-    g.N = N;
     g.T = T;
-    g.Npad = round_up(N, TILE_ROWS);
-    g.type = type;
-    g.w_scale = w_scale;
     g.sm_count = c->sm_count;
+    g.device = c->device;
+    g.n_tens = ncalls;
+    int strips = 0;
+    for (int i = 0; i < ncalls; i++) {
+        TensorRef &t = g.tens[i];
+        t.w = (const uint8_t *) calls[i].t2;
+        t.out = calls[i].out;
+        t.N = calls[i].N;
+        t.ldo = calls[i].ldo;
+        t.w_scale = calls[i].w_scale;
+        t.strip0 = strips;
+        strips += (int) (round_up(t.N, TILE_ROWS) / TILE_ROWS);
+    }
+    g.tens[ncalls].strip0 = strips;   // sentinel
+    // single-tensor view (every kernel but TCS reads these)
+    g.w = g.tens[0].w;
+    g.out = g.tens[0].out;
+    g.ldo = g.tens[0].ldo;
+    g.N = g.tens[0].N;
+    g.Npad = round_up(g.N, TILE_ROWS);
+    g.type = calls[0].type;
+    g.w_scale = g.tens[0].w_scale;
 
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP ||
-        algo == VLUT_ALGO_LUT) {
-        // stream-K workspace: two private partial-tile slots per persistent CTA (no initialisation needed) and
-        // self-resetting per-tile arrival counters (zeroed once at (re)allocation)
+    if (algo == VLUT_ALGO_TCP || algo == VLUT_ALGO_LUT) {
+        // stream-K workspace: private partial-tile slots per persistent CTA (no initialisation needed), self-resetting
+        // per-tile arrival counters and accumulation tiles (zeroed once at (re)allocation)
         bool grew = false;
-        const size_t pb = (size_t) c->sm_count * 6 * 128 * 128 * sizeof(int32_t);  // 4 partial-tile slots + 2 scratch per CTA
+        const size_t pb = (size_t) c->sm_count * 6 * 128 * 128 * sizeof(int32_t);
         if (c->part.reserve(pb) != cudaSuccess) return VLUT_ERR_NOMEM;
         const size_t cb = (size_t) ((g.Npad / TILE_ROWS + 1) * (c->act.Tpad / c->act.NT)) * sizeof(int32_t);
         if (c->counters.reserve(cb, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->counters.p, 0, c->counters.cap, c->stream));
-        const size_t ab = (size_t) c->sm_count * 128 * 128 * sizeof(int32_t);
+        const size_t ab = (size_t) c->sm_count * 128 * 256 * sizeof(int32_t);
         if (c->acc.reserve(ab, &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
         if (grew) CK(cudaMemsetAsync(c->acc.p, 0, c->acc.cap, c->stream));
         g.acc = (int32_t *) c->acc.p;
@@ -412,18 +585,25 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     }
 
     int launches = 0;
+    bool plain_launch = false;   // some kernel went out without the programmatic attribute (serialises the stream)
     cudaError_t e;
-    if (algo == VLUT_ALGO_TC || algo == VLUT_ALGO_TC1 || algo == VLUT_ALGO_TC2 || algo == VLUT_ALGO_TCP ||
-        algo == VLUT_ALGO_TCS) {
-        // the workspace was quantised for another kernel's swizzled-tile height: rewrite q_sw from q_rm
+    if (algo == VLUT_ALGO_TCP || algo == VLUT_ALGO_TCS) {
+        // the workspace was quantised for another kernel's swizzled-tile layout: rewrite q_sw (through q_rm)
         const int want = want_sw_tile(algo, c->act.NT), wantp = want_perm(algo, c->act.NT);
         if (c->act.sw_tile != want || c->act.perm != wantp) {
+            int rc = ensure_q_rm(c);
+            if (rc) return rc;
             c->act.sw_tile = want;
             c->act.perm = wantp;
             CK(launch_relayout(c->act, c->stream));
             launches++;
+            plain_launch = true;
         }
         g.act = c->act;
+    } else if (algo == VLUT_ALGO_SIMPLE || algo == VLUT_ALGO_LUT) {
+        int rc = ensure_q_rm(c);
+        if (rc) return rc;
+        plain_launch = true;
     }
     switch (algo) {
         case VLUT_ALGO_SIMPLE:
@@ -431,28 +611,16 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
             e = launch_gemm_simple(g, c->stream);
             launches += 1;
             break;
-        case VLUT_ALGO_TC:
-            if (!gemm_tc4_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
-            e = launch_gemm_tc4(g, c->stream, &launches);
-            break;
         case VLUT_ALGO_TCS:
-            if (!gemm_tcs_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            if (!gemm_tcs_supported(g.type, K, g.N, T)) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tcs(g, c->stream, &launches);
             break;
-        case VLUT_ALGO_TC2:
-            if (!gemm_tc3_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
-            e = launch_gemm_tc3(g, c->stream, &launches);
-            break;
         case VLUT_ALGO_TCP:
-            if (!gemm_tc5_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            if (!gemm_tc5_supported(g.type, K, g.N, T)) return VLUT_ERR_UNSUPPORTED;
             e = launch_gemm_tc5(g, c->stream, &launches);
             break;
-        case VLUT_ALGO_TC1:
-            if (!gemm_tc_supported(type, K, N, T) || g.n_out) return VLUT_ERR_UNSUPPORTED;
-            e = launch_gemm_tc(g, c->stream, &launches);
-            break;
         case VLUT_ALGO_LUT:
-            if (!gemm_lut_supported(type, K, N, T)) return VLUT_ERR_UNSUPPORTED;
+            if (!gemm_lut_supported(g.type, K, g.N, T) || g.n_out) return VLUT_ERR_UNSUPPORTED;
             // the LUT candidate accumulates with atomics into the (shared) workspace: hand it a zeroed region
             if ((size_t) (16 * g.Npad) * sizeof(int32_t) > c->part.cap) return VLUT_ERR_UNSUPPORTED;
             CK(cudaMemsetAsync(c->part.p, 0, (size_t) (16 * g.Npad) * sizeof(int32_t), c->stream));
@@ -464,31 +632,163 @@ static int gemm_impl(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, con
     if (e != cudaSuccess) return cuda_fail(e, "gemm launch");
     c->launches += launches;
     c->last_algo = algo;
-    c->last_out_lo = c->last_out_hi = nullptr;
-    if (out_dev && n_out == 0) {
-        c->last_out_lo = (const char *) out_dev;
-        c->last_out_hi = c->last_out_lo + ((size_t) (T - 1) * ldo + N) * sizeof(float);
+    // early-read bookkeeping: the output ranges now in flight
+    if (plain_launch || !knobs().pdl || algo == VLUT_ALGO_SIMPLE || algo == VLUT_ALGO_LUT) {
+        c->inflight.clear();
+        c->inflight_unknown = false;
+    }
+    c->last_was_gemm = true;
+    if (n_out > 0 || c->inflight.size() >= 8) {
+        c->inflight_unknown = true;
+    } else {
+        for (int i = 0; i < ncalls; i++) {
+            const char *lo = (const char *) calls[i].out;
+            c->inflight.push_back({lo, lo + ((size_t) (T - 1) * calls[i].ldo + calls[i].N) * sizeof(float)});
+        }
     }
     return VLUT_OK;
 }
 
+// the whole op in ONE launch on the CUDA cores (quantisation fused): does not touch the activation workspace
+static int gemv_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, int ncalls, const float *x_dev, int64_t ldx) {
+    if (!c || !calls || !x_dev || ncalls < 1 || ncalls > MAX_BATCH || T <= 0 || ldx < K) return VLUT_ERR_INVALID;
+    GemmArgs g{};
+    g.K = K;
+    g.T = T;
+    g.sm_count = c->sm_count;
+    g.device = c->device;
+    g.n_tens = ncalls;
+    int strips = 0;
+    for (int i = 0; i < ncalls; i++) {
+        const GemmCall &q = calls[i];
+        if (!q.t2 || !q.out || q.ldo < q.N) return VLUT_ERR_INVALID;
+        int rc = check_shape(q.type, K, q.N);
+        if (rc) return rc;
+        if (group_size(q.type) != group_size(calls[0].type)) return VLUT_ERR_INVALID;
+        g.tens[i] = TensorRef{(const uint8_t *) q.t2, q.out, q.N, q.ldo, q.w_scale, strips};
+        strips += (int) (round_up(q.N, TILE_ROWS) / TILE_ROWS);
+    }
+    g.tens[ncalls].strip0 = strips;
+    g.type = calls[0].type;
+    g.N = calls[0].N;
+    if (!gemm_gemv_supported(g.type, K, g.N, T, x_dev, ldx)) return VLUT_ERR_UNSUPPORTED;
+    CK(cudaSetDevice(c->device));
+    int launches = 0;
+    cudaError_t e = launch_gemm_gemv(g, x_dev, ldx, c->stream, &launches);
+    if (e != cudaSuccess) return cuda_fail(e, "gemv launch");
+    c->launches += launches;
+    c->last_algo = VLUT_ALGO_GEMV;
+    c->act_T = 0;   // the workspace holds no quantisation of this x
+    c->last_was_gemm = true;
+    if (!knobs().pdl) {
+        c->inflight.clear();
+        c->inflight_unknown = false;
+    }
+    if (c->inflight.size() >= 8) {
+        c->inflight_unknown = true;
+    } else {
+        for (int i = 0; i < ncalls; i++) {
+            const char *lo = (const char *) calls[i].out;
+            c->inflight.push_back({lo, lo + ((size_t) (T - 1) * calls[i].ldo + calls[i].N) * sizeof(float)});
+        }
+    }
+    return VLUT_OK;
+}
+
+// AUTO -> GEMV only where the kernel can run (aligned rows); a forced GEMV that cannot run reports UNSUPPORTED
+static bool use_gemv(int *algo, int type, int64_t K, int64_t Nsum, int64_t T, const float *x_dev, int64_t ldx) {
+    const bool was_auto = (*algo == VLUT_ALGO_AUTO);
+    const int a = was_auto ? vlut_pick_algo(type, K, Nsum, T) : *algo;
+    if (a != VLUT_ALGO_GEMV) return false;
+    if (was_auto && !gemm_gemv_supported(type, K, Nsum, T, x_dev, ldx)) {
+        *algo = VLUT_ALGO_TCS;
+        return false;
+    }
+    return true;
+}
+
 int vlut_gemm(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, float *out_dev, int64_t ldo,
               float w_scale, int algo) {
-    return gemm_impl(c, type, K, N, T, t2_dev, out_dev, nullptr, 0, 0, ldo, w_scale, algo);
+    if (!out_dev) return VLUT_ERR_INVALID;
+    const GemmCall q{type, N, t2_dev, out_dev, ldo, w_scale};
+    return gemm_impl(c, K, T, &q, 1, nullptr, 0, 0, algo);
+}
+
+int vlut_gemm_batch(vlut_ctx *c, int n, const int *types, int64_t K, const int64_t *Ns, int64_t T, const void *const *t2_dev,
+                    float *const *outs_dev, const int64_t *ldos, const float *w_scales, int algo) {
+    if (!c || n < 1 || !types || !Ns || !t2_dev || !outs_dev || !ldos) return VLUT_ERR_INVALID;
+    for (int i0 = 0; i0 < n; i0 += MAX_BATCH) {
+        GemmCall q[MAX_BATCH];
+        const int m = std::min(MAX_BATCH, n - i0);
+        for (int i = 0; i < m; i++) {
+            if (!outs_dev[i0 + i]) return VLUT_ERR_INVALID;
+            q[i] = GemmCall{types[i0 + i], Ns[i0 + i], t2_dev[i0 + i], outs_dev[i0 + i], ldos[i0 + i],
+                            w_scales ? w_scales[i0 + i] : 1.0f};
+        }
+        int rc = gemm_impl(c, K, T, q, m, nullptr, 0, 0, algo);
+        if (rc) return rc;
+    }
+    return VLUT_OK;
+}
+
+int vlut_mul_mat_batch(vlut_ctx *c, int n, const int *types, int64_t K, const int64_t *Ns, int64_t T, const void *const *t2_dev,
+                       const float *x_dev, int64_t ldx, float *const *outs_dev, const int64_t *ldos, const float *w_scales,
+                       int algo) {
+    if (!c || n < 1 || !types || !Ns) return VLUT_ERR_INVALID;
+    if (!t2_dev || !outs_dev || !ldos) return VLUT_ERR_INVALID;
+    int64_t Nsum = 0;
+    for (int i = 0; i < n; i++) Nsum += Ns[i];
+    if (use_gemv(&algo, types[0], K, Nsum, T, x_dev, ldx)) {
+        for (int i0 = 0; i0 < n; i0 += MAX_BATCH) {
+            GemmCall q[MAX_BATCH];
+            const int m = std::min(MAX_BATCH, n - i0);
+            for (int i = 0; i < m; i++)
+                q[i] = GemmCall{types[i0 + i], Ns[i0 + i], t2_dev[i0 + i], outs_dev[i0 + i], ldos[i0 + i],
+                                w_scales ? w_scales[i0 + i] : 1.0f};
+            int rc = gemv_impl(c, K, T, q, m, x_dev, ldx);
+            if (rc) return rc;
+        }
+        return VLUT_OK;
+    }
+    int rc = quantize_impl(c, types[0], x_dev, ldx, K, T, algo, Nsum);
+    if (rc) return rc;
+    return vlut_gemm_batch(c, n, types, K, Ns, T, t2_dev, outs_dev, ldos, w_scales, algo);
 }
 
 int vlut_mul_mat_scatter(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                          int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
                          int algo) {
     if (!outs_dev || n_out < 1 || n_out > 8 || (multicast && n_out != 1)) return VLUT_ERR_INVALID;
-    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo);
+    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo, N);
     if (rc) return rc;
-    return gemm_impl(c, type, K, N, T, t2_dev, nullptr, outs_dev, n_out, multicast, ldo, w_scale, algo);
+    const GemmCall q{type, N, t2_dev, nullptr, ldo, w_scale};
+    return gemm_impl(c, K, T, &q, 1, outs_dev, n_out, multicast, algo);
+}
+
+int vlut_barrier(vlut_ctx *c, void *const *flags_dev, int n_ranks, int rank) {
+    if (!c || !flags_dev || n_ranks < 1 || n_ranks > 8 || rank < 0 || rank >= n_ranks) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    uint32_t *f[8];
+    for (int i = 0; i < n_ranks; i++) {
+        if (!flags_dev[i]) return VLUT_ERR_INVALID;
+        f[i] = (uint32_t *) flags_dev[i];
+    }
+    cudaError_t e = launch_barrier(f, n_ranks, rank, c->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "barrier launch");
+    c->launches++;
+    c->inflight.clear();   // plain launch: everything before it has completed when it runs
+    c->inflight_unknown = false;
+    c->last_was_gemm = false;
+    return VLUT_OK;
 }
 
 int vlut_mul_mat(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                  int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo) {
-    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo);
+    if (use_gemv(&algo, type, K, N, T, x_dev, ldx)) {
+        const GemmCall q{type, N, t2_dev, out_dev, ldo, w_scale};
+        return gemv_impl(c, K, T, &q, 1, x_dev, ldx);
+    }
+    int rc = quantize_impl(c, type, x_dev, ldx, K, T, algo, N);
     if (rc) return rc;
     return vlut_gemm(c, type, K, N, T, t2_dev, out_dev, ldo, w_scale, algo);
 }
@@ -505,7 +805,7 @@ int vlut_scale_rows(vlut_ctx *c, const float *x_dev, int64_t ldx, float *out_dev
                     float scale) {
     if (!c || !x_dev || !out_dev || N <= 0 || T <= 0 || ldx < N || ldo < N) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
-    c->last_out_lo = c->last_out_hi = nullptr;  // this kernel's output may be the next quantise's input
+    note_foreign_write(c);  // this kernel's output may be the next quantise's input
     cudaError_t e = launch_scale_rows(x_dev, ldx, out_dev, ldo, N, T, scale, c->stream);
     if (e != cudaSuccess) return cuda_fail(e, "scale_rows launch");
     c->launches += (T + 65534) / 65535;
@@ -521,14 +821,7 @@ static cudaError_t copy_rows(void *dst, size_t dpitch, const void *src, size_t s
 
 // Token chunk of the host-buffer pipeline.  Quantisation is per token, so cutting T is exact; 128 tokens is one TCP token
 // tile (GEMM ~11 us) against ~130 us of D2H for the chunk's 7.3 MB of f32 results at 4096->14336.
-static int host_chunk_tokens() {
-    static const int v = [] {
-        const char *e = getenv("VLUT_HOST_CHUNK");
-        const int n = e ? atoi(e) : 128;
-        return n < 0 ? 0 : n;
-    }();
-    return v;
-}
+static int host_chunk_tokens() { return knobs().host_chunk; }
 
 int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_host,
                       int64_t ldx, float *out_host, int64_t ldo, float w_scale, int algo) {
@@ -595,6 +888,10 @@ int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, co
 int vlut_debug_get_act(vlut_ctx *c, int64_t K, int64_t T, int8_t *q_host, float *scales_host) {
     if (!c || c->act_K != K || c->act_T != T) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
+    if (q_host) {
+        int rc = ensure_q_rm(c);
+        if (rc) return rc;
+    }
     CK(cudaStreamSynchronize(c->stream));
     if (q_host)
         CK(cudaMemcpy2D(q_host, (size_t) K, c->act.q_rm, (size_t) c->act.Kpad, (size_t) K, (size_t) T, cudaMemcpyDeviceToHost));
@@ -615,6 +912,27 @@ int vlut_debug_unpack_t2(vlut_ctx *c, int type, int64_t K, int64_t N, const void
     cudaFree(tmp);
     if (e != cudaSuccess) return cuda_fail(e, "unpack_t2");
     c->launches++;
+    note_foreign_write(c);
+    return VLUT_OK;
+}
+
+int vlut_measure_int8_peak(vlut_ctx *c, double *tops, double *clk_per_mma) {
+    if (!c || !tops) return VLUT_ERR_INVALID;
+    CK(cudaSetDevice(c->device));
+    CK(cudaStreamSynchronize(c->stream));
+    cudaError_t e = measure_int8_peak(c->sm_count, c->stream, 8192, tops, clk_per_mma);
+    if (e != cudaSuccess) return cuda_fail(e, "measure_int8_peak");
+    c->launches += 4;
+    note_foreign_write(c);
+    return VLUT_OK;
+}
+
+int vlut_debug_tc_counters(long long *out_host, int n_words) {
+    if (!out_host || n_words <= 0 || n_words > vlut::DBG_WORDS) return VLUT_ERR_INVALID;
+    if (!vlut::g_dbg_buf) return VLUT_ERR_UNSUPPORTED;
+    if (cudaDeviceSynchronize() != cudaSuccess) return VLUT_ERR_CUDA;
+    if (cudaMemcpy(out_host, vlut::g_dbg_buf, (size_t) n_words * sizeof(long long), cudaMemcpyDeviceToHost) != cudaSuccess)
+        return VLUT_ERR_CUDA;
     return VLUT_OK;
 }
 

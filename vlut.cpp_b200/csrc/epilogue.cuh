@@ -29,11 +29,35 @@ __device__ __forceinline__ void reg_fence(uint32_t (&v)[16]) {
                    "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])::"memory");
 }
 
+// 4 x 4 transpose inside every group of four lanes: on entry lane 4g + j holds a[tt] = (row 4g + j, token tt); on exit it
+// holds a[rr] = (row 4g + rr, token j).  Two butterfly stages, 4 shuffles.
+__device__ __forceinline__ void transpose4(float (&a)[4], int lane) {
+    const bool b0 = lane & 1, b1 = lane & 2;
+    {
+        const float s0 = b0 ? a[0] : a[1], s1 = b0 ? a[2] : a[3];
+        const float r0 = __shfl_xor_sync(0xffffffffu, s0, 1), r1 = __shfl_xor_sync(0xffffffffu, s1, 1);
+        if (b0) { a[0] = r0; a[2] = r1; } else { a[1] = r0; a[3] = r1; }
+    }
+    {
+        const float s0 = b1 ? a[0] : a[2], s1 = b1 ? a[1] : a[3];
+        const float r0 = __shfl_xor_sync(0xffffffffu, s0, 2), r1 = __shfl_xor_sync(0xffffffffu, s1, 2);
+        if (b1) { a[0] = r0; a[1] = r1; } else { a[2] = r0; a[3] = r1; }
+    }
+}
+
 // 16 final int32 sums of one weight row (tokens t .. t+15) -> fp32 outputs: out[(t+i) * ldo + n] = (float) x * s[t+i]
-// (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all).
+// (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all); nvalid = this
+// lane's row exists.  WARP-COLLECTIVE for the scatter flavours (OUT != 0): every lane of the warp must call it.
+//
+// Scatter flavours (multi-GPU fused all-gather): the values cross NVLink, where a 4-byte store per lane is a 4-byte
+// transaction (7.3 M of them per rank per step at T = 512 filled 31-66 % of the link, round 1).  Lanes are transposed in
+// groups of four so that every lane stores FOUR consecutive rows of one token as one 16-byte multimem.st / peer store:
+// a warp instruction then writes 4 tokens x 128 contiguous bytes.  Needs 16-byte aligned rows (vec_ok); ragged row tails and
+// unaligned destinations take the scalar stores.
 template <int OUT>
 __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_smem, bool ws, float w_scale, float *out0,
-                                        float *const *outs, int n_out, int64_t idx0, int64_t ldo, int nv) {
+                                        float *const *outs, int n_out, int64_t idx0, int64_t ldo, int nv, bool nvalid,
+                                        bool vec_ok = false) {
     float f[16];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -47,6 +71,31 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
 #pragma unroll
         for (int i = 0; i < 16; i++) f[i] *= w_scale;
     }
+    if (OUT != 0 && vec_ok) {
+        const int lane = threadIdx.x & 31, j = lane & 3;
+        // which rows of this lane's group of four exist (ragged tail of the matrix)
+        const unsigned gm = (__ballot_sync(0xffffffffu, nvalid) >> (lane & ~3)) & 0xfu;
+        // idx of (token c0, row of lane 4g): this lane's idx0 minus its position in the group
+        const int64_t idxg = idx0 - j;
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            float a[4] = {f[4 * i + 0], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]};
+            transpose4(a, lane);
+            // now: rows 4g .. 4g+3 of token 4i + j
+            const int tok = 4 * i + j;
+            if (tok < nv) {
+                if (gm == 0xfu) {
+                    store_out4<OUT>(out0, outs, n_out, idxg + tok * ldo, make_float4(a[0], a[1], a[2], a[3]));
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 4; r++)
+                        if ((gm >> r) & 1u) store_out<OUT>(out0, outs, n_out, idxg + tok * ldo + r, a[r]);
+                }
+            }
+        }
+        return;
+    }
+    if (!nvalid) return;
     if (nv >= 16) {
 #pragma unroll
         for (int i = 0; i < 16; i++) store_out<OUT>(out0, outs, n_out, idx0 + i * ldo, f[i]);
@@ -61,7 +110,7 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
 template <int OUT, int TO_SLOT>  // TO_SLOT: 0 fp32 output, 1 store the int32 partial, 2 red.add it into an accumulation tile
 __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, const int32_t *s_gs, const float *s_sc, bool ws,
                                            float w_scale, float *out0, float *const *outs, int n_out, int64_t idx0,
-                                           int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m) {
+                                           int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m, bool vec_ok = false) {
     int32_t x[16];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -77,8 +126,8 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
     } else if (TO_SLOT == 1) {
 #pragma unroll
         for (int i = 0; i < 16; i++) __stcg(slot_m + (c0 + i) * 128, x[i]);
-    } else if (nvalid) {
-        store16<OUT>(x, s_sc + c0, ws, w_scale, out0, outs, n_out, idx0 + (int64_t) c0 * ldo, ldo, tvalid - c0);
+    } else {
+        store16<OUT>(x, s_sc + c0, ws, w_scale, out0, outs, n_out, idx0 + (int64_t) c0 * ldo, ldo, tvalid - c0, nvalid, vec_ok);
     }
 }
 
@@ -88,24 +137,24 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
 template <int NT, int OUT, int TO_SLOT>
 __device__ __forceinline__ void drain_fast(uint32_t ta, const int32_t *s_gs, const float *s_sc, float w_scale, float *out0,
                                            float *const *outs, int n_out, int64_t idx0, int64_t ldo, int tvalid, bool nvalid,
-                                           int32_t *slot_m) {
+                                           int32_t *slot_m, bool vec_ok = false) {
     const bool ws = (w_scale != 1.0f);
     uint32_t va[16];
     ptx::tmem_ld_32x32b_x16(ta, va);
     if constexpr (NT == 16) {
         tmem_ld_wait_dep(va);
-        fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m);
+        fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok);
     } else {
         uint32_t vb[16];
 #pragma unroll 1
         for (int c0 = 0; c0 < NT; c0 += 32) {
             tmem_ld_wait_dep(va);
             ptx::tmem_ld_32x32b_x16(ta + c0 + 16, vb);
-            fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m);
+            fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok);
             tmem_ld_wait_dep(vb);
             if (c0 + 32 < NT) ptx::tmem_ld_32x32b_x16(ta + c0 + 32, va);
             fast_chunk<OUT, TO_SLOT>(vb, c0 + 16, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid,
-                                     slot_m);
+                                     slot_m, vec_ok);
         }
     }
 }

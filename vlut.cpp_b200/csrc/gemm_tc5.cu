@@ -16,15 +16,11 @@
 // the even CTA ("leader") owns afull[] (16 arrivals: 8 decode warps of each CTA -- a decode warp has waited for its CTA's
 // stage, so A-ready implies that CTA's half of the activations has landed) and accempty[] (8 arrivals: 4 epilogue warps of
 // each CTA).  The leader's commits are multicast to both CTAs.
-#include <stdlib.h>
-
 #include "epilogue.cuh"
 #include "ptx.cuh"
 #include "vlut_common.cuh"
 
 namespace vlut {
-
-long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
 
 namespace tc5 {
 
@@ -448,7 +444,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
                     if (complete)
                         epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
-                                                        p.g.ldo, tvalid, n < p.g.N, nullptr);
+                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0);
                     else
                         epi::drain_fast<NT, OUT, 2>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                        p.g.ldo, tvalid, n < p.g.N, slot + m);
@@ -510,10 +506,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                             for (int i = 0; i < 16; i++) __stcg(slot + (c0 + 16 * j + i) * 128 + m, 0);
 #pragma unroll
                         for (int j = 0; j < CB; j++)
-                            if (n < p.g.N)
-                                epi::store16<OUT>(a[j], s_sc + c0 + 16 * j, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs,
-                                                  p.g.n_out, (t0 + c0 + 16 * j) * p.g.ldo + n, p.g.ldo,
-                                                  (int) min((int64_t) 16, p.g.T - t0 - c0 - 16 * j));
+                            epi::store16<OUT>(a[j], s_sc + c0 + 16 * j, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs,
+                                              p.g.n_out, (t0 + c0 + 16 * j) * p.g.ldo + n, p.g.ldo,
+                                              (int) min((int64_t) 16, p.g.T - t0 - c0 - 16 * j), n < p.g.N, p.g.vec_ok != 0);
                     }
                     if (et == 0) *counter = 0;
                     mark(12);
@@ -533,18 +528,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     }
 }
 
-static int env_int(const char *name, int dflt) {
-    const char *v = getenv(name);
-    return v ? atoi(v) : dflt;
-}
-
 template <int NT, int SPS, int OUT>
 static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
-    const int budget = env_int("VLUT_TC_SMEM_KB", 200) * 1024;
+    const Knobs &kn = knobs();
+    const int budget = kn.tc_smem_kb * 1024;
     p.stage_bytes = SPS * (NT / 2 * 128 + SUB_W_BYTES);  // multiple of 1024
     int ns = (budget - 1024) / p.stage_bytes;
     if (ns > MAX_STAGES) ns = MAX_STAGES;
-    int forced = env_int("VLUT_TC_STAGES", 0);
+    int forced = kn.tc_stages;
     // the decode warps fetch the first stage of the next A block before they hand over the current one: the ring must
     // hold one stage more than an A block, or that fetch would wait for an MMA that waits for the hand-over
     constexpr int MIN_STAGES = SPA / SPS + 1;
@@ -554,7 +545,8 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     p.nstages = ns;
     const size_t smem = (size_t) ns * p.stage_bytes + 1024;
     auto kern = kernel<NT, SPS, OUT>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    static int smem_set[MAX_DEVICES] = {};
+    cudaError_t e = ensure_dyn_smem(kern, smem, p.g.device, smem_set);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.blockDim = dim3(THREADS);
@@ -596,10 +588,10 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     p.whole = 1;
     if (full >= 1 && cost_hybrid < cost_whole && cost_hybrid <= cost_sk) p.whole = 2;
     else if (cost_sk < cost_whole) p.whole = 0;
-    const int forced_grid = env_int("VLUT_TC_GRID", 0);  // tests: force a grid (and with it the split paths)
+    const int forced_grid = kn.tc_grid;  // tests: force a grid (and with it the split paths)
     if (forced_grid > 0) p.whole = 0;
-    p.whole = env_int("VLUT_TC_WHOLE", p.whole);
-    p.split_last = env_int("VLUT_TC_SPLIT_LAST", 0);
+    if (kn.tc_whole >= 0) p.whole = kn.tc_whole;
+    p.split_last = kn.tc_split_last;
     if (forced_grid > 0) npairs = forced_grid / 2;
     else if (p.whole == 1) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;
@@ -633,11 +625,12 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     const int NT = g.act.NT;
     p.TT = (int) (g.act.Tpad / NT);
     p.U = p.RP * p.TT * p.G;
-    p.allow_fast = tc5::env_int("VLUT_TC_FAST", 1);
-    p.pdl = tc5::env_int("VLUT_PDL", 1);
-    p.abl = tc5::env_int("VLUT_TC_ABL", 0);
-    p.dbg_skip = tc5::env_int("VLUT_TC_DEBUG_SKIP", 0);
-    p.dbg = tc5::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, tc5::env_int("VLUT_TC_DEBUG_SKIP", 0)) : nullptr;
+    const Knobs &kn = knobs();
+    p.allow_fast = kn.tc_fast;
+    p.pdl = kn.pdl;
+    p.abl = kn.tc_abl;
+    p.dbg_skip = kn.tc_debug_skip;
+    p.dbg = kn.tc_debug ? debug_buffer(s, kn.tc_debug_skip) : nullptr;
     if (launches) *launches += 1;
     switch (NT) {
         case 64: return tc5::launch_one<64, 2>(p, g.sm_count, s);

@@ -23,8 +23,6 @@
 //   warps 0-3   epilogue (TMEM lane quadrant = warp)
 //   warps 4-19  decode: d = warp - 4, quadrant q = d % 4, sub-block h = (d / 4) % 2, block parity p = d / 8
 //   warp 20     TMEM allocator + activation producer (TMA)     warps 21, 22  MMA issuers (even / odd blocks)
-#include <stdlib.h>
-
 #include "epilogue.cuh"
 #include "ptx.cuh"
 #include "vlut_common.cuh"
@@ -44,8 +42,6 @@
 #define WAIT(bit, ns, bar, par) do { if (VLUT_TCS_BACKOFF & (bit)) ptx::mbar_wait_backoff(bar, par, ns); else ptx::mbar_wait(bar, par); } while (0)
 
 namespace vlut {
-
-long long *debug_buffer(cudaStream_t s, int skip);  // gemm_tc.cu
 
 namespace tcs {
 
@@ -111,7 +107,13 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
     const int warp = __shfl_sync(0xffffffffu, (int) (threadIdx.x >> 5), 0), lane = threadIdx.x & 31;
     const int S = p.S;
     const int rank = (S > 1) ? (int) ptx::cluster_ctarank() : 0;
-    const int rt = blockIdx.x / S;
+    // strip of the launch's concatenated strip space -> (tensor of the batch, strip inside it)
+    const int rt_all = blockIdx.x / S;
+    int ti = 0;
+#pragma unroll
+    for (int i = 1; i < MAX_BATCH; i++) ti += (i < p.g.n_tens && rt_all >= p.g.tens[i].strip0) ? 1 : 0;
+    const TensorRef &ten = p.g.tens[ti];
+    const int rt = rt_all - ten.strip0;
     const int tt = blockIdx.y;
     const int g0 = (rank * p.G) / S, g1 = ((rank + 1) * p.G) / S;   // this CTA's K-groups
     const int kb_begin = g0 * p.gsub, kb_end = min(g1 * p.gsub, p.KB);
@@ -159,7 +161,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         const bool dmark = (d == 0);
         // this thread unpacks its row of the blocks b = ph, ph + 4, ...: 4 x 16 B per block (two 128-k sub-blocks of two
         // 64-k chunks), 32 KB further on each time
-        const uint8_t *wsrc = p.g.w + ((int64_t) rt * (2 * p.KB) + 2 * kb_begin) * TILE_BYTES + m * 16;
+        const uint8_t *wsrc = ten.w + ((int64_t) rt * (2 * p.KB) + 2 * kb_begin) * TILE_BYTES + m * 16;
         const uint32_t wdst = wring + dt * 16;
         auto issue = [&](int b, int slot) {   // this thread's 64 bytes of block b -> ring slot; always one commit group
             if (!ABL(8) && b < nblk) {
@@ -428,7 +430,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             const int64_t n = (int64_t) rt * TILE_ROWS + m;
             const int64_t t0 = (int64_t) tt * NT;
             const int32_t *pre = p.g.act.gpre + (t0 + et) * (p.G + 1);
-            float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
+            float *const out0 = (OUT == 0) ? ten.out : p.g.outs[0];
             if (et < NT) s_sc[et] = __ldg(p.g.act.scales + t0 + et);
             const uint32_t ta0 = tmem_base + ((uint32_t) (ew * 32) << 16);
             if (fast) {
@@ -440,7 +442,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 if (nsets == 2) WAIT(1, 200, ptx::smem_u32(&s_accfull[1]), 0);
                 ptx::tc_fence_after();
                 if (ew == 0) mark(0);
-                const bool ws = (p.g.w_scale != 1.0f);
+                const bool ws = (ten.w_scale != 1.0f);
                 const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
 #pragma unroll 1
                 for (int c0 = 0; c0 < NT; c0 += 16) {
@@ -463,8 +465,8 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                             for (int j = 0; j < 16; j++) va[j] += (uint32_t) ((int32_t) v[i][j] >> (2 * i));
                     }
                     if (S == 1) {
-                        epi::fast_chunk<OUT, false>(va, c0, s_gs, s_sc, ws, p.g.w_scale, out0, p.g.outs, p.g.n_out, t0 * p.g.ldo + n,
-                                                    p.g.ldo, tvalid, n < p.g.N, nullptr);
+                        epi::fast_chunk<OUT, false>(va, c0, s_gs, s_sc, ws, ten.w_scale, out0, p.g.outs, p.g.n_out, t0 * ten.ldo + n,
+                                                    ten.ldo, tvalid, n < ten.N, nullptr, p.g.vec_ok != 0);
                     } else {
 #pragma unroll
                         for (int i = 0; i < 16; i++) red[(c0 + i) * 128 + m] = (int32_t) va[i] - s_gs[c0 + i];
@@ -503,13 +505,13 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                     if (lane == 0) ptx::mbar_arrive(ptx::smem_u32(&s_accempty[ab]));
                     ptx::bar_sync(1, 128);  // s_gs is rewritten for the next group
                 }
-                if (S == 1 && n < p.g.N) {
+                if (S == 1 && n < ten.N) {
 #pragma unroll 1
                     for (int c = 0; c < NT; c++) {
                         if (t0 + c < p.g.T) {
                             float v = (float) red[c * 128 + m] * s_sc[c];
-                            if (p.g.w_scale != 1.0f) v *= p.g.w_scale;
-                            store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c) * p.g.ldo + n, v);
+                            if (ten.w_scale != 1.0f) v *= ten.w_scale;
+                            store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c) * ten.ldo + n, v);
                         }
                     }
                 }
@@ -525,7 +527,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             const int m = warp * 32 + lane;
             const int64_t n = (int64_t) rt * TILE_ROWS + m;
             const int64_t t0 = (int64_t) tt * NT;
-            float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
+            float *const out0 = (OUT == 0) ? ten.out : p.g.outs[0];
             const int c_lo = (rank * NT) / S, c_hi = ((rank + 1) * NT) / S;
             uint32_t peer[8];
 #pragma unroll
@@ -536,10 +538,10 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
 #pragma unroll
                 for (int r = 0; r < 8; r++) v[r] = (r < S) ? ptx::ld_shared_cluster_s32(peer[r] + c * 512) : 0;
                 const int32_t sum = ((v[0] + v[1]) + (v[2] + v[3])) + ((v[4] + v[5]) + (v[6] + v[7]));
-                if (n < p.g.N && t0 + c < p.g.T) {
+                if (n < ten.N && t0 + c < p.g.T) {
                     float f = (float) sum * s_sc[c];
-                    if (p.g.w_scale != 1.0f) f *= p.g.w_scale;
-                    store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c) * p.g.ldo + n, f);
+                    if (ten.w_scale != 1.0f) f *= ten.w_scale;
+                    store_out<OUT>(out0, p.g.outs, p.g.n_out, (t0 + c) * ten.ldo + n, f);
                 }
             }
         }
@@ -554,11 +556,6 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         ptx::tc_fence_after();
         ptx::tmem_dealloc(s_tmem_base, TMEM_COLS);
     }
-}
-
-static int env_int(const char *name, int dflt) {
-    const char *v = getenv(name);
-    return v ? atoi(v) : dflt;
 }
 
 constexpr int SMEM_BUDGET = 216 * 1024;
@@ -580,12 +577,13 @@ static cudaError_t launch_out(Params &p, cudaStream_t s) {
     int nas = need < MAX_AS ? need : MAX_AS;
     if (nas < 1) nas = 1;
     while (nas > 2 && (int) smem_bytes<NT, DT>(nas, p.ASB) > SMEM_BUDGET) --nas;
-    const int forced = env_int("VLUT_TCS_NAS", 0);
+    const int forced = knobs().tcs_nas;
     if (forced > 0 && forced <= MAX_AS) nas = forced;
     p.NAS = nas;
     const size_t smem = smem_bytes<NT, DT>(p.NAS, p.ASB);
     auto kern = kernel<NT, OUT, DT, DBG>;
-    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    static int smem_set[MAX_DEVICES] = {};
+    cudaError_t e = ensure_dyn_smem(kern, smem, p.g.device, smem_set);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) (p.RT * p.S), (unsigned) (p.g.act.Tpad / NT));
@@ -624,7 +622,7 @@ static cudaError_t launch_one(Params &p, cudaStream_t s) {
 // barrier and a distributed-shared-memory reduction.  Whole K-groups per CTA, at most 8 (portable cluster size), one CTA
 // per SM.
 static int pick_split(const Params &p) {
-    const int forced = env_int("VLUT_TCS_SPLIT", 0);
+    const int forced = knobs().tcs_split;
     const int smax = p.G < 8 ? p.G : 8;
     if (forced > 0) return forced < smax ? forced : smax;
     const int slots = p.g.sm_count;
@@ -657,17 +655,18 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.KB = (int) (g.act.Kpad / 128);
     p.gsub = g.act.gsize / 128;
     p.G = g.act.G;
-    p.RT = (int) (g.Npad / TILE_ROWS);
-    p.allow_fast = tcs::env_int("VLUT_TC_FAST", 1);
-    p.pdl = tcs::env_int("VLUT_PDL", 1);
+    const Knobs &kn = knobs();
+    p.RT = g.tens[g.n_tens].strip0;   // strips of all the tensors of the batch
+    p.allow_fast = kn.tc_fast;
+    p.pdl = kn.pdl;
     p.S = tcs::pick_split(p);
-    p.issuers = tcs::env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
-    p.dbg = tcs::env_int("VLUT_TC_DEBUG", 0) ? debug_buffer(s, 0) : nullptr;
-    p.dbg_cta = tcs::env_int("VLUT_TCS_DBG_CTA", 0);
-    p.dbg_mask = tcs::env_int("VLUT_TCS_DBG_MASK", 15);
+    p.issuers = kn.tcs_issuers;
+    p.dbg = kn.tc_debug ? debug_buffer(s, 0) : nullptr;
+    p.dbg_cta = kn.tcs_dbg_cta;
+    p.dbg_mask = kn.tcs_dbg_mask;
     if (launches) *launches += 1;
     // ring slots per decode thread: 4 phases x DT blocks = DT x 32 KB of packed weights in flight per CTA
-    const int deep = tcs::env_int("VLUT_TCS_DEPTH", 3);
+    const int deep = kn.tcs_depth;
     switch (NT) {
         case 16: return deep >= 4 ? tcs::launch_one<16, 4>(p, s) : deep <= 2 ? tcs::launch_one<16, 2>(p, s) : tcs::launch_one<16, 3>(p, s);
         case 32: return deep <= 2 ? tcs::launch_one<32, 2>(p, s) : tcs::launch_one<32, 3>(p, s);

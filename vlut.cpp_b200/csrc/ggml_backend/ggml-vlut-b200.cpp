@@ -80,7 +80,7 @@ struct backend_ctx {
     std::string name;
     act_cache act;
     // counters behind the "vlut_b200_backend_stats" proc address (tests)
-    int64_t n_mul_mat = 0, n_quantize = 0, n_fused_scale = 0, n_scale_rows = 0;
+    int64_t n_mul_mat = 0, n_quantize = 0, n_fused_scale = 0, n_scale_rows = 0, n_batched = 0;
 };
 
 bool is_i1_family(enum ggml_type t) { return t == GGML_TYPE_I1_V || t == GGML_TYPE_I1_V_2; }
@@ -228,6 +228,12 @@ const char *backend_get_name(ggml_backend_t backend) { return ((backend_ctx *) b
 
 void backend_free(ggml_backend_t backend) {
     backend_ctx *b = (backend_ctx *) backend->context;
+    // VLUT_B200_STATS=1: what ran here, for runs under the reference's own tools (llama-bench has no hook to ask)
+    if (getenv("VLUT_B200_STATS"))
+        fprintf(stderr, "vlut_b200_backend_stats %s: mul_mat=%lld quantise=%lld fused_scale=%lld scale_rows=%lld batched=%lld "
+                "kernel_launches=%lld\n", b->name.c_str(), (long long) b->n_mul_mat, (long long) b->n_quantize,
+                (long long) b->n_fused_scale, (long long) b->n_scale_rows, (long long) b->n_batched,
+                (long long) vlut_ctx_launch_count(b->ctx));
     vlut_ctx_destroy(b->ctx);
     delete b;
     delete backend;
@@ -269,6 +275,50 @@ void note_write(backend_ctx *b, const ggml_tensor *dst) {
 // ggml_compute_forward_mul_mat (ggml-cpu.c:1372-1421): quantise activations per token, Vec-LUT GEMM, fp32 epilogue.
 // `out_t` is where the result goes (the MUL_MAT node itself, or the trailing MUL node when its scale is folded into
 // the epilogue as w_scale: ((float) acc * s_t) * w_scale, the same two roundings as MUL_MAT followed by MUL).
+struct mm_item {
+    const ggml_tensor *dst;     // the MUL_MAT node
+    const ggml_tensor *out_t;   // where its result is stored
+    float w_scale;
+};
+
+ggml_status mm_fail(backend_ctx *b, const ggml_tensor *dst, int rc) {
+    b->act = act_cache{};
+    GGML_LOG_ERROR("%s: vlut MUL_MAT(%s) failed: %s (%s)\n", __func__, dst->name, vlut_error_string(rc), vlut_last_cuda_error());
+    return rc == VLUT_ERR_NOMEM ? GGML_STATUS_ALLOC_FAILED : GGML_STATUS_FAILED;
+}
+
+// A group of MUL_MATs that read the SAME 2-D activation tensor (Q/K/V on the attention input, up/gate on the FFN input:
+// consecutive build_lora_mm calls, src/models/bitnet.cpp:28-60, src/llama-graph.cpp:668-671): one quantisation and, in
+// the small-token regime, ONE kernel launch over all the weights (vlut_mul_mat_batch).
+ggml_status compute_group(backend_ctx *b, const mm_item *items, int n) {
+    const ggml_tensor *src1 = items[0].dst->src[1];
+    const int64_t K = src1->ne[0], T = src1->ne[1];
+    int types[4];
+    int64_t Ns[4], ldos[4];
+    const void *t2[4];
+    float *outs[4];
+    float scales[4];
+    for (int i = 0; i < n; i++) {
+        const ggml_tensor *src0 = items[i].dst->src[0];
+        GGML_ASSERT(src0->ne[0] == K && items[i].out_t->nb[0] == sizeof(float));
+        types[i] = (int) src0->type;
+        Ns[i] = src0->ne[1];
+        t2[i] = src0->data;
+        outs[i] = (float *) items[i].out_t->data;
+        ldos[i] = (int64_t) (items[i].out_t->nb[1] / sizeof(float));
+        scales[i] = items[i].w_scale;
+    }
+    const int rc = vlut_mul_mat_batch(b->ctx, n, types, K, Ns, T, t2, (const float *) src1->data,
+                                      (int64_t) (src1->nb[1] / sizeof(float)), outs, ldos, scales, VLUT_ALGO_AUTO);
+    if (rc != VLUT_OK) return mm_fail(b, items[0].dst, rc);
+    b->n_mul_mat += n;
+    b->n_quantize++;
+    b->n_batched += (n > 1) ? n : 0;
+    b->act = act_cache{};
+    for (int i = 0; i < n; i++) note_write(b, items[i].out_t);
+    return GGML_STATUS_SUCCESS;
+}
+
 ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst, const ggml_tensor *out_t, float w_scale) {
     const ggml_tensor *src0 = dst->src[0];
     const ggml_tensor *src1 = dst->src[1];
@@ -284,11 +334,15 @@ ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst, const ggml_t
             int rc = VLUT_OK;
             const bool reuse = !batched && b->act.src1 == src1 && b->act.K == K && b->act.T == T &&
                                b->act.i1_family == is_i1_family(src0->type);
-            if (!reuse) {
-                rc = vlut_quantize_act(b->ctx, (int) src0->type, x, ldx, K, T);
+            if (reuse) {
+                rc = vlut_gemm(b->ctx, (int) src0->type, K, N, T, src0->data, out, ldo, w_scale, VLUT_ALGO_AUTO);
+            } else {
+                // the whole op: the library may run it as ONE kernel at a handful of tokens (quantisation fused), in which
+                // case the workspace holds no quantisation to reuse
+                rc = vlut_mul_mat(b->ctx, (int) src0->type, K, N, T, src0->data, x, ldx, out, ldo, w_scale, VLUT_ALGO_AUTO);
                 b->n_quantize++;
                 b->act = act_cache{};
-                if (rc == VLUT_OK && !batched) {
+                if (rc == VLUT_OK && !batched && vlut_ctx_last_algo(b->ctx) != VLUT_ALGO_GEMV) {
                     b->act.src1 = src1;
                     b->act.lo = (const char *) x;
                     b->act.hi = (const char *) x + (size_t) (T - 1) * src1->nb[1] + (size_t) K * sizeof(float);
@@ -297,13 +351,7 @@ ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst, const ggml_t
                     b->act.i1_family = is_i1_family(src0->type);
                 }
             }
-            if (rc == VLUT_OK) rc = vlut_gemm(b->ctx, (int) src0->type, K, N, T, src0->data, out, ldo, w_scale, VLUT_ALGO_AUTO);
-            if (rc != VLUT_OK) {
-                b->act = act_cache{};
-                GGML_LOG_ERROR("%s: vlut_mul_mat(%s) failed: %s (%s)\n", __func__, dst->name, vlut_error_string(rc),
-                               vlut_last_cuda_error());
-                return rc == VLUT_ERR_NOMEM ? GGML_STATUS_ALLOC_FAILED : GGML_STATUS_FAILED;
-            }
+            if (rc != VLUT_OK) return mm_fail(b, dst, rc);
             b->n_mul_mat++;
         }
     }
@@ -335,31 +383,72 @@ ggml_status compute_scalar_mul(backend_ctx *b, const ggml_tensor *dst) {
     return GGML_STATUS_SUCCESS;
 }
 
+// MUL_MAT node i, with its trailing MUL by the weight's {1} scale folded in when ggml_can_fuse allows (same shape, single
+// use, not a graph output: ggml/src/ggml-impl.h:604-643).  Returns how many graph nodes the item covers (1 or 2).
+int make_item(backend_ctx *b, ggml_cgraph *cgraph, int i, bool no_fuse, mm_item *it) {
+    static const enum ggml_op fuse_ops[2] = {GGML_OP_MUL_MAT, GGML_OP_MUL};
+    ggml_tensor *node = cgraph->nodes[i];
+    *it = mm_item{node, node, 1.0f};
+    float sc = 1.0f;
+    if (!no_fuse && ggml_can_fuse(cgraph, i, fuse_ops, 2)) {
+        const ggml_tensor *mul = cgraph->nodes[i + 1];
+        const int j = scalar_mul_operand(mul);
+        if (j >= 0 && mul->src[1 - j] == node && scalar_value(b, mul->src[j], &sc)) {
+            it->out_t = mul;
+            it->w_scale = sc;
+            return 2;
+        }
+    }
+    return 1;
+}
+
+bool ranges_overlap(const ggml_tensor *a, const ggml_tensor *c) {
+    const char *al = (const char *) a->data, *ah = al + ggml_nbytes(a);
+    const char *cl = (const char *) c->data, *ch = cl + ggml_nbytes(c);
+    return al < ch && cl < ah;
+}
+
 ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
     backend_ctx *b = (backend_ctx *) backend->context;
     static const bool no_fuse = getenv("VLUT_B200_NO_FUSE") != nullptr;
+    static const bool no_batch = getenv("VLUT_B200_NO_BATCH") != nullptr;
     b->act = act_cache{};  // inputs may have been rewritten since the last graph
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor *node = cgraph->nodes[i];
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
-                // look ahead: MUL_MAT -> MUL by the weight's {1} scale folds into the epilogue (same-shape, single
-                // use, not a graph output: ggml_can_fuse, ggml-impl.h:604-643)
-                static const enum ggml_op fuse_ops[2] = {GGML_OP_MUL_MAT, GGML_OP_MUL};
-                float sc = 1.0f;
-                if (!no_fuse && ggml_can_fuse(cgraph, i, fuse_ops, 2)) {
-                    const ggml_tensor *mul = cgraph->nodes[i + 1];
-                    const int j = scalar_mul_operand(mul);
-                    if (j >= 0 && mul->src[1 - j] == node && scalar_value(b, mul->src[j], &sc)) {
-                        const ggml_status st = compute_mul_mat(b, node, mul, sc);
-                        if (st != GGML_STATUS_SUCCESS) return st;
-                        b->n_fused_scale++;
-                        i++;  // the MUL is done
+                mm_item items[4];
+                int n = 0, next = i;
+                next += make_item(b, cgraph, i, no_fuse, &items[n++]);
+                // look ahead: the following MUL_MATs that read the same (2-D) activation tensor with the same K-group
+                // family join the group, as long as no member's output overlaps the shared input or another output
+                const ggml_tensor *src1 = node->src[1];
+                const bool groupable = !no_batch && src1->ne[2] * src1->ne[3] == 1;
+                while (groupable && n < 4 && next < cgraph->n_nodes) {
+                    ggml_tensor *cand = cgraph->nodes[next];
+                    if (cand->op != GGML_OP_MUL_MAT || cand->src[1] != src1 || !cand->src[0] ||
+                        !ggml_backend_dev_supports_op(backend->device, cand) ||
+                        is_i1_family(cand->src[0]->type) != is_i1_family(node->src[0]->type))
                         break;
-                    }
+                    mm_item it;
+                    const int adv = make_item(b, cgraph, next, no_fuse, &it);
+                    bool clash = ranges_overlap(it.out_t, src1);
+                    for (int k = 0; k < n; k++) clash = clash || ranges_overlap(it.out_t, items[k].out_t);
+                    if (clash) break;
+                    items[n++] = it;
+                    next += adv;
                 }
-                const ggml_status st = compute_mul_mat(b, node, node, 1.0f);
+                if (ranges_overlap(items[0].out_t, src1)) n = 1;
+                ggml_status st;
+                if (n > 1) {
+                    st = compute_group(b, items, n);
+                } else {
+                    st = compute_mul_mat(b, items[0].dst, items[0].out_t, items[0].w_scale);
+                    next = i + (items[0].out_t != items[0].dst ? 2 : 1);
+                }
                 if (st != GGML_STATUS_SUCCESS) return st;
+                for (int k = 0; k < n; k++) b->n_fused_scale += (items[k].out_t != items[k].dst) ? 1 : 0;
+                i = next - 1;
             } break;
             case GGML_OP_MUL: {
                 const ggml_status st = compute_scalar_mul(b, node);
@@ -471,7 +560,8 @@ bool dev_supports_op(ggml_backend_dev_t dev, const ggml_tensor *op) {
             if (src0->ne[2] != 1 || src0->ne[3] != 1) return false;
             if (src1->type != GGML_TYPE_F32 || op->type != GGML_TYPE_F32) return false;
             if (src1->nb[0] != sizeof(float) || src1->nb[1] % sizeof(float) != 0) return false;
-            if (vlut_gguf_nbytes((int) src0->type, src0->ne[0], src0->ne[1]) == 0) return false;
+            // exactly what the launch path accepts (packing constraints, at most 64 K-groups)
+            if (!vlut_op_supported((int) src0->type, src0->ne[0], src0->ne[1], src1->ne[1] > 0 ? src1->ne[1] : 1)) return false;
             // the weight must live (or be about to live) in our buffer type: it is stored repacked there
             if (src0->buffer && src0->buffer->buft != &d->buft) return false;
             return true;
@@ -534,9 +624,15 @@ void backend_stats(ggml_backend_t backend, int64_t *out) {
     out[2] = b->n_fused_scale;
     out[3] = b->n_scale_rows;
 }
+// "vlut_b200_backend_stats2": adds out[4] = MUL_MATs that ran inside a batched group
+void backend_stats2(ggml_backend_t backend, int64_t *out) {
+    backend_stats(backend, out);
+    out[4] = ((backend_ctx *) backend->context)->n_batched;
+}
 
 void *reg_get_proc_address(ggml_backend_reg_t, const char *name) {
     if (name && strcmp(name, "vlut_b200_backend_stats") == 0) return (void *) backend_stats;
+    if (name && strcmp(name, "vlut_b200_backend_stats2") == 0) return (void *) backend_stats2;
     return nullptr;
 }
 

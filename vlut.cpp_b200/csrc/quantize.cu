@@ -11,8 +11,7 @@
 // 128-bit loads of x, 32-bit stores of q in two layouts (row-major, and pre-swizzled K-major UMMA operand tiles
 // that a TMA bulk copy drops into shared memory ready for tcgen05.mma), plus per (token, K-group): the sum of q
 // that undoes the +1 offset of the u8 weight codes, and whether sum|q| rules out any int16 wrap.
-#include <stdlib.h>
-
+#include "quant_math.cuh"
 #include "vlut_common.cuh"
 
 namespace vlut {
@@ -20,7 +19,7 @@ namespace vlut {
 constexpr int QT = 256;
 
 __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
-                                                      ActView a) {
+                                                      ActView a, int want_rm) {
     const int t = blockIdx.x;
     const int tid = threadIdx.x;
     // programmatic dependent launch: let the GEMM that follows start its prologue and its weight prefetch now; it
@@ -82,7 +81,7 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         }
         const uint32_t pk = (uint32_t) (qv[0] & 0xff) | ((uint32_t) (qv[1] & 0xff) << 8) |
                             ((uint32_t) (qv[2] & 0xff) << 16) | ((uint32_t) (qv[3] & 0xff) << 24);
-        *reinterpret_cast<uint32_t *>(a.q_rm + (int64_t) t * Kpad + k) = pk;
+        if (want_rm) *reinterpret_cast<uint32_t *>(a.q_rm + (int64_t) t * Kpad + k) = pk;
         // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
         const int64_t kb = k / BLOCK_K;
         const int kk = act_row_pos((int) (k % BLOCK_K), a.perm);   // 4 consecutive k stay 4 consecutive bytes in both orders
@@ -128,33 +127,9 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
 // by a warp scan.  Launched with the programmatic-serialisation attribute: the CTA is resident and past its prologue when
 // the predecessor (the previous GEMM, which reads the workspace this kernel rewrites) drains; griddepcontrol.wait orders
 // every global access after it.
-__device__ __forceinline__ int quant1_exact(float x, double is) {
-    // clamp(round((double) x * is), -128, 127) with round = half away from zero, exactly: the clamp is applied first (it
-    // commutes with rounding at integers), then truncation and an exact fractional test
-    double p = (double) x * is;
-    p = fmin(fmax(p, -129.0), 128.0);
-    int ti = __double2int_rz(p);
-    const double fr = p - (double) ti;
-    ti += (fr >= 0.5) - (fr <= -0.5);
-    return max(-128, min(127, ti));
-}
-
-// Same value, fp32 first: pf = x * (float) is differs from the exact double product by at most |p| * 2^-23 <= 1.6e-5 inside
-// the clamp range, so whenever pf is further than 1e-4 from a rounding boundary (k + 0.5) both round the same way; the
-// few elements closer than that (about 1 in 5000) take the double path.  The FP64 pipe (conversions included) was ~2 us of
-// the kernel at T = 512.
-__device__ __forceinline__ int quant1(float x, double is, float isf) {
-    float pf = fminf(fmaxf(x * isf, -129.0f), 128.0f);
-    const float tr = truncf(pf);
-    const float fr = fabsf(pf - tr);   // exact
-    if (fabsf(fr - 0.5f) <= 1e-4f) return quant1_exact(x, is);
-    const int ti = (int) tr + ((fr > 0.5f) ? (pf < 0.0f ? -1 : 1) : 0);
-    return max(-128, min(127, ti));
-}
-
 template <int CH>
 __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
-                                                          ActView a, int early) {
+                                                          ActView a, int early, int want_rm) {
     const int t = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
@@ -226,7 +201,7 @@ __global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restric
             asum = __dp4a(__vabs4(pk[i]), 0x01010101u, asum);
         }
         if (k < Kpad) {
-            *reinterpret_cast<uint4 *>(a.q_rm + (int64_t) t * Kpad + k) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            if (want_rm) *reinterpret_cast<uint4 *>(a.q_rm + (int64_t) t * Kpad + k) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
             const int64_t kb = k / BLOCK_K;
             const int c = (int) (k % BLOCK_K) / 16;
@@ -313,9 +288,41 @@ cudaError_t launch_relayout(const ActView &a, cudaStream_t s) {
     return cudaGetLastError();
 }
 
+// Materialise q_rm from q_sw (inverse of the tiling / swizzle / regrouping above): only the scalar anchor kernel, the LUT
+// candidate, the re-tiling fallback and the test read-back need the row-major copy, so the hot path does not write it.
+__global__ void unswizzle_kernel(ActView a) {
+    const int64_t chunks_per_row = a.Kpad / 16;
+    const int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t) a.Tpad * chunks_per_row) return;
+    const int64_t t = i / chunks_per_row;
+    const int64_t k = (i % chunks_per_row) * 16;
+    const int64_t kb = k / BLOCK_K;
+    const int c = (int) (k % BLOCK_K) / 16;
+    const int8_t *row = a.q_sw + (((t / a.sw_tile) * (a.Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128;
+    uint4 v;
+    if (!a.perm) {
+        v = *reinterpret_cast<const uint4 *>(row + ((c ^ (int) (t & 7)) << 4));
+    } else {
+        uint32_t pk[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int pos = j * 32 + c * 4;
+            pk[j] = *reinterpret_cast<const uint32_t *>(row + ((((pos >> 4) ^ (int) (t & 7)) << 4) | (pos & 15)));
+        }
+        v = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+    }
+    *reinterpret_cast<uint4 *>(a.q_rm + t * a.Kpad + k) = v;
+}
+
+cudaError_t launch_unswizzle(const ActView &a, cudaStream_t s) {
+    const int64_t n = (int64_t) a.Tpad * (a.Kpad / 16);
+    unswizzle_kernel<<<(unsigned) ((n + 255) / 256), 256, 0, s>>>(a);
+    return cudaGetLastError();
+}
+
 template <int CH>
 static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
-                              int early) {
+                              int early, int want_rm) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) a.Tpad);
     cfg.blockDim = dim3(QT);
@@ -326,36 +333,19 @@ static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T,
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a, early);
+    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a, early, want_rm);
 }
 
-cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
-                            int early_ok) {
+cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
+                            bool early, bool want_rm) {
     if (a.G > 64) return cudaErrorInvalidValue;
-    const char *e2 = getenv("VLUT_QUANT_2PASS"), *ep = getenv("VLUT_PDL");
-    const bool two_pass = e2 && atoi(e2) != 0;
-    // programmatic launch of the quantiser itself (behind the previous GEMM): measured on the quantise + GEMM chain at
-    // 4096 -> 14336 it gains 0.1-0.5 us for T <= 64 and from T = 1024 up, and loses 1.6-2 us in between (scripts/time_op.py)
-    const char *eq = getenv("VLUT_QUANT_PDL");
-    // Early mode: programmatic launch with the loads ahead of the dependency wait.  early_ok: 0 = the host cannot rule out
-    // that the preceding kernel writes x; 1 = it can (vlut_ctx_set_option(VLUT_OPT_INPUTS_VISIBLE) + the last launch was a
-    // GEMM that does not write x): used where it measured faster (scripts/time_op.py).
-    // VLUT_QUANT_EARLY=0 never, =1 at every T (needs the same host-side proof about the last launch).
-    const char *ee = getenv("VLUT_QUANT_EARLY");
-    const bool pdl_on = ep ? atoi(ep) != 0 : true;
-    int early = 0;
-    if (pdl_on && early_ok) {
-        if (ee) early = atoi(ee) != 0;
-        else early = (early_ok == 1) && (T <= 64 || (T >= 512 && T <= 1024));
-    }
-    const bool pdl = early || (pdl_on && (eq ? atoi(eq) != 0 : (T <= 64 || T > 512)));
     const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
-    if (!two_pass && aligned && a.Kpad <= 16384) {
-        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl, early);
-        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl, early);
-        return launch_reg<4>(x, ldx, K, T, a, s, pdl, early);
+    if (!knobs().quant_2pass && aligned && a.Kpad <= 16384) {
+        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl, early, want_rm);
+        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl, early, want_rm);
+        return launch_reg<4>(x, ldx, K, T, a, s, pdl, early, want_rm);
     }
-    quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a);
+    quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a, want_rm);
     return cudaGetLastError();
 }
 

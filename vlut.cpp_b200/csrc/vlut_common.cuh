@@ -95,7 +95,19 @@ __host__ __device__ inline int act_row_pos(int k128, int perm) {
     return perm ? ((k128 & 15) >> 2) * 32 + (k128 >> 4) * 4 + (k128 & 3) : k128;
 }
 
+// one weight of a batched launch (several weights that share the quantised activations)
+constexpr int MAX_BATCH = 4;
+struct TensorRef {
+    const uint8_t *w;   // T2
+    float *out;         // f32 [T][ldo]
+    int64_t N, ldo;
+    float w_scale;
+    int strip0;         // first 128-row strip of this tensor in the launch's concatenated strip index space
+};
+
 struct GemmArgs {
+    TensorRef tens[MAX_BATCH + 1];   // tens[n_tens].strip0 = total strips (sentinel); tens[0] mirrors the fields below
+    int n_tens;
     const uint8_t *w;  // T2
     ActView act;
     float *out;         // single-GPU destination, f32 [T][ldo]
@@ -106,6 +118,7 @@ struct GemmArgs {
     float *outs[8];
     int n_out;
     int multicast;
+    int vec_ok;         // scatter destinations are 16-byte aligned with ldo % 4 == 0: four rows per lane per store
     int64_t ldo;
     int64_t K, N, T, Npad;
     int type;
@@ -115,6 +128,7 @@ struct GemmArgs {
     int32_t *acc;       // int32 [CTAs][128][128] accumulation tiles of split output tiles (TCP): contributors red.add their
                         // partials, the last arriver reads the sum and writes zeros back (zeroed at allocation, self-cleaning)
     int sm_count;
+    int device;         // CUDA device ordinal (per-device caches of function attributes in the launchers)
 };
 
 // epilogue store, selected at compile time: 0 local, 1 peer scatter (NVLink P2P), 2 NVSwitch multicast (multimem.st)
@@ -129,27 +143,77 @@ __device__ __forceinline__ void store_out(float *const out, float *const *outs, 
     }
 }
 
+// 16-byte flavours of the scatter stores: four consecutive rows n .. n+3 of one token
+template <int MODE>
+__device__ __forceinline__ void store_out4(float *const out, float *const *outs, int n_out, int64_t idx, float4 v) {
+    if (MODE == 0) {
+        *reinterpret_cast<float4 *>(out + idx) = v;
+    } else if (MODE == 2) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(out + idx), "f"(v.x), "f"(v.y),
+                     "f"(v.z), "f"(v.w)
+                     : "memory");
+    } else {
+        for (int i = 0; i < n_out; i++) *reinterpret_cast<float4 *>(outs[i] + idx) = v;
+    }
+}
+
 inline __device__ int32_t wrap16(int32_t v) { return (int32_t) (int16_t) (uint16_t) ((uint32_t) v & 0xffffu); }
 
+// ---- run-time knobs ------------------------------------------------------------------------------------------------
+// Every VLUT_* environment variable the library understands, read ONCE (first use, vlut_ctx_create, or the test hook
+// vlut_reload_env) -- never on the launch path.  -1 = not set (the launcher's own policy applies).
+struct Knobs {
+    int algo;                      // VLUT_B200_ALGO      force a GEMM algorithm (VLUT_ALGO_*)
+    int host_chunk;                // VLUT_HOST_CHUNK     token chunk of the host-buffer pipeline (0 = no pipeline)
+    int pdl;                       // VLUT_PDL            programmatic dependent launch (default 1)
+    int tc_fast;                   // VLUT_TC_FAST        0 forces the exact (per-K-group drain) path
+    int tc_smem_kb, tc_stages;     // VLUT_TC_SMEM_KB, VLUT_TC_STAGES
+    int tc_grid, tc_whole, tc_split_last;   // VLUT_TC_GRID, VLUT_TC_WHOLE, VLUT_TC_SPLIT_LAST (tests: force the split paths)
+    int tc_abl, tc_debug, tc_debug_skip;    // VLUT_TC_ABL, VLUT_TC_DEBUG, VLUT_TC_DEBUG_SKIP
+    int tc_nt;                     // VLUT_TC_NT          force the TCP token tile (128 / 256)
+    int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask;   // VLUT_TCS_*
+    int quant_2pass, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
+    int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
+    int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
+};
+const Knobs &knobs();
+void knobs_reload();
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) once per (kernel instantiation, device) instead of on every launch:
+// `cache` is a static int[MAX_DEVICES] owned by the calling launcher template
+constexpr int MAX_DEVICES = 16;
+template <typename Kern>
+inline cudaError_t ensure_dyn_smem(Kern kern, size_t smem, int device, int *cache) {
+    if (device >= 0 && device < MAX_DEVICES && cache[device] >= (int) smem) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    if (e == cudaSuccess && device >= 0 && device < MAX_DEVICES) cache[device] = (int) smem;
+    return e;
+}
+
+long long *debug_buffer(cudaStream_t s, int skip);   // c_api.cu: zeroed buffer of the kernels' optional instrumentation
+
+cudaError_t measure_int8_peak(int sm_count, cudaStream_t s, int iters, double *tops, double *clk_per_mma);  // peak.cu
+
+cudaError_t launch_barrier(uint32_t *const *flags, int n, int rank, cudaStream_t s);   // barrier.cu
 // launchers (one per .cu)
 cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, uint8_t *t2, cudaStream_t s);
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);
-cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
-                            int early_ok);  // early_ok: 1 = policy, 2 = VLUT_QUANT_EARLY=1 experiment without the option
-cudaError_t launch_relayout(const ActView &a, cudaStream_t s);  // rewrite q_sw from q_rm for a.sw_tile
+// pdl: launch with the programmatic-serialisation attribute; early: row loads ahead of griddepcontrol.wait (the host has
+// proved that no kernel in flight writes x); want_rm: also write the row-major copy q_rm
+cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
+                            bool early, bool want_rm);
+cudaError_t launch_relayout(const ActView &a, cudaStream_t s);   // rewrite q_sw from q_rm for a.sw_tile / a.perm
+cudaError_t launch_unswizzle(const ActView &a, cudaStream_t s);  // materialise q_rm from q_sw
 cudaError_t launch_gemm_simple(const GemmArgs &g, cudaStream_t s);
 cudaError_t launch_scale_rows(const float *x, int64_t ldx, float *out, int64_t ldo, int64_t N, int64_t T, float sc,
                               cudaStream_t s);
-cudaError_t launch_gemm_tc(const GemmArgs &g, cudaStream_t s, int *launches);   // single pipeline (TS or SS)
-bool gemm_tc_supported(int type, int64_t K, int64_t N, int64_t T);
-cudaError_t launch_gemm_tc3(const GemmArgs &g, cudaStream_t s, int *launches);  // 256 rows / CTA, shared act stages
-bool gemm_tc3_supported(int type, int64_t K, int64_t N, int64_t T);
-cudaError_t launch_gemm_tc4(const GemmArgs &g, cudaStream_t s, int *launches);  // production: 8 decode warps, PDL
-bool gemm_tc4_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches);  // CTA pairs, cta_group::2
 bool gemm_tc5_supported(int type, int64_t K, int64_t N, int64_t T);
 cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches);  // small T: cp.async weight stream, cluster split-K
 bool gemm_tcs_supported(int type, int64_t K, int64_t N, int64_t T);
+// whole op in one launch (activation quantisation fused), T <= 8
+cudaError_t launch_gemm_gemv(const GemmArgs &g, const float *x, int64_t ldx, cudaStream_t s, int *launches);
+bool gemm_gemv_supported(int type, int64_t K, int64_t N, int64_t T, const float *x, int64_t ldx);
 cudaError_t launch_gemm_lut(const GemmArgs &g, cudaStream_t s, int *launches);
 bool gemm_lut_supported(int type, int64_t K, int64_t N, int64_t T);
 

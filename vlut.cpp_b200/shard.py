@@ -93,6 +93,7 @@ class RowShardedWeight:
             local_gguf = shard_gguf(type_, K, N, self.plan, self.rank, gguf)
         self.local = ctx.upload(type_, K, self.rows, local_gguf)
         self._symm = {}
+        self._turn = {}
 
     # ---- baseline: NCCL all-gather ----------------------------------------------------------------------
     def mul_mat(self, x: torch.Tensor, w_scale: float = 1.0) -> torch.Tensor:
@@ -102,9 +103,11 @@ class RowShardedWeight:
         return all_gather_rows(local, self.plan, self.group)
 
     # ---- fused: epilogue stores into every rank's output through symmetric memory ---------------------------
-    def symm_out(self, T: int):
+    N_BUF = 2  # result buffers per token count, used in rotation
+
+    def symm_out(self, T: int, slot: int = 0):
         """[T][N] f32 symmetric-memory output buffer (same virtual layout on every rank) + its rendezvous handle."""
-        key = T
+        key = (T, slot)
         if key not in self._symm:
             import torch.distributed._symmetric_memory as symm_mem
             buf = symm_mem.empty((T, self.N), dtype=torch.float32, device=self.ctx.device)
@@ -112,14 +115,28 @@ class RowShardedWeight:
             self._symm[key] = (buf, hdl)
         return self._symm[key]
 
+    @staticmethod
+    def flag_ptrs(hdl) -> list[int]:
+        """Per-rank flag arrays for vlut_barrier: the tail of the allocation's signal pad (zero-initialised by torch,
+        far from the words torch's own barrier uses)."""
+        size = int(hdl.signal_pad_size)
+        return [int(p) + size - 256 for p in hdl.signal_pad_ptrs]
+
     def mul_mat_fused(self, x: torch.Tensor, w_scale: float = 1.0) -> torch.Tensor:
+        """Row-sharded MUL_MAT with the all-gather fused into the GEMM epilogue.  The result buffers of one token count
+        rotate (N_BUF = 2) and every call ends with the cross-rank barrier that publishes its stores, so a fast rank can
+        never overwrite a buffer a slower peer still reads: rank A reaches the call that rewrites buffer b only after the
+        barrier of the call in between, which every peer joins after (in stream order) all its reads of b's previous
+        contents.  A RESULT IS VALID UNTIL THE SECOND NEXT CALL WITH THE SAME TOKEN COUNT."""
         T = x.shape[0]
         if self.world == 1:
             return self.ctx.mul_mat(self.local, x, w_scale=w_scale)
-        buf, hdl = self.symm_out(T)
+        slot = self._turn.get(T, 0)
+        self._turn[T] = (slot + 1) % self.N_BUF
+        buf, hdl = self.symm_out(T, slot)
         mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
         peers = [int(p) for p in hdl.buffer_ptrs]
         self.ctx.mul_mat_scatter(self.local, x, peers=peers, multicast_ptr=mc, ldo=self.N, col0=self.row0,
                                  w_scale=w_scale)
-        hdl.barrier()  # every rank's stores have landed everywhere
+        self.ctx.barrier(self.flag_ptrs(hdl), self.rank)  # every rank's stores have landed everywhere
         return buf
