@@ -37,6 +37,7 @@ SHAPES = {  # name: (n_embd, n_ff, n_head, n_head_kv)
     "bitnet-3b": (3200, 8640, 32, 32),
     "falcon3-1b": (2048, 8192, 8, 4),
     "trilm-3.9b": (3072, 9216, 24, 24),
+    "tiny": (512, 1536, 8, 4),   # test-sized
 }
 
 

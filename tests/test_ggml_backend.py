@@ -121,5 +121,5 @@ def test_scale_fusion_and_shared_activations(tmp_path, orc, type_, K, N, T, fuse
         assert np.array_equal(bits(out[i]), bits(e)), f"output {i} differs"
     # fused: the four MUL_MATs on one input (two of them with their scale folded in) run as ONE batched group
     want = ("gemm=4 quantize=1 fused_scale=2 scale_rows=1 batched=4" if fuse
-            else "gemm=4 quantize=1 fused_scale=0 scale_rows=3 batched=0")
+            else "gemm=4 quantize=1 fused_scale=0 scale_rows=3 batched=2")
     assert want in r.stdout, r.stdout

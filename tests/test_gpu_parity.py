@@ -318,16 +318,19 @@ def test_strided_output_and_errors(ctx, orc):
         ctx.upload(O.I2_V_4, 1000, 8, np.zeros(10, dtype=np.uint8))  # K % 16 != 0
 
 
+@pytest.mark.parametrize("nt", [0, 256], ids=["tile-auto", "tile-256"])
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("grid,stages", [(4, 0), (6, 2), (20, 3), (148, 0)])
 @pytest.mark.parametrize("T", [33, 64, 130, 300, 520])
-def test_streamk_split_tiles_and_ring_wrap(ctx, orc, knobs, grid, stages, T, fast):
+def test_streamk_split_tiles_and_ring_wrap(ctx, orc, knobs, grid, stages, T, fast, nt):
     """Force few persistent CTA pairs / few pipeline stages so that every pair walks several (tile, K-group) units:
     exercises the shared-memory ring wrap-around, tiles completed by a single pair (direct store), tiles split
     across pairs (int32 partials + last-arriver epilogue), the self-cleaning workspace and both drain policies (single
     drain when no int16 wrap is possible / per K-group)."""
     a = api()
-    knobs(VLUT_TC_GRID=grid, VLUT_TC_STAGES=stages, VLUT_TC_FAST=fast)
+    if nt == 256 and T <= 64:
+        pytest.skip("the 256-token tile is for T > 64")
+    knobs(VLUT_TC_GRID=grid, VLUT_TC_STAGES=stages, VLUT_TC_FAST=fast, VLUT_TC_NT=nt)
     for type_, K, N in [(O.I2_V_4, 4096, 640), (O.I1_V_2, 3200, 520)]:
         w = O.make_ternary(N, K, seed=grid)
         x = O.make_acts(T, K, seed=T, kind="uniform" if T % 2 else "normal")  # uniform: sum|q| often > 32767
@@ -338,15 +341,16 @@ def test_streamk_split_tiles_and_ring_wrap(ctx, orc, knobs, grid, stages, T, fas
             assert np.array_equal(bits(out), bits(ref)), f"rep={rep}"
 
 
+@pytest.mark.parametrize("nt", [0, 256], ids=["tile-auto", "tile-256"])
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("grid", [4, 10, 14, 22, 148])
 @pytest.mark.parametrize("T", [65, 300, 600])
-def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, knobs, grid, T, fast):
+def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, knobs, grid, T, fast, nt):
     """VLUT_TC_WHOLE=2: every CTA pair walks its share of the split units first (tiles shared with other pairs; pairs
     with no split unit, ranges crossing a tile boundary, last-arriver fix-up skipping empty pairs) and then its whole
     tiles.  Forced grids make floor(tiles / pairs) and the remainder take many values."""
     a = api()
-    knobs(VLUT_TC_GRID=grid, VLUT_TC_WHOLE=2, VLUT_TC_FAST=fast)
+    knobs(VLUT_TC_GRID=grid, VLUT_TC_WHOLE=2, VLUT_TC_FAST=fast, VLUT_TC_NT=nt)
     for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I1_V_2, 3200, 900), (O.I2_V_4, 4096, 1800)]:
         w = O.make_ternary(N, K, seed=grid)
         x = O.make_acts(T, K, seed=T, kind="uniform" if grid % 4 else "normal")

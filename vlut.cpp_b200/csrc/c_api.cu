@@ -373,7 +373,7 @@ static int want_perm(int algo, int NT) { return (algo == VLUT_ALGO_TCS && NT <= 
 
 static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo) {
     const int64_t Kpad = round_up(K, BLOCK_K);
-    const int NT = token_tile(T);
+    const int NT = (algo == VLUT_ALGO_TCP) ? token_tile_pair(T, knobs().tc_nt) : token_tile(T);
     const int64_t Tpad = round_up(T, NT);
     const int gsize = group_size(type);
     const int G = (int) ceil_div(K, gsize);
@@ -384,7 +384,7 @@ static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo) {
     if (c->gpre.reserve((size_t) Tpad * (G + 1) * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (c->nowrap.reserve((size_t) Tpad * sizeof(int32_t)) != cudaSuccess) return VLUT_ERR_NOMEM;
     bool grew = false;
-    if (c->tile_unsafe.reserve((size_t) (Tpad / 16) * sizeof(uint32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (c->tile_unsafe.reserve((size_t) (Tpad / 16 + 1) * sizeof(uint32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
     if (grew && cudaMemsetAsync(c->tile_unsafe.p, 0, c->tile_unsafe.cap, c->stream) != cudaSuccess) return VLUT_ERR_CUDA;
     c->act.q_rm = (int8_t *) c->q_rm.p;
     c->act.q_sw = (int8_t *) c->q_sw.p;

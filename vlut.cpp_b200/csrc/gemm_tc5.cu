@@ -108,7 +108,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     constexpr int NH = NT / 2;                       // tokens staged by this CTA
     constexpr int ACT_BYTES = NH * 128;              // one 128-k sub-block of this CTA's half
     constexpr int W_OFF = SPS * ACT_BYTES;           // stage: [activations][weights]
-    constexpr uint32_t A_COL0 = 2 * NT;              // two accumulators of NT columns, then two A stages
+    // TMEM: NACC accumulators of NT columns, then two A stages of 128 columns.  NT = 256 (one decoded A stage multiplies TWO
+    // 128-token halves: the weights are unpacked T/256 instead of T/128 times and every decode -> MMA hand-off feeds 2048
+    // clk of tensor-pipe time) leaves room for ONE accumulator: the drain of a tile is not overlapped with the next tile's
+    // MMAs, but its loads and unpacks are (both A stages and the whole shared-memory ring refill meanwhile).
+    constexpr int NACC = (NT > 128) ? 1 : 2;
+    constexpr uint32_t A_COL0 = NACC * NT;
     static_assert(A_COL0 + 2 * A_COLS <= 512, "TMEM budget");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_full[MAX_STAGES], s_empty[MAX_STAGES];
@@ -238,7 +243,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             Ring st, ar;
             st.init(S);
             ar.init(2);
-            uint32_t ndrain = 0;  // drains committed so far; accumulator buffer = ndrain % 2
+            uint32_t ndrain = 0;  // drains committed so far; accumulator buffer = ndrain % NACC
             if (p.pdl) ptx::pdl_wait();  // tile_fast below is written by the predecessor (quantise) kernel
             int run_tile = -1;
             bool fast = false, open = false;
@@ -247,9 +252,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     run_tile = w.tile;
                     fast = tile_fast(w.tt);
                 }
-                const uint32_t ab = ndrain & 1;
+                const uint32_t ab = ndrain % NACC;
                 if (!open) {
-                    ptx::mbar_wait_cluster(ptx::smem_u32(&s_accempty[ab]), ((ndrain >> 1) & 1) ^ 1);
+                    ptx::mbar_wait_cluster(ptx::smem_u32(&s_accempty[ab]), ((ndrain / NACC) & 1) ^ 1);
                     ptx::tc_fence_after();
                 }
                 const uint32_t d_tmem = tmem_base + ab * NT;
@@ -405,7 +410,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             if (!complete) {
                 const long long x = (long long) tile * p.G - sbase;
                 const int b_first = (int) (((x + 1) * npairs - 1) / SU);
-                slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * 128);
+                slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * NT);
             }
             if (et < NT) s_sc[et] = __ldg(p.g.act.scales + t0 + et);
 
@@ -429,12 +434,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
 
             for (int u = ra; u <= rb; u++, w.next()) {
                 if (fast && u != rb) continue;  // fast path: a single drain at the end of the run
-                const uint32_t ab = ndrain & 1;
+                const uint32_t ab = ndrain % NACC;
                 for (int i = et; i < NT; i += 128)
                     s_gs[i] = __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + w.g + 1) -
                               __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + (fast ? g_begin : w.g));
                 ptx::bar_sync(1, 128);
-                ptx::mbar_wait(ptx::smem_u32(&s_accfull[ab]), (ndrain >> 1) & 1);
+                ptx::mbar_wait(ptx::smem_u32(&s_accfull[ab]), (ndrain / NACC) & 1);
                 mark(0);
                 ptx::tc_fence_after();
                 const uint32_t ta = tmem_base + ((uint32_t) (ew * 32) << 16) + ab * NT;
@@ -531,7 +536,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
 template <int NT, int SPS, int OUT>
 static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     const Knobs &kn = knobs();
-    const int budget = kn.tc_smem_kb * 1024;
+    // 200 KB by default; the 256-token tile (40 KB stages) takes 5 stages = 201 KB + alignment slack
+    const int budget = (NT > 128 && kn.tc_smem_kb == 200 ? 204 : kn.tc_smem_kb) * 1024;
     p.stage_bytes = SPS * (NT / 2 * 128 + SUB_W_BYTES);  // multiple of 1024
     int ns = (budget - 1024) / p.stage_bytes;
     if (ns > MAX_STAGES) ns = MAX_STAGES;
@@ -559,8 +565,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     cfg.numAttrs = p.pdl ? 1 : 0;
     // persistent: one CTA pair per co-resident cluster
     int npairs = sm_count / 2;
-    static int max_clusters[3][3] = {};  // cached per (NT, OUT) instantiation below
-    int &cached = max_clusters[NT == 128 ? 0 : (NT == 64 ? 1 : 2)][OUT];
+    static int cached = 0;   // per (NT, SPS, OUT) instantiation
     if (cached == 0) {
         cfg.gridDim = dim3((unsigned) (2 * npairs));
         int n = 0;
@@ -635,6 +640,7 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     switch (NT) {
         case 64: return tc5::launch_one<64, 2>(p, g.sm_count, s);
         case 128: return tc5::launch_one<128, 4>(p, g.sm_count, s);
+        case 256: return tc5::launch_one<256, 2>(p, g.sm_count, s);
         default: return cudaErrorInvalidValue;
     }
 }

@@ -308,13 +308,28 @@ ggml_status compute_group(backend_ctx *b, const mm_item *items, int n) {
         ldos[i] = (int64_t) (items[i].out_t->nb[1] / sizeof(float));
         scales[i] = items[i].w_scale;
     }
-    const int rc = vlut_mul_mat_batch(b->ctx, n, types, K, Ns, T, t2, (const float *) src1->data,
-                                      (int64_t) (src1->nb[1] / sizeof(float)), outs, ldos, scales, VLUT_ALGO_AUTO);
+    // the input may already be quantised in the workspace (an earlier MUL_MAT of this graph read it)
+    const bool reuse = b->act.src1 == src1 && b->act.K == K && b->act.T == T && b->act.i1_family == is_i1_family(items[0].dst->src[0]->type);
+    int rc;
+    if (reuse) {
+        rc = vlut_gemm_batch(b->ctx, n, types, K, Ns, T, t2, outs, ldos, scales, VLUT_ALGO_AUTO);
+    } else {
+        rc = vlut_mul_mat_batch(b->ctx, n, types, K, Ns, T, t2, (const float *) src1->data,
+                                (int64_t) (src1->nb[1] / sizeof(float)), outs, ldos, scales, VLUT_ALGO_AUTO);
+        b->n_quantize++;
+        b->act = act_cache{};
+        if (rc == VLUT_OK && vlut_ctx_last_algo(b->ctx) != VLUT_ALGO_GEMV) {
+            b->act.src1 = src1;
+            b->act.lo = (const char *) src1->data;
+            b->act.hi = (const char *) src1->data + (size_t) (T - 1) * src1->nb[1] + (size_t) K * sizeof(float);
+            b->act.K = K;
+            b->act.T = T;
+            b->act.i1_family = is_i1_family(items[0].dst->src[0]->type);
+        }
+    }
     if (rc != VLUT_OK) return mm_fail(b, items[0].dst, rc);
     b->n_mul_mat += n;
-    b->n_quantize++;
-    b->n_batched += (n > 1) ? n : 0;
-    b->act = act_cache{};
+    b->n_batched += n;
     for (int i = 0; i < n; i++) note_write(b, items[i].out_t);
     return GGML_STATUS_SUCCESS;
 }

@@ -58,6 +58,15 @@ __host__ __device__ inline int t2_shift(int64_t k) {
 
 // token tile (UMMA N) used for a token count
 __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : 128; }
+// The CTA-pair kernel also has a 256-token tile (one decoded A stage feeds two 128-token halves).  It pays when the token
+// count fills whole 256-tiles well: T > 256 with at most 1/8 of the last tile padded (crossover measured).
+__host__ __device__ inline int token_tile_pair(int64_t T, int forced) {
+    if (forced == 64 || forced == 128 || forced == 256) return (forced == 64 && T > 64) ? 128 : forced;
+    if (T <= 64) return 64;
+    if (T <= 256) return 128;
+    const int64_t pad256 = round_up(T, 256) - T, pad128 = round_up(T, 128) - T;
+    return (pad256 - pad128) * 8 <= round_up(T, 256) ? 256 : 128;
+}
 
 // ---- activation workspace -------------------------------------------------------------------------------
 // q_rm   int8  [Tpad][Kpad]   row-major, zero padded (SIMPLE kernel, test read-back)
