@@ -167,6 +167,34 @@ int vlut_op_supported(int type, int64_t K, int64_t N, int64_t T);
 int vlut_pick_algo(int type, int64_t K, int64_t N, int64_t T);
 int vlut_ctx_last_algo(const vlut_ctx *ctx);
 
+/* ---- multi-GPU behind the C boundary: ONE process, G GPUs of one box ----------------------------------------------------
+ * Output-row tensor parallelism (the thread split of ggml-cpu.c:1413-1419 across GPUs).  Member 0 of a group is the ROOT:
+ * activations live there, every member quantises them itself (peer read over NVLink), computes its row shard, and its GEMM
+ * epilogue stores the slice straight into the destination buffer(s) -- the gather is fused into the GEMM; ordering between the
+ * members' streams is by CUDA events.  What the ggml plugin uses for VLUT_B200_GPUS=G (one logical ggml device owning G GPUs).
+ * `devices` may name the same ordinal more than once (several members on one GPU: emulation for tests). */
+typedef struct vlut_group vlut_group;
+typedef struct vlut_group_weight vlut_group_weight;
+int       vlut_group_create(int n_dev, const int *devices, vlut_group **out);
+void      vlut_group_destroy(vlut_group *g);
+int       vlut_group_size(const vlut_group *g);
+vlut_ctx *vlut_group_ctx(vlut_group *g, int member);
+/* rows [row0, row0+rows) of an N-row weight owned by `member`: whole 128-row strips, shards differ by at most one strip */
+int       vlut_group_rows(const vlut_group *g, int64_t N, int member, int64_t *row0, int64_t *rows);
+/* bytes of member 0's repacked shard (what a caller that owns member 0's storage -- the ggml buffer -- must provide) */
+size_t    vlut_group_shard0_nbytes(const vlut_group *g, int type, int64_t K, int64_t N);
+/* Row-shard a GGUF-packed weight on the host and upload + repack every member's shard.  shard0_dev: caller-owned storage
+ * for member 0's shard on the root (the ggml tensor's data), or NULL to let the group allocate it. */
+int       vlut_group_upload_weights(vlut_group *g, int type, int64_t K, int64_t N, const void *gguf_host, void *shard0_dev,
+                                    vlut_group_weight **out);
+void      vlut_group_free_weights(vlut_group *g, vlut_group_weight *w);
+/* The op.  x_root f32 [T][ldx] on the root.  outs[j] = base of an f32 [T][ldo] result buffer (peer-accessible device memory);
+ * n_dst = 1 gathers into one buffer (typically on the root), n_dst = G all-gathers into a buffer on every member.  On return
+ * the root's stream is ordered after every member's stores. */
+int       vlut_group_mul_mat(vlut_group *g, const vlut_group_weight *w, int64_t T, const float *x_root, int64_t ldx,
+                             float *const *outs, int n_dst, int64_t ldo, float w_scale);
+int       vlut_group_sync(vlut_group *g);
+
 /* ---- measurement ------------------------------------------------------------------------------------- */
 /* The int8 tensor-pipe peak of the context's device, measured: one CTA per SM issuing tcgen05.mma kind::i8 (M128 N256 K32,
  * A in TMEM like the GEMM kernels) back to back, timed with CUDA events.  *tops = 2 * MAC / s over the whole device in

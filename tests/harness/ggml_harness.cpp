@@ -163,10 +163,10 @@ int main(int argc, char **argv) {
         stats_fn stats = (stats_fn) ggml_backend_reg_get_proc_address(reg, "vlut_b200_backend_stats");
         stats_fn stats2 = (stats_fn) ggml_backend_reg_get_proc_address(reg, "vlut_b200_backend_stats2");
         if (stats) {
-            int64_t s4[5] = {0, 0, 0, 0, 0};
+            int64_t s4[6] = {0, 0, 0, 0, 0, 0};
             if (stats2) stats2(backend, s4); else stats(backend, s4);
-            printf("stats: gemm=%lld quantize=%lld fused_scale=%lld scale_rows=%lld batched=%lld\n", (long long) s4[0],
-                   (long long) s4[1], (long long) s4[2], (long long) s4[3], (long long) s4[4]);
+            printf("stats: gemm=%lld quantize=%lld fused_scale=%lld scale_rows=%lld batched=%lld sharded=%lld\n", (long long) s4[0],
+                   (long long) s4[1], (long long) s4[2], (long long) s4[3], (long long) s4[4], (long long) s4[5]);
         }
         out.resize((size_t) 5 * T * N);
         for (int i = 0; i < 5; i++)

@@ -50,8 +50,23 @@ def main():
             msg += f" fused FAILED: {type(e).__name__}: {e}"
             ok = False
         print(msg, flush=True)
+        # repeated calls rotate the result buffers: every one of them must hold the right bits
+        try:
+            for rep in range(5):
+                o = W.mul_mat_fused(xd)
+                torch.cuda.synchronize()
+                ok &= bool(np.array_equal(o.cpu().numpy().view(np.uint32), ref.view(np.uint32)))
+        except Exception as e:  # noqa: BLE001
+            print(f"rank {rank}: repeated fused calls FAILED: {e}", flush=True)
+            ok = False
+
+        def fused_scalar(xx):
+            return W.mul_mat_fused(xx)
+
         # timing, device events, max over ranks
-        for name, fn in (("nccl", W.mul_mat), ("fused", W.mul_mat_fused)):
+        for name, fn in (("nccl", W.mul_mat), ("fused (16-byte scatter stores)", W.mul_mat_fused), ("fused (4-byte scatter stores)", fused_scalar)):
+            os.environ["VLUT_SCATTER_VEC"] = "0" if "4-byte" in name else "1"
+            api.reload_env()
             try:
                 for _ in range(5):
                     fn(xd)
@@ -70,6 +85,8 @@ def main():
             except Exception as e:  # noqa: BLE001
                 if rank == 0:
                     print(f"   {name}: timing failed: {e}", flush=True)
+    os.environ["VLUT_SCATTER_VEC"] = "1"
+    api.reload_env()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.all_reduce(flag, op=dist.ReduceOp.MIN)
     if rank == 0:

@@ -123,3 +123,37 @@ def test_scale_fusion_and_shared_activations(tmp_path, orc, type_, K, N, T, fuse
     want = ("gemm=4 quantize=1 fused_scale=2 scale_rows=1 batched=4" if fuse
             else "gemm=4 quantize=1 fused_scale=0 scale_rows=3 batched=2")
     assert want in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["direct", "sched", "block"])
+@pytest.mark.parametrize("gpus", [2, 3])
+def test_one_logical_device_owning_several_gpus(tmp_path, orc, mode, gpus):
+    """VLUT_B200_GPUS=G: ONE ggml device whose set_tensor row-shards every vlut weight over G GPUs and whose graph_compute
+    runs the MUL_MAT on all of them with the gather fused into the GEMM epilogues (SURVEY.md section 8e "Exposure").  On a box
+    with fewer GPUs the members share GPU 0 (VLUT_B200_GROUP_SAME_DEVICE): same code path."""
+    need_artifacts()
+    import torch
+    env = {"VLUT_B200_GPUS": str(gpus)}
+    if torch.cuda.device_count() < gpus:
+        env["VLUT_B200_GROUP_SAME_DEVICE"] = "1"
+    type_, K, N, T = O.I2_V_4, 2048, 1000, 70
+    w = O.make_ternary(N, K, seed=gpus)
+    x = O.make_acts(T, K, seed=N, kind="outlier")
+    packed = orc.pack(type_, w)
+    r = run_harness(tmp_path, mode, type_, K, N, T, packed, x, env=env)
+    assert r.returncode == 0, r.stdout
+    assert f"row-sharded over {gpus} GPUs" in r.stdout, r.stdout
+    base = orc.mul_mat(type_, packed, x, N)
+    if mode == "direct":
+        out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(T, N)
+        assert np.array_equal(bits(out), bits(base))
+    elif mode == "sched":
+        out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(T, N)
+        assert np.array_equal(bits(out), bits(base + np.float32(1.0)))
+    else:
+        out = np.fromfile(tmp_path / "out.bin", dtype=np.float32).reshape(5, T, N)
+        expect = [base * np.float32(0.37), base * np.float32(-1.9), base, base * np.float32(0.37), base + np.float32(1.0)]
+        for i, e in enumerate(expect):
+            assert np.array_equal(bits(out[i]), bits(e)), f"output {i} differs"
+        assert "sharded=4" in r.stdout, r.stdout

@@ -48,6 +48,16 @@ _SIGNATURES = {
     "vlut_gemm": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, f32, cint]),
     "vlut_mul_mat": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_mul_mat_scatter": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, cint, cint, i64, f32, cint]),
+    "vlut_group_create": (cint, [cint, vp, C.POINTER(vp)]),
+    "vlut_group_destroy": (None, [vp]),
+    "vlut_group_size": (cint, [vp]),
+    "vlut_group_ctx": (vp, [vp, cint]),
+    "vlut_group_rows": (cint, [vp, i64, cint, C.POINTER(i64), C.POINTER(i64)]),
+    "vlut_group_shard0_nbytes": (C.c_size_t, [vp, cint, i64, i64]),
+    "vlut_group_upload_weights": (cint, [vp, cint, i64, i64, vp, vp, C.POINTER(vp)]),
+    "vlut_group_free_weights": (None, [vp, vp]),
+    "vlut_group_mul_mat": (cint, [vp, vp, i64, vp, i64, vp, cint, i64, f32]),
+    "vlut_group_sync": (cint, [vp]),
     "vlut_barrier": (cint, [vp, vp, cint, cint]),
     "vlut_mul_mat_host": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_scale_rows": (cint, [vp, vp, i64, vp, i64, i64, i64, f32]),

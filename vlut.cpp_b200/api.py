@@ -253,3 +253,59 @@ class Context:
     @property
     def last_algo(self) -> int:
         return int(_lib.lib().vlut_ctx_last_algo(self._h))
+
+
+class Group:
+    """vlut_group: ONE process driving G GPUs (output-row tensor parallelism behind the C boundary).  Member 0 is the root:
+    activations live there, the gathered result lands in the buffer(s) the caller names."""
+
+    def __init__(self, devices: list[int]):
+        if not torch.cuda.is_available():
+            raise RuntimeError("vlut_b200 needs CUDA devices (sm_100a); there is no CPU fallback")
+        arr = (C.c_int * len(devices))(*devices)
+        h = C.c_void_p()
+        check(_lib.lib().vlut_group_create(len(devices), arr, C.byref(h)), "vlut_group_create")
+        self._h = h
+        self.devices = list(devices)
+        self._weights = []
+
+    def rows(self, N: int, member: int) -> tuple[int, int]:
+        r0, rows = C.c_int64(0), C.c_int64(0)
+        check(_lib.lib().vlut_group_rows(self._h, N, member, C.byref(r0), C.byref(rows)), "vlut_group_rows")
+        return r0.value, rows.value
+
+    def upload(self, type_: int, K: int, N: int, gguf: np.ndarray):
+        g = np.ascontiguousarray(gguf, dtype=np.uint8)
+        assert g.size == nbytes(type_, K, N)
+        w = C.c_void_p()
+        check(_lib.lib().vlut_group_upload_weights(self._h, type_, K, N, g.ctypes.data, None, C.byref(w)),
+              "vlut_group_upload_weights")
+        self._weights.append(w)
+        return (w, type_, K, N)
+
+    def mul_mat(self, w, x_root: torch.Tensor, outs: list[torch.Tensor], w_scale: float = 1.0) -> None:
+        """x on the root; outs = one [T][N] f32 buffer (gather) or one per member (all-gather)."""
+        wh, type_, K, N = w
+        T = x_root.shape[0]
+        assert x_root.dtype == torch.float32 and x_root.stride(1) == 1 and x_root.shape[1] == K
+        for o in outs:
+            assert o.dtype == torch.float32 and o.shape == (T, N) and o.stride(1) == 1
+        arr = (C.c_void_p * len(outs))(*[o.data_ptr() for o in outs])
+        check(_lib.lib().vlut_group_mul_mat(self._h, wh, T, x_root.data_ptr(), x_root.stride(0), arr, len(outs),
+                                            outs[0].stride(0), w_scale), "vlut_group_mul_mat")
+
+    def sync(self) -> None:
+        check(_lib.lib().vlut_group_sync(self._h), "vlut_group_sync")
+
+    def close(self) -> None:
+        if getattr(self, "_h", None):
+            for w in self._weights:
+                _lib.lib().vlut_group_free_weights(self._h, w)
+            _lib.lib().vlut_group_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

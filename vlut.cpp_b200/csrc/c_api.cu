@@ -50,12 +50,14 @@ void knobs_reload() {
     k.tc_debug = env_int("VLUT_TC_DEBUG", 0);
     k.tc_debug_skip = env_int("VLUT_TC_DEBUG_SKIP", 0);
     k.tc_nt = env_int("VLUT_TC_NT", 0);
+    k.tc_astages = env_int("VLUT_TC_ASTAGES", 0);
     k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
     k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
     k.tcs_issuers = env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
     k.tcs_depth = env_int("VLUT_TCS_DEPTH", 3);
     k.tcs_dbg_cta = env_int("VLUT_TCS_DBG_CTA", 0);
     k.tcs_dbg_mask = env_int("VLUT_TCS_DBG_MASK", 15);
+    k.tcs_pre = env_int("VLUT_TCS_PRE", -1);
     k.quant_2pass = env_int("VLUT_QUANT_2PASS", 0);
     k.quant_pdl = env_int("VLUT_QUANT_PDL", -1);
     k.quant_early = env_int("VLUT_QUANT_EARLY", -1);
@@ -129,8 +131,8 @@ struct vlut_ctx {
     // `inflight_unknown` says some launch since then wrote a range we do not know (scatter epilogue, scale_rows, ...).
     struct Range { const char *lo, *hi; };
     std::vector<Range> inflight;
-    bool inflight_unknown = true;
-    bool last_was_gemm = false;
+    bool inflight_unknown = false;
+    bool prev_tracked = false;   // the last launch was a quantise / GEMM kernel of this library (programmatic chain)
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
     std::vector<cudaEvent_t> ev_in, ev_done;
 };
@@ -296,10 +298,14 @@ int vlut_dev_memset(vlut_ctx *c, void *dst_dev, int value, size_t nbytes) {
 }
 
 static int check_shape(int type, int64_t K, int64_t N);
-// a kernel of ours that writes memory the early-read bookkeeping does not track was just launched
+// A kernel of ours that is launched WITHOUT the programmatic attribute and never signals launch_dependents (repack,
+// scale_rows, the anchor / LUT kernels, re-tiling, the barrier, the peak loop) was just launched.  It starts only after
+// everything before it has completed, and -- its completion being the implicit trigger -- its successor starts only after it
+// has completed: a full serialisation point of the stream.  Nothing launched before or by it can race with a later early read.
 static void note_foreign_write(vlut_ctx *c) {
-    c->inflight_unknown = true;
-    c->last_was_gemm = false;
+    c->inflight.clear();
+    c->inflight_unknown = false;
+    c->prev_tracked = false;
 }
 
 size_t vlut_gguf_nbytes(int type, int64_t K, int64_t N) {
@@ -371,9 +377,10 @@ int vlut_shard_rows_host(int type, int64_t K, int64_t N, int64_t row0, int64_t r
 static int want_sw_tile(int algo, int NT) { return (algo == VLUT_ALGO_TCP && NT >= 64) ? NT / 2 : NT; }
 static int want_perm(int algo, int NT) { return (algo == VLUT_ALGO_TCS && NT <= 32) ? 1 : 0; }
 
-static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo) {
+static int prepare_act(vlut_ctx *c, int type, int64_t K, int64_t T, int algo, int64_t N_hint) {
     const int64_t Kpad = round_up(K, BLOCK_K);
-    const int NT = (algo == VLUT_ALGO_TCP) ? token_tile_pair(T, knobs().tc_nt) : token_tile(T);
+    const int NT = (algo == VLUT_ALGO_TCP) ? token_tile_pair(K, N_hint, T, group_size(type), c->sm_count, knobs().tc_nt)
+                                           : token_tile(T);
     const int64_t Tpad = round_up(T, NT);
     const int gsize = group_size(type);
     const int G = (int) ceil_div(K, gsize);
@@ -431,12 +438,14 @@ static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx,
     if (!type_valid(type) || K <= 0 || K % 4) return VLUT_ERR_INVALID;
     CK(cudaSetDevice(c->device));
     if (algo == VLUT_ALGO_AUTO) algo = vlut_pick_algo(type, K, N_hint, T);
-    int rc = prepare_act(c, type, K, T, algo);
+    int rc = prepare_act(c, type, K, T, algo, N_hint);
     if (rc) return rc;
     // x is not written by any kernel of this context that may still be running: the last launch was a GEMM and the
     // output ranges of every GEMM launched since the last fully serialising launch are known and do not meet x
     const char *xl = (const char *) x_dev, *xh = xl + ((size_t) (T - 1) * ldx + K) * sizeof(float);
-    bool untouched = c->last_was_gemm && !c->inflight_unknown;
+    // ... and the launch right before this one is one of the tracked kernels (quantise / GEMM): behind a plain launch the
+    // early reads would rely on the implicit completion trigger alone, without the dependency wait's memory flush
+    bool untouched = c->prev_tracked && !c->inflight_unknown;
     for (const vlut_ctx::Range &r : c->inflight) untouched = untouched && (xh <= r.lo || xl >= r.hi);
     const QuantPolicy qp = quant_policy(T, untouched, c->inputs_visible != 0);
     // q_rm (row-major copy) is only written for the kernels that read it; otherwise it is materialised on demand
@@ -444,7 +453,7 @@ static int quantize_impl(vlut_ctx *c, int type, const float *x_dev, int64_t ldx,
     CK(launch_quantize(x_dev, ldx, K, T, c->act, c->stream, qp.pdl, qp.early, want_rm));
     c->act_rm_valid = want_rm;
     c->launches++;
-    c->last_was_gemm = false;
+    c->prev_tracked = true;
     if (!qp.pdl) {   // launched without the programmatic attribute: starts after everything before it has completed
         c->inflight.clear();
         c->inflight_unknown = false;
@@ -460,7 +469,7 @@ static int ensure_q_rm(vlut_ctx *c) {
     c->act_rm_valid = true;
     c->inflight.clear();           // plain launch: serialises the stream
     c->inflight_unknown = false;
-    c->last_was_gemm = false;
+    c->prev_tracked = false;
     return VLUT_OK;
 }
 
@@ -637,7 +646,7 @@ static int gemm_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, i
         c->inflight.clear();
         c->inflight_unknown = false;
     }
-    c->last_was_gemm = true;
+    c->prev_tracked = knobs().pdl && algo != VLUT_ALGO_SIMPLE && algo != VLUT_ALGO_LUT;
     if (n_out > 0 || c->inflight.size() >= 8) {
         c->inflight_unknown = true;
     } else {
@@ -679,7 +688,7 @@ static int gemv_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, i
     c->launches += launches;
     c->last_algo = VLUT_ALGO_GEMV;
     c->act_T = 0;   // the workspace holds no quantisation of this x
-    c->last_was_gemm = true;
+    c->prev_tracked = true;
     if (!knobs().pdl) {
         c->inflight.clear();
         c->inflight_unknown = false;
@@ -778,7 +787,7 @@ int vlut_barrier(vlut_ctx *c, void *const *flags_dev, int n_ranks, int rank) {
     c->launches++;
     c->inflight.clear();   // plain launch: everything before it has completed when it runs
     c->inflight_unknown = false;
-    c->last_was_gemm = false;
+    c->prev_tracked = false;
     return VLUT_OK;
 }
 

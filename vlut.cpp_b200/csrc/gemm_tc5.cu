@@ -25,8 +25,7 @@ namespace vlut {
 namespace tc5 {
 
 constexpr int THREADS = 480;
-constexpr int SPA = 4;             // 128-k sub-blocks per A stage / decode->MMA hand-off
-constexpr int A_COLS = SPA * 32;   // TMEM columns of one A stage
+constexpr int MAX_NA = 4;          // A stages in TMEM (ring)
 constexpr int MAX_STAGES = 12;
 constexpr int SUB_W_BYTES = 4096;
 
@@ -101,8 +100,13 @@ struct Ring {
 };
 
 // NT: tokens per tile (N of the pair MMA); every CTA stages NT/2 of them.  OUT: epilogue store flavour.
-template <int NT, int SPS, int OUT>
+// SPA: 128-k sub-blocks per A stage (= per decode -> MMA hand-off); NA: A stages in TMEM.  (SPA, NA) = (4, 2): two hand-offs of
+// 512 k in flight; (2, 4): four of 256 k -- the in-kernel timeline (profiles/r2_timeline_tcp.txt) showed the issuer waiting
+// ~700 clk per 512-k block for the decode -> st -> wait::st -> remote-arrive chain with only two stages to hide it behind.
+template <int NT, int SPS, int OUT, int SPA, int NA>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
+    constexpr int A_COLS = SPA * 32;                 // TMEM columns of one A stage
+    static_assert(NA <= MAX_NA, "A ring");
     static_assert(SPA % SPS == 0, "an A stage is a whole number of shared-memory stages");
     static_assert(NT % 32 == 0 && NT >= 32 && NT <= 256, "pair MMA with A in TMEM: N multiple of 32");
     constexpr int NH = NT / 2;                       // tokens staged by this CTA
@@ -114,10 +118,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     // MMAs, but its loads and unpacks are (both A stages and the whole shared-memory ring refill meanwhile).
     constexpr int NACC = (NT > 128) ? 1 : 2;
     constexpr uint32_t A_COL0 = NACC * NT;
-    static_assert(A_COL0 + 2 * A_COLS <= 512, "TMEM budget");
+    static_assert(A_COL0 + NA * A_COLS <= 512, "TMEM budget");
     extern __shared__ __align__(1024) uint8_t smem_raw[];
     __shared__ __align__(8) uint64_t s_full[MAX_STAGES], s_empty[MAX_STAGES];
-    __shared__ __align__(8) uint64_t s_afull[2], s_aempty[2];
+    __shared__ __align__(8) uint64_t s_afull[MAX_NA], s_aempty[MAX_NA];
     __shared__ __align__(8) uint64_t s_accfull[2], s_accempty[2];
     __shared__ uint32_t s_tmem_base;
     __shared__ int s_last;
@@ -139,9 +143,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             ptx::mbar_init(ptx::smem_u32(&s_full[s]), 2);       // the two producer warps (arrive.expect_tx each)
             ptx::mbar_init(ptx::smem_u32(&s_empty[s]), 8 + 1);  // 8 local decode warps + the leader's multicast commit
         }
-        for (int d = 0; d < 2; d++) {
+        for (int d = 0; d < NA; d++) {
             ptx::mbar_init(ptx::smem_u32(&s_afull[d]), 16);     // used in the leader: decode warps of both CTAs
             ptx::mbar_init(ptx::smem_u32(&s_aempty[d]), 1);
+        }
+        for (int d = 0; d < 2; d++) {
             ptx::mbar_init(ptx::smem_u32(&s_accfull[d]), 1);
             ptx::mbar_init(ptx::smem_u32(&s_accempty[d]), 8);   // used in the leader: epilogue warps of both CTAs
         }
@@ -242,7 +248,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             w.init(p, rg);
             Ring st, ar;
             st.init(S);
-            ar.init(2);
+            ar.init(NA);
             uint32_t ndrain = 0;  // drains committed so far; accumulator buffer = ndrain % NACC
             if (p.pdl) ptx::pdl_wait();  // tile_fast below is written by the predecessor (quantise) kernel
             int run_tile = -1;
@@ -311,13 +317,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         const int m = q * 32 + lane;    // weight row inside the strip == TMEM lane
         constexpr int CPS = 2 * SPS;    // 64-k chunks per stage
         constexpr int CPH = CPS / 2;    // chunks per half
-        const uint32_t afull_leader0 = ptx::mapa(ptx::smem_u32(&s_afull[0]), 0);
-        const uint32_t afull_leader1 = ptx::mapa(ptx::smem_u32(&s_afull[1]), 0);
+        const uint32_t afull_leader0 = ptx::mapa(ptx::smem_u32(&s_afull[0]), 0);   // the ring's barriers are 8 bytes apart
         Walk w;
         w.init(p, rg);
         Ring st, ar;
         st.init(S);
-        ar.init(2);
+        ar.init(NA);
         int ab0 = 0, s0 = 0;            // position of the stage whose words are in cw: unit w, A block ab0, sub-block s0
         uint4 cw[CPH];
         int ns = 0;
@@ -373,7 +378,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                 ptx::tc_fence_before();
                 __syncwarp();
                 // A-ready goes to the leader; it also tells the leader that this CTA's activation half has landed
-                if (lane == 0) ptx::mbar_arrive_cluster(ar.i ? afull_leader1 : afull_leader0);
+                if (lane == 0) ptx::mbar_arrive_cluster(afull_leader0 + 8u * (uint32_t) ar.i);
                 mark(9);
                 ar.advance();
             }
@@ -412,7 +417,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                 const int b_first = (int) (((x + 1) * npairs - 1) / SU);
                 slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * NT);
             }
-            if (et < NT) s_sc[et] = __ldg(p.g.act.scales + t0 + et);
+            for (int i = et; i < NT; i += 128) s_sc[i] = __ldg(p.g.act.scales + t0 + i);
 
             auto emit = [&](int c0, const int32_t (&vals)[16]) {
                 if (complete) {
@@ -533,7 +538,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     }
 }
 
-template <int NT, int SPS, int OUT>
+template <int NT, int SPS, int OUT, int SPA, int NA>
 static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     const Knobs &kn = knobs();
     // 200 KB by default; the 256-token tile (40 KB stages) takes 5 stages = 201 KB + alignment slack
@@ -550,7 +555,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     if (ns < MIN_STAGES) return cudaErrorInvalidValue;
     p.nstages = ns;
     const size_t smem = (size_t) ns * p.stage_bytes + 1024;
-    auto kern = kernel<NT, SPS, OUT>;
+    auto kern = kernel<NT, SPS, OUT, SPA, NA>;
     static int smem_set[MAX_DEVICES] = {};
     cudaError_t e = ensure_dyn_smem(kern, smem, p.g.device, smem_set);
     if (e != cudaSuccess) return e;
@@ -606,10 +611,10 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     return cudaLaunchKernelEx(&cfg, kern, p);
 }
 
-template <int NT, int SPS>
+template <int NT, int SPS, int SPA, int NA>
 static cudaError_t launch_one(Params &p, int sm_count, cudaStream_t s) {
-    if (p.g.n_out == 0) return launch_out<NT, SPS, 0>(p, sm_count, s);
-    return p.g.multicast ? launch_out<NT, SPS, 2>(p, sm_count, s) : launch_out<NT, SPS, 1>(p, sm_count, s);
+    if (p.g.n_out == 0) return launch_out<NT, SPS, 0, SPA, NA>(p, sm_count, s);
+    return p.g.multicast ? launch_out<NT, SPS, 2, SPA, NA>(p, sm_count, s) : launch_out<NT, SPS, 1, SPA, NA>(p, sm_count, s);
 }
 
 }  // namespace tc5
@@ -638,9 +643,11 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.dbg = kn.tc_debug ? debug_buffer(s, kn.tc_debug_skip) : nullptr;
     if (launches) *launches += 1;
     switch (NT) {
-        case 64: return tc5::launch_one<64, 2>(p, g.sm_count, s);
-        case 128: return tc5::launch_one<128, 4>(p, g.sm_count, s);
-        case 256: return tc5::launch_one<256, 2>(p, g.sm_count, s);
+        case 64: return tc5::launch_one<64, 2, 4, 2>(p, g.sm_count, s);
+        // A-stage depth (measured, profiles/r2_tcp_tiles.txt): the 128-token tile is faster with two hand-offs of 512 k
+        // (T = 512: 26.8 vs 32.5 us), the 256-token tile with four of 256 k (T = 2048: 87.0 vs 91.1 us)
+        case 128: return kn.tc_astages == 4 ? tc5::launch_one<128, 2, 2, 4>(p, g.sm_count, s) : tc5::launch_one<128, 4, 4, 2>(p, g.sm_count, s);
+        case 256: return kn.tc_astages == 2 ? tc5::launch_one<256, 2, 4, 2>(p, g.sm_count, s) : tc5::launch_one<256, 2, 2, 4>(p, g.sm_count, s);
         default: return cudaErrorInvalidValue;
     }
 }

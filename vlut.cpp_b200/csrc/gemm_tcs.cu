@@ -69,6 +69,7 @@ struct Params {
     int asb_shift;
     int allow_fast, pdl;
     int issuers;    // MMA issuer warps used on the fast path (2; 1 = experiment / fallback)
+    int pre;        // weight-ring slots requested before the activation tile is on its way (the rest right after)
     long long *dbg;   // optional timeline of one CTA (VLUT_TC_DEBUG=1): [4 roles][256] x (clock64, kind)
     int dbg_cta, dbg_mask;
 };
@@ -175,12 +176,23 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             }
             ptx::cp_async_commit();
         };
-        // weights are static data: the stream starts now, whatever the predecessor kernel (quantise) is still doing
+        // weights are static data: the stream starts now, whatever the predecessor kernel (quantise) is still doing.
+        // (`pre` < DT is an experiment knob, VLUT_TCS_PRE: request only `pre` ring slots here and the rest once the
+        // activation producer has its first stage on the way.  The in-kernel timeline shows the first MMA ~2200 clk after
+        // the first weights land; the hypothesis that the activation copies queue behind the 10 MB of weight prefetch did
+        // not hold: delaying the prefetch measured 0.3-0.6 us slower, profiles/r2_tcs_pre.txt.)
 #pragma unroll
-        for (int i = 0; i < DT; i++) issue(ph + NPH * i, i);
+        for (int i = 0; i < DT; i++)
+            if (i < p.pre) issue(ph + NPH * i, i);
         // barriers / TMEM address are set up by warp 20 meanwhile
         ptx::bar_sync(2, THREADS);
         ptx::tc_fence_after();
+        if (p.pre < DT) {
+            ptx::bar_sync(3, DEC_THREADS + 32);   // the activation producer arrives after issuing its first copy
+#pragma unroll
+            for (int i = 0; i < DT; i++)
+                if (i >= p.pre) issue(ph + NPH * i, i);
+        }
         const uint32_t tmem_base = s_tmem_base;
         const uint32_t taddr0 = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0;
         int slot = 0;
@@ -292,8 +304,10 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
                 }
                 __syncwarp();
                 mark(1);
+                if (asi == 0 && p.pre < DT) ptx::bar_arrive(3, DEC_THREADS + 32);   // releases the rest of the weight prefetch
                 if (++ring == p.NAS) { ring = 0; ph ^= 1; }
             }
+            if (n_as == 0 && p.pre < DT) ptx::bar_arrive(3, DEC_THREADS + 32);
         } else if (warp >= W_MMA0) {
             // ===================== MMA issuers =====================
             constexpr uint32_t idesc = make_idesc(NT);
@@ -661,6 +675,7 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.pdl = kn.pdl;
     p.S = tcs::pick_split(p);
     p.issuers = kn.tcs_issuers;
+    p.pre = kn.tcs_pre >= 0 ? kn.tcs_pre : 8;   // default: the whole ring up front (staggering measured slower: 6.0 vs 5.5 us)
     p.dbg = kn.tc_debug ? debug_buffer(s, 0) : nullptr;
     p.dbg_cta = kn.tcs_dbg_cta;
     p.dbg_mask = kn.tcs_dbg_mask;

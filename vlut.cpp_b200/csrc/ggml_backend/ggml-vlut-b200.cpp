@@ -46,6 +46,10 @@ struct device_ctx {
     vlut_ctx *io_ctx = nullptr;  // context used by buffer uploads / downloads
     std::mutex io_mutex;
     ggml_backend_buffer_type buft{};
+    // VLUT_B200_GPUS=G > 1: this ONE logical ggml device owns G GPUs.  Weights are row-sharded over
+    // them at load, every vlut MUL_MAT runs on all of them with the gather fused into the GEMM epilogues (vlut_group).
+    int n_gpus = 1;
+    vlut_group *grp = nullptr;
 };
 
 struct buffer_ctx {
@@ -54,6 +58,9 @@ struct buffer_ctx {
     // host copies of one-element f32 tensors written through set_tensor (the `.scale` of a ternary weight): the
     // GEMM epilogue takes the scale by value, so graph_compute needs no device read-back.  Guarded by dev->io_mutex.
     std::unordered_map<const void *, float> scalars;
+    // group mode: the row shards of every vlut weight of this buffer, keyed by the tensor's data pointer (shard 0 lives
+    // there, in the ggml buffer; the other members' shards are the group's own allocations)
+    std::unordered_map<const void *, vlut_group_weight *> shards;
 };
 
 // call with dev->io_mutex held: bytes [lo, hi) of the buffer are being rewritten
@@ -80,7 +87,8 @@ struct backend_ctx {
     std::string name;
     act_cache act;
     // counters behind the "vlut_b200_backend_stats" proc address (tests)
-    int64_t n_mul_mat = 0, n_quantize = 0, n_fused_scale = 0, n_scale_rows = 0, n_batched = 0;
+    int64_t n_mul_mat = 0, n_quantize = 0, n_fused_scale = 0, n_scale_rows = 0, n_batched = 0, n_sharded = 0;
+    bool owns_ctx = true;   // false in group mode: the backend rides the group's root context
 };
 
 bool is_i1_family(enum ggml_type t) { return t == GGML_TYPE_I1_V || t == GGML_TYPE_I1_V_2; }
@@ -100,6 +108,24 @@ int scalar_mul_operand(const ggml_tensor *op) {
     return -1;
 }
 
+// the device's GPU group (group mode only), created on first use
+vlut_group *device_group(device_ctx *d) {
+    if (d->n_gpus <= 1) return nullptr;
+    if (!d->grp) {
+        int devs[8];
+        // VLUT_B200_GROUP_SAME_DEVICE=1: all members on this one GPU (exercises the group path on a single-GPU box)
+        const bool same = getenv("VLUT_B200_GROUP_SAME_DEVICE") != nullptr;
+        for (int i = 0; i < d->n_gpus; i++) devs[i] = same ? d->device : d->device + i;
+        const int rc = vlut_group_create(d->n_gpus, devs, &d->grp);
+        if (rc != VLUT_OK) {
+            GGML_LOG_ERROR("%s: vlut_group_create(%d GPUs) failed: %s (%s)\n", __func__, d->n_gpus, vlut_error_string(rc),
+                           vlut_last_cuda_error());
+            d->grp = nullptr;
+        }
+    }
+    return d->grp;
+}
+
 vlut_ctx *io_ctx(device_ctx *d) {
     if (!d->io_ctx) {
         if (vlut_ctx_create(d->device, nullptr, &d->io_ctx) != VLUT_OK) {
@@ -115,6 +141,7 @@ vlut_ctx *io_ctx(device_ctx *d) {
 // ---------------------------------------------------------------------------------------------------------------
 void buffer_free(ggml_backend_buffer_t buffer) {
     buffer_ctx *b = (buffer_ctx *) buffer->context;
+    for (auto &kv : b->shards) vlut_group_free_weights(b->dev->grp, kv.second);
     vlut_dev_free(b->dev->device, b->base);
     delete b;
 }
@@ -138,6 +165,20 @@ void buffer_set_tensor(ggml_backend_buffer_t buffer, ggml_tensor *tensor, const 
         GGML_ASSERT(offset == 0 && size == ggml_nbytes(tensor) && "vlut weights must be uploaded whole (they are repacked)");
         GGML_ASSERT(ggml_n_dims(tensor) <= 2);
         forget_scalars(b, tensor->data, vlut_repacked_nbytes((int) tensor->type, tensor->ne[0], tensor->ne[1]));
+        if (vlut_group *grp = device_group(b->dev)) {
+            // row-shard on the host, upload + repack every member's shard; member 0's goes into the tensor's own storage
+            auto old = b->shards.find(tensor->data);
+            if (old != b->shards.end()) {
+                vlut_group_sync(grp);
+                vlut_group_free_weights(grp, old->second);
+                b->shards.erase(old);
+            }
+            vlut_group_weight *gw = nullptr;
+            const int rc = vlut_group_upload_weights(grp, (int) tensor->type, tensor->ne[0], tensor->ne[1], data, tensor->data, &gw);
+            if (rc != VLUT_OK) GGML_ABORT("vlut_group_upload_weights failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
+            b->shards[tensor->data] = gw;
+            return;
+        }
         const int rc = vlut_upload_weights(c, (int) tensor->type, tensor->ne[0], tensor->ne[1], data, tensor->data);
         if (rc != VLUT_OK) GGML_ABORT("vlut_upload_weights failed: %s (%s)", vlut_error_string(rc), vlut_last_cuda_error());
         return;
@@ -231,15 +272,20 @@ void backend_free(ggml_backend_t backend) {
     // VLUT_B200_STATS=1: what ran here, for runs under the reference's own tools (llama-bench has no hook to ask)
     if (getenv("VLUT_B200_STATS"))
         fprintf(stderr, "vlut_b200_backend_stats %s: mul_mat=%lld quantise=%lld fused_scale=%lld scale_rows=%lld batched=%lld "
-                "kernel_launches=%lld\n", b->name.c_str(), (long long) b->n_mul_mat, (long long) b->n_quantize,
-                (long long) b->n_fused_scale, (long long) b->n_scale_rows, (long long) b->n_batched,
-                (long long) vlut_ctx_launch_count(b->ctx));
-    vlut_ctx_destroy(b->ctx);
+                "sharded=%lld (x%d GPUs) kernel_launches=%lld\n", b->name.c_str(), (long long) b->n_mul_mat, (long long) b->n_quantize,
+                (long long) b->n_fused_scale, (long long) b->n_scale_rows, (long long) b->n_batched, (long long) b->n_sharded,
+                b->dev->n_gpus, (long long) vlut_ctx_launch_count(b->ctx));
+    if (b->owns_ctx) vlut_ctx_destroy(b->ctx);
+    else vlut_group_sync(b->dev->grp);
     delete b;
     delete backend;
 }
 
-void backend_synchronize(ggml_backend_t backend) { vlut_ctx_sync(((backend_ctx *) backend->context)->ctx); }
+void backend_synchronize(ggml_backend_t backend) {
+    backend_ctx *b = (backend_ctx *) backend->context;
+    if (b->dev->grp) vlut_group_sync(b->dev->grp);
+    else vlut_ctx_sync(b->ctx);
+}
 
 // value of a one-element f32 tensor living in one of our buffers: the host copy kept by set_tensor, else one 4-byte
 // read-back (after which it is cached too)
@@ -341,12 +387,36 @@ ggml_status compute_mul_mat(backend_ctx *b, const ggml_tensor *dst, const ggml_t
     GGML_ASSERT(src1->ne[0] == K && dst->ne[0] == N && dst->ne[1] == T);
     GGML_ASSERT(src1->nb[0] == sizeof(float) && out_t->nb[0] == sizeof(float));
     const bool batched = src1->ne[2] * src1->ne[3] > 1;
+    // group mode: the weight is row-sharded over the device's GPUs
+    vlut_group_weight *gw = nullptr;
+    if (b->dev->grp) {
+        const ggml_tensor *wbase = src0->view_src ? src0->view_src : src0;
+        buffer_ctx *bc = wbase->buffer ? (buffer_ctx *) wbase->buffer->context : nullptr;
+        std::lock_guard<std::mutex> lock(b->dev->io_mutex);
+        auto it = bc ? bc->shards.find(src0->data) : decltype(bc->shards.end()){};
+        if (!bc || it == bc->shards.end()) {
+            GGML_LOG_ERROR("%s: no row shards for weight %s\n", __func__, src0->name);
+            return GGML_STATUS_FAILED;
+        }
+        gw = it->second;
+    }
     for (int64_t i3 = 0; i3 < src1->ne[3]; i3++) {
         for (int64_t i2 = 0; i2 < src1->ne[2]; i2++) {
             const float *x = (const float *) ((const char *) src1->data + i2 * src1->nb[2] + i3 * src1->nb[3]);
             float *out = (float *) ((char *) out_t->data + i2 * out_t->nb[2] + i3 * out_t->nb[3]);
             const int64_t ldx = (int64_t) (src1->nb[1] / sizeof(float)), ldo = (int64_t) (out_t->nb[1] / sizeof(float));
             int rc = VLUT_OK;
+            if (gw) {
+                // every member quantises x (peer read from the root), computes its rows and stores its slice straight into
+                // `out` on the root; on return the root's stream is ordered after all of them
+                float *dst1[1] = {out};
+                rc = vlut_group_mul_mat(b->dev->grp, gw, T, x, ldx, dst1, 1, ldo, w_scale);
+                if (rc != VLUT_OK) return mm_fail(b, dst, rc);
+                b->n_mul_mat++;
+                b->n_quantize++;
+                b->n_sharded++;
+                continue;
+            }
             const bool reuse = !batched && b->act.src1 == src1 && b->act.K == K && b->act.T == T &&
                                b->act.i1_family == is_i1_family(src0->type);
             if (reuse) {
@@ -430,6 +500,9 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
     b->act = act_cache{};  // inputs may have been rewritten since the last graph
     for (int i = 0; i < cgraph->n_nodes; i++) {
         ggml_tensor *node = cgraph->nodes[i];
+        // empty tensors (a ubatch without output tokens leaves the last layer's FFN with zero rows) are no-ops, as in
+        // every other backend
+        if (ggml_is_empty(node)) continue;
         switch (node->op) {
             case GGML_OP_MUL_MAT: {
                 mm_item items[4];
@@ -438,10 +511,10 @@ ggml_status backend_graph_compute(ggml_backend_t backend, ggml_cgraph *cgraph) {
                 // look ahead: the following MUL_MATs that read the same (2-D) activation tensor with the same K-group
                 // family join the group, as long as no member's output overlaps the shared input or another output
                 const ggml_tensor *src1 = node->src[1];
-                const bool groupable = !no_batch && src1->ne[2] * src1->ne[3] == 1;
+                const bool groupable = !no_batch && !b->dev->grp && src1->ne[2] * src1->ne[3] == 1;
                 while (groupable && n < 4 && next < cgraph->n_nodes) {
                     ggml_tensor *cand = cgraph->nodes[next];
-                    if (cand->op != GGML_OP_MUL_MAT || cand->src[1] != src1 || !cand->src[0] ||
+                    if (cand->op != GGML_OP_MUL_MAT || cand->src[1] != src1 || !cand->src[0] || ggml_is_empty(cand) ||
                         !ggml_backend_dev_supports_op(backend->device, cand) ||
                         is_i1_family(cand->src[0]->type) != is_i1_family(node->src[0]->type))
                         break;
@@ -537,6 +610,21 @@ ggml_backend_t dev_init_backend(ggml_backend_dev_t dev, const char * /*params*/)
     backend_ctx *b = new backend_ctx;
     b->dev = d;
     b->name = d->name;
+    if (vlut_group *grp = device_group(d)) {
+        // group mode: the backend's stream is the group's root stream (member streams are ordered against it by events)
+        b->ctx = vlut_group_ctx(grp, 0);
+        b->owns_ctx = false;
+        return new ggml_backend{
+            /* .guid    = */ backend_guid(),
+            /* .iface   = */ backend_iface,
+            /* .device  = */ dev,
+            /* .context = */ b,
+        };
+    }
+    if (d->n_gpus > 1) {
+        delete b;
+        return nullptr;
+    }
     const int rc = vlut_ctx_create(d->device, nullptr, &b->ctx);
     if (rc != VLUT_OK) {
         GGML_LOG_ERROR("%s: vlut_ctx_create(%d) failed: %s (%s)\n", __func__, d->device, vlut_error_string(rc), vlut_last_cuda_error());
@@ -639,10 +727,12 @@ void backend_stats(ggml_backend_t backend, int64_t *out) {
     out[2] = b->n_fused_scale;
     out[3] = b->n_scale_rows;
 }
-// "vlut_b200_backend_stats2": adds out[4] = MUL_MATs that ran inside a batched group
+// "vlut_b200_backend_stats2": adds out[4] = MUL_MATs that ran inside a batched group, out[5] = MUL_MATs that ran row-sharded
+// over the device's GPU group
 void backend_stats2(ggml_backend_t backend, int64_t *out) {
     backend_stats(backend, out);
     out[4] = ((backend_ctx *) backend->context)->n_batched;
+    out[5] = ((backend_ctx *) backend->context)->n_sharded;
 }
 
 void *reg_get_proc_address(ggml_backend_reg_t, const char *name) {
@@ -672,6 +762,18 @@ ggml_backend_reg_t vlut_b200_reg() {
             const int l = atoi(lim);
             if (l >= 0 && l < n) n = l;
         }
+        // env VLUT_B200_GPUS=G (2, 4, 8): ONE logical ggml device that owns G GPUs -- weights row-sharded at load, every
+        // vlut MUL_MAT runs on all G with the gather fused into the GEMM epilogues (SURVEY.md section 8e "Exposure")
+        int gpus = 1;
+        if (const char *g = getenv("VLUT_B200_GPUS")) {
+            gpus = atoi(g);
+            const bool same = getenv("VLUT_B200_GROUP_SAME_DEVICE") != nullptr;
+            if (gpus < 1 || gpus > 8 || (!same && gpus > n)) {
+                GGML_LOG_ERROR("VLUT_B200_GPUS=%s: %d usable GPU(s); falling back to one GPU per device\n", g, n);
+                gpus = 1;
+            }
+            if (gpus > 1 && n > 1) n = 1;
+        }
         reg = ggml_backend_reg{
             /* .api_version = */ GGML_BACKEND_API_VERSION,
             /* .iface       = */ reg_iface,
@@ -681,10 +783,12 @@ ggml_backend_reg_t vlut_b200_reg() {
         for (int i = 0; i < n; i++) {
             device_ctx *d = new device_ctx;
             d->device = i;
+            d->n_gpus = gpus;
             d->name = "VLUT_B200_" + std::to_string(i);
             char gpu[128] = "";
             vlut_device_info(i, gpu, sizeof(gpu), nullptr, nullptr, nullptr);
-            d->description = std::string(gpu) + " (Vec-LUT ternary MUL_MAT, sm_100a)";
+            d->description = std::string(gpu) + " (Vec-LUT ternary MUL_MAT, sm_100a" +
+                             (gpus > 1 ? ", row-sharded over " + std::to_string(gpus) + " GPUs)" : std::string(")"));
             d->buft = ggml_backend_buffer_type{
                 /* .iface   = */ buft_iface,
                 /* .device  = */ nullptr,  // fixed up below

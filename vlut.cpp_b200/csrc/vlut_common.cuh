@@ -58,14 +58,27 @@ __host__ __device__ inline int t2_shift(int64_t k) {
 
 // token tile (UMMA N) used for a token count
 __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : 128; }
-// The CTA-pair kernel also has a 256-token tile (one decoded A stage feeds two 128-token halves).  It pays when the token
-// count fills whole 256-tiles well: T > 256 with at most 1/8 of the last tile padded (crossover measured).
-__host__ __device__ inline int token_tile_pair(int64_t T, int forced) {
+// The CTA-pair kernel also has a 256-token tile (one decoded A stage feeds two 128-token halves: weights unpacked T/256
+// instead of T/128 times, 2048 clk of MMA per hand-off, but a single accumulator, so every tile pays an un-overlapped drain).
+// Which tile is faster depends on K (the drain bubble amortises over K), on how the tiles quantise into rounds on the 74 CTA
+// pairs, and on the type (I1: 640-k groups).  Cost model in SM clocks, fitted to measurements at four shapes x six token
+// counts (profiles/r2_tcp_tiles.txt: it picks the faster tile in 23 of 24 cases, the miss costs 6 %):
+//     tile time = G * unit + tile_overhead;  whole / hybrid schedule as in launch_out (gemm_tc5.cu);  + fixed
+inline double pair_tile_cost(int64_t K, int64_t N, int64_t T, int NT, int gsize, int sm_count) {
+    const double unit = (NT > 128 ? 2000.0 : 1200.0) * (gsize == 640 ? 1.25 : 1.0);
+    const double tile = NT > 128 ? 10000.0 : 3500.0, fixed = NT > 128 ? 5000.0 : 9000.0;
+    const int64_t G = ceil_div(K, gsize), RP = (ceil_div(N, TILE_ROWS) + 1) / 2, TT = ceil_div(T, NT);
+    const int64_t ptiles = RP * TT, npairs = sm_count / 2 > 0 ? sm_count / 2 : 1;
+    const int64_t rounds = ceil_div(ptiles, npairs), full = ptiles / npairs, su = (ptiles - full * npairs) * G;
+    const double whole = (double) rounds * (G * unit + tile);
+    const double hybrid = (double) full * (G * unit + tile) + (su ? (2.0 * ceil_div(su, npairs) + 3.0) * unit : 0.0);
+    return (full >= 1 && hybrid < whole ? hybrid : whole) + fixed;
+}
+inline int token_tile_pair(int64_t K, int64_t N, int64_t T, int gsize, int sm_count, int forced) {
     if (forced == 64 || forced == 128 || forced == 256) return (forced == 64 && T > 64) ? 128 : forced;
     if (T <= 64) return 64;
-    if (T <= 256) return 128;
-    const int64_t pad256 = round_up(T, 256) - T, pad128 = round_up(T, 128) - T;
-    return (pad256 - pad128) * 8 <= round_up(T, 256) ? 256 : 128;
+    if (T <= 128) return 128;
+    return pair_tile_cost(K, N, T, 256, gsize, sm_count) < pair_tile_cost(K, N, T, 128, gsize, sm_count) ? 256 : 128;
 }
 
 // ---- activation workspace -------------------------------------------------------------------------------
@@ -180,7 +193,8 @@ struct Knobs {
     int tc_grid, tc_whole, tc_split_last;   // VLUT_TC_GRID, VLUT_TC_WHOLE, VLUT_TC_SPLIT_LAST (tests: force the split paths)
     int tc_abl, tc_debug, tc_debug_skip;    // VLUT_TC_ABL, VLUT_TC_DEBUG, VLUT_TC_DEBUG_SKIP
     int tc_nt;                     // VLUT_TC_NT          force the TCP token tile (128 / 256)
-    int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask;   // VLUT_TCS_*
+    int tc_astages;                // VLUT_TC_ASTAGES     2: two A stages of 512 k, 4: four of 256 k; default per token tile
+    int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask, tcs_pre;   // VLUT_TCS_*
     int quant_2pass, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
     int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
     int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
