@@ -70,9 +70,19 @@ def test_repack_round_trip(ctx, orc, type_, K, N):
     assert torch.equal(W.t2, W2.t2)
 
 
+# VLUT_QUANT_KERNEL / VLUT_QUANT_THREADS: register-resident rows with 128 / 256 / 512 threads per token, or the two-pass kernel
+QUANT_KERNELS = {"register-kernel": (0, 0), "register-128": (0, 128), "register-256": (0, 256), "register-512": (0, 512),
+                 "two-pass-kernel": (2, 0)}
+
+
+@pytest.mark.parametrize("kernel", list(QUANT_KERNELS.values()), ids=list(QUANT_KERNELS))
 @pytest.mark.parametrize("kind", ["normal", "uniform", "outlier", "negative", "zeros", "ones"])
-@pytest.mark.parametrize("T,K", [(1, 512), (7, 4096), (33, 3200), (70, 1300), (5, 8640), (18, 14336), (3, 16400)])
-def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
+@pytest.mark.parametrize("T,K", [(1, 512), (7, 4096), (33, 3200), (70, 1300), (5, 8640), (18, 14336), (3, 16400), (600, 2048),
+                                 (2, 32768)])
+def test_quantize_act_bit_exact(ctx, orc, knobs, kernel, kind, T, K):
+    if kernel != (0, 0) and kind not in ("normal", "outlier", "negative"):
+        pytest.skip("three kinds are enough for the non-default launches")
+    knobs(VLUT_QUANT_KERNEL=kernel[0], VLUT_QUANT_THREADS=kernel[1])
     x = O.make_acts(T, K, seed=T + K, kind=kind)
     q_ref, s_ref = orc.quantize(x)
     ctx.quantize_act(O.I2_V_4 if K % 16 == 0 else O.I1_V, torch.from_numpy(x).cuda())
@@ -81,11 +91,11 @@ def test_quantize_act_bit_exact(ctx, orc, kind, T, K):
     assert np.array_equal(bits(s), bits(s_ref))
 
 
-@pytest.mark.parametrize("two_pass", [0, 1], ids=["register-kernel", "two-pass-kernel"])
+@pytest.mark.parametrize("two_pass", list(QUANT_KERNELS.values()), ids=list(QUANT_KERNELS))
 def test_quantize_ties_and_saturation(ctx, orc, knobs, two_pass):
     """round() is half AWAY from zero and the clamp is asymmetric: exact .5 products (row max 127 -> scale 1), values far
     outside the int8 range, and a row whose signed max is negative (everything saturates to -128)."""
-    knobs(VLUT_QUANT_2PASS=two_pass)
+    knobs(VLUT_QUANT_KERNEL=two_pass[0], VLUT_QUANT_THREADS=two_pass[1])
     K = 1024
     x = np.zeros((3, K), dtype=np.float32)
     ties = np.array([0.5, -0.5, 1.5, -1.5, 2.5, -2.5, 126.5, -126.5, -127.5, -128.5, -129.0, -1000.0, 127.0, 0.49999997,

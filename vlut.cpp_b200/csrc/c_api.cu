@@ -58,7 +58,9 @@ void knobs_reload() {
     k.tcs_dbg_cta = env_int("VLUT_TCS_DBG_CTA", 0);
     k.tcs_dbg_mask = env_int("VLUT_TCS_DBG_MASK", 15);
     k.tcs_pre = env_int("VLUT_TCS_PRE", -1);
-    k.quant_2pass = env_int("VLUT_QUANT_2PASS", 0);
+    // activation quantise kernel: 0 register-resident rows (default), 2 two-pass (also the unaligned / K > 16384 fallback)
+    k.quant_kernel = env_int("VLUT_QUANT_KERNEL", env_int("VLUT_QUANT_2PASS", 0) ? 2 : 0);
+    k.quant_threads = env_int("VLUT_QUANT_THREADS", 0);   // 0 = by shape; 128 / 256 / 512
     k.quant_pdl = env_int("VLUT_QUANT_PDL", -1);
     k.quant_early = env_int("VLUT_QUANT_EARLY", -1);
     k.quant_tpc = env_int("VLUT_QUANT_TPC", 0);

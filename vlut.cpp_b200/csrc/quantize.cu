@@ -11,6 +11,7 @@
 // 128-bit loads of x, 32-bit stores of q in two layouts (row-major, and pre-swizzled K-major UMMA operand tiles
 // that a TMA bulk copy drops into shared memory ready for tcgen05.mma), plus per (token, K-group): the sum of q
 // that undoes the +1 offset of the u8 weight codes, and whether sum|q| rules out any int16 wrap.
+#include "ptx.cuh"
 #include "quant_math.cuh"
 #include "vlut_common.cuh"
 
@@ -119,114 +120,90 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
     }
 }
 
-// ---- register-resident single-pass kernel (K <= 16384, 16-byte aligned rows) ---------------------------------------
-// One CTA per token; thread i owns the 16-element chunks i, i + 256, ... of the row: 4 x LDG.128 per chunk, all issued
-// before the first use, the row stays in registers between the max pass and the quantise pass (the two-pass kernel above
-// re-reads it through L1/L2 and costs ~6 us per call whatever T).  Output per chunk: one 16-byte store into q_rm and one
-// into its pre-swizzled position of q_sw (16 bytes = the swizzle granule).  Group sums with dp4a + redux.sync, prefix sums
-// by a warp scan.  Launched with the programmatic-serialisation attribute: the CTA is resident and past its prologue when
-// the predecessor (the previous GEMM, which reads the workspace this kernel rewrites) drains; griddepcontrol.wait orders
-// every global access after it.
-template <int CH>
-__global__ void __launch_bounds__(QT) quantize_reg_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
-                                                          ActView a, int early, int want_rm) {
+// ---- register-resident single-pass kernel (K <= 16384, 16-byte aligned rows): the default --------------------------------
+// One CTA of NTH threads per token; thread i owns the 16-byte words i, i + NTH, ... of the row (a warp instruction reads 512
+// contiguous bytes), all loads issued before the first use, and the row stays in registers between the max pass and the
+// quantise pass.  Output per word: one packed int8x4 into its pre-swizzled position of q_sw -- the 32 lanes of a warp fill
+// exactly one 128-byte row of one swizzled tile, and (128 divides the group sizes) belong to one K-group: two redux per 128
+// elements for the group sums, prefix sums by a warp scan.  Launched with the programmatic-serialisation attribute: the CTA
+// is resident and past its prologue when the predecessor (the previous GEMM, which reads the workspace this kernel rewrites)
+// drains; griddepcontrol.wait orders every global access after it.
+//
+// History (scripts/time_quant.py, profiles/r2_time_quant.txt): the first version of this kernel spent ~25 instructions per
+// element (per-element round / clamp / pack) with a 64-byte stride per lane on the loads and took 6.6 us at K = 4096,
+// T = 512, 20.7 us at K = 14336, T = 512, and 8.6 us for ONE token of 14336 -- it was issue-bound, not HBM-bound.  quant4
+// (quant_math.cuh) is ~9 instructions per element.  A persistent variant that streamed rows through shared memory with bulk
+// copies (512 threads, 3 CTA-wide barriers per token) measured SLOWER (10.1 / 23.5 us): per token the max -> scale ->
+// quantise -> scan chain is ~2000 clk of latency and two CTAs per SM do not hide it; many small CTAs do.
+template <int NTH, int CH>
+__global__ void __launch_bounds__(NTH) quantize_reg_kernel(const float *__restrict__ x, int64_t ldx, int64_t K, int64_t T,
+                                                           ActView a, int early, int want_rm) {
     const int t = blockIdx.x;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
-    __shared__ float s_red[QT / 32];
+    __shared__ float s_red[NTH / 32];
     __shared__ int s_gsum[64];
     __shared__ int s_gabs[64];
     if (tid < 64) { s_gsum[tid] = 0; s_gabs[tid] = 0; }
-    const int64_t Kpad = a.Kpad;
     const bool live = t < T;
-    const float *xr = x + (int64_t) t * ldx;
+    const float4 *xr = reinterpret_cast<const float4 *>(x + (int64_t) t * ldx);
     // `early` (the host knows the preceding kernel on the stream does not write x): the row is loaded, reduced and its
     // scale computed while the previous GEMM is still running; only the stores below wait for it (they overwrite the
     // workspace that GEMM reads)
     if (!early) asm volatile("griddepcontrol.wait;" ::: "memory");
 
-    float4 v[CH][4];
+    const int KW = (int) (K / 4), KPW = (int) (a.Kpad / 4);   // 16-byte words of the row / of the padded row
+    float4 v[CH];
     float mx = -INFINITY;
 #pragma unroll
     for (int j = 0; j < CH; j++) {
-        const int64_t k = (int64_t) (j * QT + tid) * 16;
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            if (live && k + 4 * i < K) v[j][i] = __ldg(reinterpret_cast<const float4 *>(xr + k + 4 * i));
-            else v[j][i] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-        }
+        const int w = j * NTH + tid;
+        if (live && w < KW) v[j] = __ldg(xr + w);
+        else v[j] = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
     }
 #pragma unroll
-    for (int j = 0; j < CH; j++)
-#pragma unroll
-        for (int i = 0; i < 4; i++) mx = fmaxf(mx, fmaxf(fmaxf(v[j][i].x, v[j][i].y), fmaxf(v[j][i].z, v[j][i].w)));
+    for (int j = 0; j < CH; j++) mx = fmaxf(mx, fmaxf(fmaxf(v[j].x, v[j].y), fmaxf(v[j].z, v[j].w)));
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
     if (lane == 0) s_red[warp] = mx;
     __syncthreads();
     float m = s_red[0];
 #pragma unroll
-    for (int i = 1; i < QT / 32; i++) m = fmaxf(m, s_red[i]);
-    double dm = (double) m;
-    if (!(dm > 1e-5)) dm = 1e-5;  // MAX(eps, .) with eps = 1e-5
-    const double sd = dm / 127;
-    const double is = 1e0 / (sd > 1e-5 ? sd : 1e-5);
+    for (int i = 1; i < NTH / 32; i++) m = fmaxf(m, s_red[i]);
+    double is;
+    float scale;
+    quant_scale(m, is, scale);
     const float isf = (float) is;
     if (early) asm volatile("griddepcontrol.wait;" ::: "memory");
-    if (tid == 0) a.scales[t] = live ? (float) sd : 0.0f;
+    if (tid == 0) a.scales[t] = live ? scale : 0.0f;
 
-    const int gsize = a.gsize;
+    const int KB = (int) (a.Kpad / BLOCK_K);
+    // word `lane` of a 128-byte q_sw row -> its position: regrouping by bit-pair position (perm: word 4c + i -> 8i + c),
+    // then the 128B swizzle (16-byte chunk c -> c ^ (t % 8))
+    const int wp = a.perm ? ((lane & 3) * 8 + (lane >> 2)) : lane;
+    const int wpos = (((wp >> 2) ^ (t & 7)) << 2) | (wp & 3);
+    // Everything per word below is 32-bit and incremental (the first version of this loop spent 24 IMAD + 12 ISETP per word
+    // on 64-bit addresses and a runtime division by the group size: ncu source page, profiles/r2_ncu_quant.txt).
+    // Word w = j * NTH + tid sits in sub-block kb = j * (NTH / 32) + warp; sub-blocks are sw_tile * 128 bytes apart in q_sw.
+    const uint32_t kb_stride = (uint32_t) a.sw_tile * 128u;
+    uint8_t *dst = reinterpret_cast<uint8_t *>(a.q_sw) +
+                   ((int64_t) (t / a.sw_tile) * KB * a.sw_tile + (t % a.sw_tile)) * 128 + (int64_t) warp * kb_stride + wpos * 4;
+    uint8_t *dst_rm = reinterpret_cast<uint8_t *>(a.q_rm) + (int64_t) t * a.Kpad + tid * 4;
+    const bool g4 = (a.gsize == 512);   // K-group = 4 sub-blocks (I2_*) or 5 (I1_*)
 #pragma unroll
     for (int j = 0; j < CH; j++) {
-        const int64_t k = (int64_t) (j * QT + tid) * 16;
-        const int kw = (j * QT + warp * 32) * 16;   // first k of this warp's 512-k span
-        if (kw >= Kpad) break;                      // warp-uniform: nothing left for this warp
-        uint32_t pk[4];
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            if (live && k + 4 * i < K) {
-                const int q0 = quant1(v[j][i].x, is, isf), q1 = quant1(v[j][i].y, is, isf), q2 = quant1(v[j][i].z, is, isf),
-                          q3 = quant1(v[j][i].w, is, isf);
-                pk[i] = (uint32_t) (q0 & 0xff) | ((uint32_t) (q1 & 0xff) << 8) | ((uint32_t) (q2 & 0xff) << 16) |
-                        ((uint32_t) (q3 & 0xff) << 24);
-            } else {
-                pk[i] = 0;
-            }
-        }
-        int sum = 0;
-        unsigned asum = 0;
-#pragma unroll
-        for (int i = 0; i < 4; i++) {
-            sum = __dp4a((int) pk[i], 0x01010101, sum);
-            asum = __dp4a(__vabs4(pk[i]), 0x01010101u, asum);
-        }
-        if (k < Kpad) {
-            if (want_rm) *reinterpret_cast<uint4 *>(a.q_rm + (int64_t) t * Kpad + k) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            // K-major UMMA tile, 128B swizzle: 16-byte chunk c of row t goes to chunk position c ^ (t % 8)
-            const int64_t kb = k / BLOCK_K;
-            const int c = (int) (k % BLOCK_K) / 16;
-            int8_t *row = a.q_sw + (((int64_t) (t / a.sw_tile) * (Kpad / BLOCK_K) + kb) * a.sw_tile + (t % a.sw_tile)) * 128;
-            if (!a.perm) {
-                *reinterpret_cast<uint4 *>(row + ((c ^ (t & 7)) << 4)) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-            } else {
-                // regrouped by bit-pair position: word pk[i] (k = 16c + 4i .. + 3) goes to byte i*32 + c*4 of the row
-#pragma unroll
-                for (int i = 0; i < 4; i++) {
-                    const int pos = i * 32 + c * 4;
-                    *reinterpret_cast<uint32_t *>(row + ((((pos >> 4) ^ (t & 7)) << 4) | (pos & 15))) = pk[i];
-                }
-            }
-        }
-        // the warp covers 512 consecutive k: at most two K-groups (512 or 640 k per group)
-        const int gA = kw / gsize;
-        const bool inA = (int) (k / gsize) == gA;
-        const int sA = __reduce_add_sync(0xffffffffu, inA ? sum : 0);
-        const int aA = __reduce_add_sync(0xffffffffu, inA ? (int) asum : 0);
-        const int sB = __reduce_add_sync(0xffffffffu, inA ? 0 : sum);
-        const int aB = __reduce_add_sync(0xffffffffu, inA ? 0 : (int) asum);
+        const int w = j * NTH + tid;
+        const int kb = j * (NTH / 32) + warp;
+        if (kb >= KB) break;   // warp-uniform: nothing left for this warp
+        const uint32_t pk = (live && w < KW) ? quant4(v[j], is, isf) : 0u;
+        *reinterpret_cast<uint32_t *>(dst + (uint32_t) (j * (NTH / 32)) * kb_stride) = pk;
+        if (want_rm) *reinterpret_cast<uint32_t *>(dst_rm + j * NTH * 4) = pk;
+        const int sum = __reduce_add_sync(0xffffffffu, sum4(pk));
+        const int asum = __reduce_add_sync(0xffffffffu, abssum4(pk));
         if (lane == 0) {
-            if (aA) { atomicAdd(&s_gsum[gA], sA); atomicAdd(&s_gabs[gA], aA); }
-            if (aB) { atomicAdd(&s_gsum[gA + 1], sB); atomicAdd(&s_gabs[gA + 1], aB); }
+            const int g = g4 ? (kb >> 2) : ((kb * 205) >> 10);   // kb / 5, exact for kb < 1029
+            atomicAdd(&s_gsum[g], sum);
+            atomicAdd(&s_gabs[g], asum);
         }
     }
     __syncthreads();
@@ -320,12 +297,12 @@ cudaError_t launch_unswizzle(const ActView &a, cudaStream_t s) {
     return cudaGetLastError();
 }
 
-template <int CH>
+template <int NTH, int CH>
 static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
                               int early, int want_rm) {
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3((unsigned) a.Tpad);
-    cfg.blockDim = dim3(QT);
+    cfg.blockDim = dim3(NTH);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
@@ -333,17 +310,36 @@ static cudaError_t launch_reg(const float *x, int64_t ldx, int64_t K, int64_t T,
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
-    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<CH>, x, ldx, K, T, a, early, want_rm);
+    return cudaLaunchKernelEx(&cfg, quantize_reg_kernel<NTH, CH>, x, ldx, K, T, a, early, want_rm);
+}
+
+template <int NTH>
+static cudaError_t launch_reg_n(int words, const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
+                                bool pdl, int early, int want_rm) {
+    const int ch = (words + NTH - 1) / NTH;   // 16-byte words per thread
+    if (ch <= 1) return launch_reg<NTH, 1>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 2) return launch_reg<NTH, 2>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 4) return launch_reg<NTH, 4>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 8) return launch_reg<NTH, 8>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 16) return launch_reg<NTH, 16>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    return cudaErrorInvalidValue;
 }
 
 cudaError_t launch_quantize(const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s, bool pdl,
                             bool early, bool want_rm) {
     if (a.G > 64) return cudaErrorInvalidValue;
     const bool aligned = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (ldx % 4 == 0);
-    if (!knobs().quant_2pass && aligned && a.Kpad <= 16384) {
-        if (a.Kpad <= 4096) return launch_reg<1>(x, ldx, K, T, a, s, pdl, early, want_rm);
-        if (a.Kpad <= 8192) return launch_reg<2>(x, ldx, K, T, a, s, pdl, early, want_rm);
-        return launch_reg<4>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    const Knobs &kn = knobs();
+    if (kn.quant_kernel != 2 && aligned && a.Kpad <= 16384) {
+        const int words = (int) (a.Kpad / 4);
+        // threads per token: 256; 512 for long rows of few tokens (the per-thread chain is what a small launch waits for),
+        // 128 for short rows (at least a few words per thread)
+        int nth = kn.quant_threads;
+        // (<= 8 words per thread: 16 need 106 registers and leave 16 warps per SM, measured 18.3 vs 14.9 us at K = 14336, T = 512)
+        if (nth == 0) nth = (words <= 512) ? 128 : ((words > 2048 || (a.Tpad <= 256 && words >= 2048)) ? 512 : 256);
+        if (nth == 512) return launch_reg_n<512>(words, x, ldx, K, T, a, s, pdl, early, want_rm);
+        if (nth == 128 && words <= 2048) return launch_reg_n<128>(words, x, ldx, K, T, a, s, pdl, early, want_rm);
+        return launch_reg_n<256>(words, x, ldx, K, T, a, s, pdl, early, want_rm);
     }
     quantize_kernel<<<(unsigned) a.Tpad, QT, 0, s>>>(x, ldx, K, T, a, want_rm);
     return cudaGetLastError();
