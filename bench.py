@@ -25,7 +25,7 @@ shape), I2_V_4 weights, synthetic random ternary weights and N(0,1) activations.
     set exceeds the 126 MB L2 (`config.l2`).
   * N > 1 (torchrun): output-row tensor parallelism, weak scaling: every rank holds its own [K, 14336] row shard
     of a [K, 14336*N] matrix, quantises the (replicated) activations, computes its slice and the GEMM epilogue stores it
-    into EVERY rank's [T][14336*N] buffer (16-byte NVSwitch multicast stores), followed by the library's own barrier
+    into EVERY rank's [T][14336*N] buffer (tiles staged in shared memory, bulk async copies to every peer), followed by the library's own barrier
     kernel.  The gathered buffer is checked bit-for-bit against an NCCL all-gather of the ranks' local results
     (`checks.gather_bit_exact`; the run fails if false).  `multi_gpu` reports GEMM-only, GEMM+gather, ingress GB/s and
     the fraction of the NVLink bound, and config 5 (TriLM shapes) strong-scaled over the ranks.
@@ -371,10 +371,13 @@ def main() -> None:
                 hdls.append(symm_mem.rendezvous(buf, dist.group.WORLD))
                 outs.append(buf)
             flags = shard.RowShardedWeight.flag_ptrs(hdls[0])
-            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST") != "0"
-            gather_mode = "fused-multimem-v4" if use_mc else "fused-p2p-v4"
+            # default: peer pointers, tiles staged in shared memory and scattered with bulk async copies (measured faster
+            # than multimem.st / direct peer stores from the epilogue, profiles/r2_multi_gpu.txt); VLUT_BENCH_MULTICAST=1
+            # selects the NVSwitch multicast stores, VLUT_SCATTER_BULK=0 the direct 16-byte peer stores
+            use_mc = bool(int(getattr(hdls[0], "multicast_ptr", 0) or 0)) and os.environ.get("VLUT_BENCH_MULTICAST", "0") == "1"
+            gather_mode = "fused-multimem-v4" if use_mc else ("fused-p2p-v4" if os.environ.get("VLUT_SCATTER_BULK") == "0" else "fused-p2p-bulk")
             if os.environ.get("VLUT_SCATTER_VEC") == "0":
-                gather_mode = gather_mode.replace("-v4", "-scalar")
+                gather_mode = gather_mode.replace("-v4", "-scalar").replace("-bulk", "-scalar")
         except Exception as e:  # noqa: BLE001
             if rank == 0:
                 print(f"[bench] symmetric memory unavailable ({e}); using the NCCL all-gather", file=sys.stderr)

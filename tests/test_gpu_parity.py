@@ -577,3 +577,35 @@ def test_fused_scatter_vector_stores(ctx, orc, knobs, vec, T, N, bounds):
     for b in bufs:
         assert np.array_equal(bits(b[:, :N].cpu().numpy()), bits(ref))
         assert (b[:, N:] == 0).all()
+
+
+@pytest.mark.parametrize("bulk", [1, 0], ids=["bulk-copies", "direct-stores"])
+@pytest.mark.parametrize("T,N,bounds,K,kind,extra", [
+    (300, 1536, [0, 768, 1536], 2048, "normal", {}),
+    (520, 1000, [0, 512, 1000], 4096, "normal", {}),                   # ragged last strip (488 rows: 416-byte copies), ragged T
+    (300, 1536, [0, 768, 1536], 2048, "ones", {}),                     # int16 wrap: exact path (direct stores)
+    (300, 1536, [0, 640, 1536], 4096, "normal", {"VLUT_TC_GRID": 6}),  # split tiles: the last arriver's fix-up scatters
+    (520, 1536, [0, 512, 1024, 1536], 2048, "outlier", {"VLUT_TC_NT": 256}),   # 256-token tile, three destinations
+], ids=["plain", "ragged", "exact-path", "split-tiles", "nt256-3way"])
+def test_fused_scatter_bulk_copies(ctx, orc, knobs, bulk, T, N, bounds, K, kind, extra):
+    """CTA-pair kernel, peer-pointer scatter through shared-memory staging + cp.async.bulk (epilogue.cuh, Scatter) against the
+    direct-store scatter and the oracle: every 'rank' buffer ends up with the whole [T][N] result, bit for bit."""
+    a = api()
+    knobs(VLUT_SCATTER_BULK=bulk, **extra)
+    type_ = O.I2_V_4
+    w = O.make_ternary(N, K, seed=N + 1) if kind != "ones" else np.ones((N, K), dtype=np.float32)
+    x = O.make_acts(T, K, seed=T, kind=kind)
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    xd = torch.from_numpy(x).cuda()
+    G = len(bounds) - 1
+    bufs = [torch.full((T + 1, N + 4), -7.0, device="cuda") for _ in range(G)]   # guard row and guard columns
+    for g in range(G):
+        r0, rows = bounds[g], bounds[g + 1] - bounds[g]
+        Wg = ctx.upload(type_, K, rows, a.shard_rows(type_, K, N, r0, rows, packed))
+        for rep in range(2):   # twice: the staging buffers and the copy groups are reused across launches
+            ctx.mul_mat_scatter(Wg, xd, peers=[b.data_ptr() for b in bufs], multicast_ptr=0, ldo=N + 4, col0=r0)
+    torch.cuda.synchronize()
+    for b in bufs:
+        assert np.array_equal(bits(b[:T, :N].cpu().numpy()), bits(ref))
+        assert (b[T:] == -7.0).all() and (b[:, N:] == -7.0).all()

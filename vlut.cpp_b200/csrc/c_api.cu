@@ -65,6 +65,7 @@ void knobs_reload() {
     k.quant_early = env_int("VLUT_QUANT_EARLY", -1);
     k.quant_tpc = env_int("VLUT_QUANT_TPC", 0);
     k.scatter_vec = env_int("VLUT_SCATTER_VEC", 1);
+    k.scatter_bulk = env_int("VLUT_SCATTER_BULK", 1);
     k.gemv_split = env_int("VLUT_GEMV_SPLIT", 0);
     k.gemv_max_t = env_int("VLUT_GEMV_MAX_T", -1);
     g_knobs = k;
@@ -552,6 +553,7 @@ static int gemm_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, i
         if (reinterpret_cast<uintptr_t>(outs[i]) & 15) g.vec_ok = 0;
     }
     if (knobs().scatter_vec == 0) g.vec_ok = 0;
+    g.bulk_ok = (g.vec_ok && !multicast && calls[0].N % 4 == 0 && knobs().scatter_bulk) ? 1 : 0;
     g.K = K;
     g.T = T;
     g.sm_count = c->sm_count;

@@ -45,6 +45,29 @@ __device__ __forceinline__ void transpose4(float (&a)[4], int lane) {
     }
 }
 
+// Staged scatter (OUT == 3, the CTA-pair kernel's fused all-gather over peer pointers).  Direct epilogue stores to peer
+// memory fill NVLink (688 GB/s with this very access pattern, scripts/ubench/peer_store.cu) -- but inside the GEMM they
+// took 91 us for a 33 us GEMM + 43 us of link time: the stalled remote stores sit in the SM's load/store path, in front of
+// the decode warps' shared-memory loads and the next accumulator's drain.  So the four epilogue warps park 16 tokens x 128
+// rows of fp32 in a shared-memory buffer (two buffers), and one bulk async copy per (token, destination) -- 512 contiguous
+// bytes, issued by up to 128 different threads -- carries them out through the TMA engine: the SM's store path stays
+// empty and the copies drain under the following MMAs.
+// Protocol per 16-token chunk k (buffer k % 2), all 128 epilogue threads:
+//   issuers wait until their bulk copies of chunk k - 1 have READ shared memory (so buffer (k + 1) % 2 is free for the
+//   next chunk) -> everybody writes buffer k % 2 (free since the barrier of chunk k - 1) -> fence.proxy.async -> barrier
+//   -> issuers launch the copies of chunk k and commit.  One named barrier per chunk.
+struct Scatter {
+    uint32_t stage;      // shared-memory address of the two 16 x 128 x 4 B buffers
+    uint32_t k;          // chunks staged so far
+    int et;              // epilogue thread 0..127 == row of the strip
+    int row_bytes;       // bytes of the strip's rows that exist (ragged last strip), multiple of 16
+    __device__ __forceinline__ void init(uint32_t stage_smem, int et_) { stage = stage_smem; k = 0; et = et_; row_bytes = 512; }
+    __device__ __forceinline__ void finish() const {   // every copy of this thread has been written out
+        asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+    }
+};
+constexpr int SCATTER_BYTES = 2 * 16 * 128 * 4;
+
 // 16 final int32 sums of one weight row (tokens t .. t+15) -> fp32 outputs: out[(t+i) * ldo + n] = (float) x * s[t+i]
 // (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all); nvalid = this
 // lane's row exists.  WARP-COLLECTIVE for the scatter flavours (OUT != 0): every lane of the warp must call it.
@@ -57,7 +80,7 @@ __device__ __forceinline__ void transpose4(float (&a)[4], int lane) {
 template <int OUT>
 __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_smem, bool ws, float w_scale, float *out0,
                                         float *const *outs, int n_out, int64_t idx0, int64_t ldo, int nv, bool nvalid,
-                                        bool vec_ok = false) {
+                                        bool vec_ok = false, Scatter *sc = nullptr) {
     float f[16];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -70,6 +93,29 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
     if (ws) {
 #pragma unroll
         for (int i = 0; i < 16; i++) f[i] *= w_scale;
+    }
+    if (OUT == 3 && sc != nullptr) {
+        // all 128 epilogue threads, same chunk: idx0 = (token of column 0) * ldo + (first row of the strip + et)
+        const bool issuer = sc->et < 16 * n_out;
+        const uint32_t buf = sc->stage + (sc->k & 1u) * (16 * 512);
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(buf + i * 512 + sc->et * 4), "f"(f[i]) : "memory");
+        ptx::fence_proxy_async();
+        if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // chunk k - 1 has left its buffer
+        ptx::bar_sync(1, 128);
+        if (issuer) {
+            const int i = sc->et & 15, d = sc->et >> 4;
+            if (i < nv) {
+                float *dst = outs[d] + (idx0 - sc->et) + (int64_t) i * ldo;
+                asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf + i * 512),
+                             "r"(sc->row_bytes)
+                             : "memory");
+            }
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        sc->k++;
+        return;
     }
     if (OUT != 0 && vec_ok) {
         const int lane = threadIdx.x & 31, j = lane & 3;
@@ -110,7 +156,8 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
 template <int OUT, int TO_SLOT>  // TO_SLOT: 0 fp32 output, 1 store the int32 partial, 2 red.add it into an accumulation tile
 __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, const int32_t *s_gs, const float *s_sc, bool ws,
                                            float w_scale, float *out0, float *const *outs, int n_out, int64_t idx0,
-                                           int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m, bool vec_ok = false) {
+                                           int64_t ldo, int tvalid, bool nvalid, int32_t *slot_m, bool vec_ok = false,
+                                           Scatter *sc = nullptr) {
     int32_t x[16];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -127,7 +174,7 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
 #pragma unroll
         for (int i = 0; i < 16; i++) __stcg(slot_m + (c0 + i) * 128, x[i]);
     } else {
-        store16<OUT>(x, s_sc + c0, ws, w_scale, out0, outs, n_out, idx0 + (int64_t) c0 * ldo, ldo, tvalid - c0, nvalid, vec_ok);
+        store16<OUT>(x, s_sc + c0, ws, w_scale, out0, outs, n_out, idx0 + (int64_t) c0 * ldo, ldo, tvalid - c0, nvalid, vec_ok, sc);
     }
 }
 
@@ -137,24 +184,24 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
 template <int NT, int OUT, int TO_SLOT>
 __device__ __forceinline__ void drain_fast(uint32_t ta, const int32_t *s_gs, const float *s_sc, float w_scale, float *out0,
                                            float *const *outs, int n_out, int64_t idx0, int64_t ldo, int tvalid, bool nvalid,
-                                           int32_t *slot_m, bool vec_ok = false) {
+                                           int32_t *slot_m, bool vec_ok = false, Scatter *sc = nullptr) {
     const bool ws = (w_scale != 1.0f);
     uint32_t va[16];
     ptx::tmem_ld_32x32b_x16(ta, va);
     if constexpr (NT == 16) {
         tmem_ld_wait_dep(va);
-        fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok);
+        fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok, sc);
     } else {
         uint32_t vb[16];
 #pragma unroll 1
         for (int c0 = 0; c0 < NT; c0 += 32) {
             tmem_ld_wait_dep(va);
             ptx::tmem_ld_32x32b_x16(ta + c0 + 16, vb);
-            fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok);
+            fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok, sc);
             tmem_ld_wait_dep(vb);
             if (c0 + 32 < NT) ptx::tmem_ld_32x32b_x16(ta + c0 + 32, va);
             fast_chunk<OUT, TO_SLOT>(vb, c0 + 16, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid,
-                                     slot_m, vec_ok);
+                                     slot_m, vec_ok, sc);
         }
     }
 }

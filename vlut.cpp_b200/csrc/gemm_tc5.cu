@@ -163,6 +163,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
     ptx::tc_fence_after();
     const uint32_t tmem_base = s_tmem_base;
     float *const out0 = (OUT == 0) ? p.g.out : p.g.outs[0];
+    static_assert(OUT >= 0 && OUT <= 3, "epilogue store flavour");
 
     const int ntiles = p.RP * p.TT;
     // p.whole: 1 = whole tiles only (uneven tile counts per pair), 0 = stream-K (every unit is a split unit),
@@ -390,6 +391,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         const int m = ew * 32 + lane;
         const int et = threadIdx.x;  // 0..127
         if (p.pdl) ptx::pdl_wait();  // reads predecessor outputs; owns all global writes of this kernel
+        // staged scatter (OUT == 3): the buffers sit behind the stage ring
+        epi::Scatter sct;
+        sct.init(smem_base + (uint32_t) S * p.stage_bytes, et);
+        epi::Scatter *const scp = (OUT == 3) ? &sct : nullptr;
         uint32_t ndrain = 0;
         const uint32_t accempty_leader0 = ptx::mapa(ptx::smem_u32(&s_accempty[0]), 0);
         const uint32_t accempty_leader1 = ptx::mapa(ptx::smem_u32(&s_accempty[1]), 0);
@@ -406,6 +411,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             const int tile = w.tile;
             const int64_t n = ((int64_t) 2 * w.rp + rank) * TILE_ROWS + m;
             const int64_t t0 = (int64_t) w.tt * NT;
+            if (OUT == 3) {
+                const int64_t rows = p.g.N - (n - m);   // rows of this strip that exist
+                sct.row_bytes = rows >= TILE_ROWS ? TILE_ROWS * 4 : (rows > 0 ? (int) rows * 4 : 0);
+            }
             // Split tile: every contributor red.adds its int32 partial into ONE accumulation tile (resolved in L2, fire
             // and forget), indexed by the first pair that owns a unit of the tile (unique among split tiles: a pair that
             // owned the first unit of two tiles would own all of the first).  The last arriver reads the sum back with
@@ -454,7 +463,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
                     if (complete)
                         epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
-                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0);
+                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0, scp);
                     else
                         epi::drain_fast<NT, OUT, 2>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                        p.g.ldo, tvalid, n < p.g.N, slot + m);
@@ -518,7 +527,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                         for (int j = 0; j < CB; j++)
                             epi::store16<OUT>(a[j], s_sc + c0 + 16 * j, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs,
                                               p.g.n_out, (t0 + c0 + 16 * j) * p.g.ldo + n, p.g.ldo,
-                                              (int) min((int64_t) 16, p.g.T - t0 - c0 - 16 * j), n < p.g.N, p.g.vec_ok != 0);
+                                              (int) min((int64_t) 16, p.g.T - t0 - c0 - 16 * j), n < p.g.N, p.g.vec_ok != 0, scp);
                     }
                     if (et == 0) *counter = 0;
                     mark(12);
@@ -526,6 +535,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             }
             ptx::bar_sync(1, 128);  // s_sc / s_last are reused by the next run
         }
+        if (OUT == 3) sct.finish();   // every bulk copy of this thread has been written out before the CTA may exit
     }
 
     // ---- teardown: nobody leaves (or frees TMEM) while the peer may still read this CTA's shared memory / TMEM ----
@@ -554,7 +564,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     if (forced > 0 && forced < ns) ns = forced;
     if (ns < MIN_STAGES) return cudaErrorInvalidValue;
     p.nstages = ns;
-    const size_t smem = (size_t) ns * p.stage_bytes + 1024;
+    const size_t smem = (size_t) ns * p.stage_bytes + 1024 + (OUT == 3 ? epi::SCATTER_BYTES : 0);
     auto kern = kernel<NT, SPS, OUT, SPA, NA>;
     static int smem_set[MAX_DEVICES] = {};
     cudaError_t e = ensure_dyn_smem(kern, smem, p.g.device, smem_set);
@@ -614,7 +624,9 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
 template <int NT, int SPS, int SPA, int NA>
 static cudaError_t launch_one(Params &p, int sm_count, cudaStream_t s) {
     if (p.g.n_out == 0) return launch_out<NT, SPS, 0, SPA, NA>(p, sm_count, s);
-    return p.g.multicast ? launch_out<NT, SPS, 2, SPA, NA>(p, sm_count, s) : launch_out<NT, SPS, 1, SPA, NA>(p, sm_count, s);
+    if (p.g.multicast) return launch_out<NT, SPS, 2, SPA, NA>(p, sm_count, s);
+    // peer pointers: staged bulk-copy scatter when the destinations allow it (16-byte aligned rows, N % 4 == 0)
+    return p.g.bulk_ok ? launch_out<NT, SPS, 3, SPA, NA>(p, sm_count, s) : launch_out<NT, SPS, 1, SPA, NA>(p, sm_count, s);
 }
 
 }  // namespace tc5

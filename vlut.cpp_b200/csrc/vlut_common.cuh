@@ -141,6 +141,8 @@ struct GemmArgs {
     int n_out;
     int multicast;
     int vec_ok;         // scatter destinations are 16-byte aligned with ldo % 4 == 0: four rows per lane per store
+    int bulk_ok;        // ... and N % 4 == 0, peer pointers: the CTA-pair kernel stages tiles in shared memory and scatters
+                        // them with bulk async copies (epilogue.cuh, Scatter)
     int64_t ldo;
     int64_t K, N, T, Npad;
     int type;
@@ -153,7 +155,8 @@ struct GemmArgs {
     int device;         // CUDA device ordinal (per-device caches of function attributes in the launchers)
 };
 
-// epilogue store, selected at compile time: 0 local, 1 peer scatter (NVLink P2P), 2 NVSwitch multicast (multimem.st)
+// epilogue store, selected at compile time: 0 local, 1 peer scatter (NVLink P2P), 2 NVSwitch multicast (multimem.st),
+// 3 peer scatter through shared-memory staging + bulk async copies (these direct stores are then only the exact path's)
 template <int MODE>
 __device__ __forceinline__ void store_out(float *const out, float *const *outs, int n_out, int64_t idx, float v) {
     if (MODE == 0) {
@@ -198,6 +201,7 @@ struct Knobs {
     int quant_kernel, quant_threads, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
     int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
     int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
+    int scatter_bulk;              // VLUT_SCATTER_BULK   0: no staged bulk-copy scatter in the CTA-pair kernel (comparison)
 };
 const Knobs &knobs();
 void knobs_reload();

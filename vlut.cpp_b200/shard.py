@@ -19,6 +19,8 @@ from __future__ import annotations
 from dataclasses import dataclass
 
 import numpy as np
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -134,7 +136,9 @@ class RowShardedWeight:
         slot = self._turn.get(T, 0)
         self._turn[T] = (slot + 1) % self.N_BUF
         buf, hdl = self.symm_out(T, slot)
-        mc = int(getattr(hdl, "multicast_ptr", 0) or 0)
+        # peer pointers by default (the CTA-pair kernel scatters staged tiles with bulk async copies);
+        # VLUT_SHARD_MULTICAST=1: NVSwitch multicast stores (multimem.st) instead
+        mc = int(getattr(hdl, "multicast_ptr", 0) or 0) if os.environ.get("VLUT_SHARD_MULTICAST", "0") == "1" else 0
         peers = [int(p) for p in hdl.buffer_ptrs]
         self.ctx.mul_mat_scatter(self.local, x, peers=peers, multicast_ptr=mc, ldo=self.N, col0=self.row0,
                                  w_scale=w_scale)
