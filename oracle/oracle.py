@@ -135,19 +135,23 @@ def ref_isa_candidates() -> list[str]:
 class RefLib:
     """The reference's own compiled kernels (kind = 'reference')."""
 
-    def __init__(self, isa: str | None = None):
+    def __init__(self, isa: str | None = None, path: Path | None = None, uneven_slices_ok: bool = False):
+        """``path``: load this build instead (tests/test_upstream_fixes.py: the kernels with docs/upstream_fixes.patch
+        applied, which also lifts the equal-slices restriction of the I1_V_2 tail, ``uneven_slices_ok``)."""
+        self.uneven_slices_ok = uneven_slices_ok
         d = HERE / "_ref"
         isa = isa or os.environ.get("VLUT_REF_ISA")
         cands = [isa] if isa else ref_isa_candidates()
-        path = next((d / f"libvlut_ref_{i}.so" for i in cands if (d / f"libvlut_ref_{i}.so").exists()), None)
+        if path is None:
+            path = next((d / f"libvlut_ref_{i}.so" for i in cands if (d / f"libvlut_ref_{i}.so").exists()), None)
         if path is None and Path("/root/reference/ggml/src/ggml-quants-vlut.c").exists():
             build(ref=True)
             path = next((d / f"libvlut_ref_{i}.so" for i in cands if (d / f"libvlut_ref_{i}.so").exists()), None)
         if path is None:
             raise FileNotFoundError("oracle/_ref/libvlut_ref_*.so not built (run `make -C oracle ref` where "
                                     "/root/reference exists)")
-        self.path = path
-        self.isa = path.stem.rsplit("_", 1)[1]
+        self.path = Path(path)
+        self.isa = self.path.stem.rsplit("_", 1)[1]
         self.lib = C.CDLL(str(path))
         L = self.lib
         L.vlut_ref_row_size.restype = C.c_size_t
@@ -191,7 +195,8 @@ class RefLib:
 
     def safe_nth(self, type_: int, K: int, N: int, nth: int) -> int:
         nth = max(1, nth)
-        if type_ == I1_V_2 and K % 20 != 0:
+        # the stock I1_V_2 tail addresses its weights with `- ith * nc`: only right when every thread has the same nc
+        if type_ == I1_V_2 and K % 20 != 0 and not self.uneven_slices_ok:
             while N % nth:
                 nth -= 1
         return nth

@@ -113,7 +113,9 @@ int vlut_ref_gemm(int type, int64_t K, int64_t N, int64_t T, const void *w, cons
     gemm_fn gemm = pick_gemm(type, &tile);
     if (!gemm) return -1;
     if (nth < 1) nth = 1;
+#ifndef VLUT_REF_UNEVEN_OK   /* defined for the build with docs/upstream_fixes.patch applied, which lifts the restriction */
     if (type == T_I1_V_2 && K % 20 != 0 && N % nth != 0) return -2;
+#endif
 #pragma omp parallel for num_threads(nth) schedule(static, 1)
     for (int ith = 0; ith < nth; ith++) {
         int64_t s0 = (ith * N) / nth, s1 = ((ith + 1) * N) / nth;
