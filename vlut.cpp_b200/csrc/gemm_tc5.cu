@@ -36,7 +36,7 @@ struct Params {
     int allow_fast, pdl;
     int split_last;  // experiment: walk the whole tiles before the split units
     int whole;  // 1: whole output tiles only (no fix-up); 0: stream-K over (tile, K-group) units; 2: hybrid (whole tiles + split remainder)
-    int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores, 16 no drain
+    int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores (exact path), 16 no fast-path drain, 32 no activation copies, 64 no weight copies
     long long *dbg;
     int dbg_skip;
 };
@@ -224,7 +224,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                         const uint32_t full = ptx::smem_u32(&s_full[st.i]);
                         const uint32_t dst = smem_base + st.i * p.stage_bytes;
                         const int64_t kb = w.kb0 + ab0 + s0;
-                        if (is_w) {
+                        if (p.abl & (is_w ? 64 : 32)) {
+                            ptx::mbar_arrive(full);   // timing ablation: this operand stream is not fetched
+                        } else if (is_w) {
                             ptx::mbar_arrive_expect_tx(full, ns * SUB_W_BYTES);
                             ptx::bulk_g2s_hint(dst + W_OFF, p.g.w + ((int64_t) rt * p.KB + kb) * SUB_W_BYTES, ns * SUB_W_BYTES,
                                                full, pol);
@@ -461,7 +463,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     // hot path: one drain per tile run, branch-free per value (epilogue.cuh)
                     const int64_t idx0 = t0 * p.g.ldo + n;
                     const int tvalid = (int) min((int64_t) NT, p.g.T - t0);
-                    if (complete)
+                    if (p.abl & 16) {
+                        // timing ablation: the accumulator is handed back undrained
+                    } else if (complete)
                         epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                         p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0, scp);
                     else
