@@ -43,7 +43,9 @@ def timed(fn, iters):
 
 ABLS = [(0, "full kernel"), (2, "no MMA"), (5, "no tcgen05.st / wait::st"), (16, "no drain"), (32, "no activation copies"),
         (64, "no weight copies"), (96, "no copies at all"), (2 | 5 | 16, "copies + barriers only"),
-        (2 | 5 | 16 | 96, "barriers only")]
+        (2 | 5 | 16 | 96, "barriers only"), (5 | 16 | 96, "MMA + barriers only"), (5 | 16, "MMA + copies"),
+        (5 | 96, "MMA + drain"), (16 | 96, "MMA + tcgen05.st"), (119 | 256, "barriers only, no LDS/unpack"),
+        (119 | 256 | 512, "A ring only (no stage ring)"), (117 | 256 | 512, "A ring + MMA only")]
 nts = [int(a) for a in sys.argv[1:]] or [128, 256]
 nb = api.nbytes(type_, K, N)
 for nt in nts:

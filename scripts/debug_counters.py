@@ -20,17 +20,20 @@ for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "16,128,512").s
     rc = _lib.lib().vlut_debug_tc_counters(buf.ctypes.data, buf.size)
     c = buf[:8192].reshape(256, 4, 8)
     ev = buf[8192:].reshape(4, 24, 2)
-    used = c[:, 1, 7] > 0
-    n = int(used.sum())
-    m = c[used].mean(axis=0)
-    print(f"T={T} rc={rc} CTAs={n}")
-    print(f"  producer: life {m[0,7]:.0f}  wait_empty {m[0,0]:.0f}")
-    print(f"  mma     : life {m[1,7]:.0f}  wait_full {m[1,0]:.0f}  wait_afull {m[1,1]:.0f}  wait_accempty {m[1,2]:.0f}")
-    print(f"  decode  : life {m[2,7]:.0f}  wait_full {m[2,0]:.0f}  wait_aempty {m[2,1]:.0f}  wait_st {m[2,2]:.0f}")
-    print(f"  epilogue: life {m[3,7]:.0f}  wait_accfull {m[3,0]:.0f}")
+    for name, used in (("leader CTAs", c[:, 1, 7] > 0), ("peer CTAs", (c[:, 1, 7] == 0) & (c[:, 2, 7] > 0))):
+        n = int(used.sum())
+        if n == 0:
+            continue
+        m = c[used].mean(axis=0)
+        print(f"T={T} rc={rc} {name}: {n}   (mean cycles per CTA; life = role start to role exit)")
+        print(f"  act producer: life {m[0,7]:.0f}  wait_empty {m[0,0]:.0f}")
+        print(f"  mma issuer  : life {m[1,7]:.0f}  wait_afull {m[1,1]:.0f}  wait_accempty {m[1,2]:.0f}")
+        print(f"  decode grp 0: life {m[2,7]:.0f}  wait_full {m[2,0]:.0f}  wait_aempty {m[2,1]:.0f}  wait_st {m[2,2]:.0f}")
+        print(f"  decode grp 1:               wait_full {m[2,3]:.0f}  wait_aempty {m[2,4]:.0f}  wait_st {m[2,5]:.0f}")
+        print(f"  epilogue    : life {m[3,7]:.0f}  wait_accfull {m[3,0]:.0f}")
 
     if os.environ.get("TIMELINE"):
         names = ["producer", "mma", "decode0", "epilogue"]
-        kinds = {0: "w0", 1: "w1", 2: "st-issued", 3: "fetched", 4: "st-done", 5: "fenced", 6: "chunk", 7: "drained", 8: "mma-issued", 9: "A-ready", 10: "parked", 11: "counted", 12: "fixed-up"}
+        kinds = {0: "w0", 1: "w1", 2: "st-issued", 3: "fetched", 4: "st-done", 5: "fenced", 6: "chunk", 7: "drained", 8: "mma-issued", 9: "A-ready", 10: "parked", 11: "counted", 12: "fixed-up", 13: "mmas-out", 14: "stage-committed"}
         for r in range(4):
             print("  timeline", names[r], " ".join(f"{int(t)}:{kinds.get(int(k), k)}" for t, k in ev[r] if t > 0))

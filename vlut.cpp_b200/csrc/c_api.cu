@@ -51,6 +51,8 @@ void knobs_reload() {
     k.tc_debug_skip = env_int("VLUT_TC_DEBUG_SKIP", 0);
     k.tc_nt = env_int("VLUT_TC_NT", 0);
     k.tc_astages = env_int("VLUT_TC_ASTAGES", 0);
+    k.tc_lean = env_int("VLUT_TC_LEAN", 1);
+    k.tc_bulk_out = env_int("VLUT_TC_BULK_OUT", 0);
     k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
     k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
     k.tcs_issuers = env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
@@ -575,6 +577,8 @@ static int gemm_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, i
     g.w = g.tens[0].w;
     g.out = g.tens[0].out;
     g.ldo = g.tens[0].ldo;
+    g.local_bulk = (g.n_out == 0 && knobs().tc_bulk_out && g.ldo % 4 == 0 && calls[0].N % 4 == 0 &&
+                    !(reinterpret_cast<uintptr_t>(g.out) & 15)) ? 1 : 0;
     g.N = g.tens[0].N;
     g.Npad = round_up(g.N, TILE_ROWS);
     g.type = calls[0].type;

@@ -94,9 +94,18 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
 #pragma unroll
         for (int i = 0; i < 16; i++) f[i] *= w_scale;
     }
-    if (OUT == 3 && sc != nullptr) {
+    constexpr int SO = (OUT == 4) ? 0 : OUT;   // the direct stores of the staged flavours' slow paths
+    if ((OUT == 3 || OUT == 4) && sc != nullptr) {
         // all 128 epilogue threads, same chunk: idx0 = (token of column 0) * ldo + (first row of the strip + et)
-        const bool issuer = sc->et < 16 * n_out;
+        // OUT == 4: one destination, the local output (the drain through direct stores spent ~270 SASS instructions per 16
+        // columns, most of them 64-bit address arithmetic and token-bound checks for 16 STG: 8300 clk per 128 x 128 tile
+        // against 8192 clk of tensor-pipe time; staged, a thread issues 16 st.shared and 16 threads one 512-byte copy each)
+        const int n_dst = (OUT == 4) ? 1 : n_out;
+        // 16 * n_dst copies per chunk, issued by threads spread over all four warps: bulk copies issued by one warp
+        // serialise (2 destinations from the 32 lanes of warp 0 moved 8 KB per ~1300 clk)
+        const int ncopies = 16 * n_dst, stride = ncopies >= 128 ? 1 : 128 / ncopies;
+        const int cidx = sc->et / stride;
+        const bool issuer = (sc->et % stride == 0) && cidx < ncopies;
         const uint32_t buf = sc->stage + (sc->k & 1u) * (16 * 512);
 #pragma unroll
         for (int i = 0; i < 16; i++)
@@ -105,9 +114,9 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // chunk k - 1 has left its buffer
         ptx::bar_sync(1, 128);
         if (issuer) {
-            const int i = sc->et & 15, d = sc->et >> 4;
+            const int i = cidx & 15, d = cidx >> 4;
             if (i < nv) {
-                float *dst = outs[d] + (idx0 - sc->et) + (int64_t) i * ldo;
+                float *dst = (OUT == 4 ? out0 : outs[d]) + (idx0 - sc->et) + (int64_t) i * ldo;
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf + i * 512),
                              "r"(sc->row_bytes)
                              : "memory");
@@ -117,7 +126,7 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         sc->k++;
         return;
     }
-    if (OUT != 0 && vec_ok) {
+    if (SO != 0 && vec_ok) {
         const int lane = threadIdx.x & 31, j = lane & 3;
         // which rows of this lane's group of four exist (ragged tail of the matrix)
         const unsigned gm = (__ballot_sync(0xffffffffu, nvalid) >> (lane & ~3)) & 0xfu;
@@ -131,11 +140,11 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
             const int tok = 4 * i + j;
             if (tok < nv) {
                 if (gm == 0xfu) {
-                    store_out4<OUT>(out0, outs, n_out, idxg + tok * ldo, make_float4(a[0], a[1], a[2], a[3]));
+                    store_out4<SO>(out0, outs, n_out, idxg + tok * ldo, make_float4(a[0], a[1], a[2], a[3]));
                 } else {
 #pragma unroll
                     for (int r = 0; r < 4; r++)
-                        if ((gm >> r) & 1u) store_out<OUT>(out0, outs, n_out, idxg + tok * ldo + r, a[r]);
+                        if ((gm >> r) & 1u) store_out<SO>(out0, outs, n_out, idxg + tok * ldo + r, a[r]);
                 }
             }
         }
@@ -143,12 +152,22 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
     }
     if (!nvalid) return;
     if (nv >= 16) {
+        if (SO == 0) {
+            // running pointer: one 64-bit add per store instead of a 64-bit multiply-add chain per store
+            float *pr = out0 + idx0;
 #pragma unroll
-        for (int i = 0; i < 16; i++) store_out<OUT>(out0, outs, n_out, idx0 + i * ldo, f[i]);
+            for (int i = 0; i < 16; i++) {
+                *pr = f[i];
+                pr += ldo;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; i++) store_out<SO>(out0, outs, n_out, idx0 + i * ldo, f[i]);
+        }
     } else {
 #pragma unroll
         for (int i = 0; i < 16; i++)
-            if (i < nv) store_out<OUT>(out0, outs, n_out, idx0 + i * ldo, f[i]);
+            if (i < nv) store_out<SO>(out0, outs, n_out, idx0 + i * ldo, f[i]);
     }
 }
 

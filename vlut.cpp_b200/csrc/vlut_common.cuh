@@ -143,6 +143,7 @@ struct GemmArgs {
     int vec_ok;         // scatter destinations are 16-byte aligned with ldo % 4 == 0: four rows per lane per store
     int bulk_ok;        // ... and N % 4 == 0, peer pointers: the CTA-pair kernel stages tiles in shared memory and scatters
                         // them with bulk async copies (epilogue.cuh, Scatter)
+    int local_bulk;     // n_out == 0 and `out` allows the staged drain (16-byte aligned, ldo % 4 == 0, N % 4 == 0): OUT = 4
     int64_t ldo;
     int64_t K, N, T, Npad;
     int type;
@@ -156,7 +157,8 @@ struct GemmArgs {
 };
 
 // epilogue store, selected at compile time: 0 local, 1 peer scatter (NVLink P2P), 2 NVSwitch multicast (multimem.st),
-// 3 peer scatter through shared-memory staging + bulk async copies (these direct stores are then only the exact path's)
+// 3 peer scatter through shared-memory staging + bulk async copies (these direct stores are then only the exact path's),
+// 4 the same staging for the single local destination
 template <int MODE>
 __device__ __forceinline__ void store_out(float *const out, float *const *outs, int n_out, int64_t idx, float v) {
     if (MODE == 0) {
@@ -196,11 +198,13 @@ struct Knobs {
     int tc_grid, tc_whole, tc_split_last;   // VLUT_TC_GRID, VLUT_TC_WHOLE, VLUT_TC_SPLIT_LAST (tests: force the split paths)
     int tc_abl, tc_debug, tc_debug_skip;    // VLUT_TC_ABL, VLUT_TC_DEBUG, VLUT_TC_DEBUG_SKIP
     int tc_nt;                     // VLUT_TC_NT          force the TCP token tile (128 / 256)
+    int tc_lean;                   // VLUT_TC_LEAN        0: the generic (unit-walking) decode loop even for uniform shapes (comparison, tests)
     int tc_astages;                // VLUT_TC_ASTAGES     2: two A stages of 512 k, 4: four of 256 k; default per token tile
     int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask, tcs_pre;   // VLUT_TCS_*
     int quant_kernel, quant_threads, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
     int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
     int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
+    int tc_bulk_out;               // VLUT_TC_BULK_OUT    1: the CTA-pair kernel drains single-GPU outputs through shared memory + bulk copies (measured slower: 16 copies of 512 B per chunk)
     int scatter_bulk;              // VLUT_SCATTER_BULK   0: no staged bulk-copy scatter in the CTA-pair kernel (comparison)
 };
 const Knobs &knobs();
