@@ -49,15 +49,16 @@ __device__ __forceinline__ void transpose4(float (&a)[4], int lane) {
 // memory fill NVLink (688 GB/s with this very access pattern, scripts/ubench/peer_store.cu) -- but inside the GEMM they
 // took 91 us for a 33 us GEMM + 43 us of link time: the stalled remote stores sit in the SM's load/store path, in front of
 // the decode warps' shared-memory loads and the next accumulator's drain.  So the four epilogue warps park 16 tokens x 128
-// rows of fp32 in a shared-memory buffer (two buffers), and one bulk async copy per (token, destination) -- 512 contiguous
+// rows of fp32 in a shared-memory buffer (a ring of SCATTER_NBUF), and one bulk async copy per (token, destination) -- 512 contiguous
 // bytes, issued by up to 128 different threads -- carries them out through the TMA engine: the SM's store path stays
 // empty and the copies drain under the following MMAs.
 // Protocol per 16-token chunk k (buffer k % 2), all 128 epilogue threads:
-//   issuers wait until their bulk copies of chunk k - 1 have READ shared memory (so buffer (k + 1) % 2 is free for the
-//   next chunk) -> everybody writes buffer k % 2 (free since the barrier of chunk k - 1) -> fence.proxy.async -> barrier
-//   -> issuers launch the copies of chunk k and commit.  One named barrier per chunk.
+//   everybody writes buffer k % NBUF (free since the barrier of chunk k - 1) -> fence.proxy.async -> issuers wait until
+//   their bulk copies of chunk k - (NBUF - 1) have READ shared memory (so buffer (k + 1) % NBUF is free for the next chunk)
+//   -> barrier -> issuers launch the copies of chunk k and commit.  One named barrier per chunk.  With two buffers only
+//   8 KB per destination and CTA were in flight: 1.2 MB chip-wide against ~2 MB of NVLink bandwidth x latency.
 struct Scatter {
-    uint32_t stage;      // shared-memory address of the two 16 x 128 x 4 B buffers
+    uint32_t stage;      // shared-memory address of the SCATTER_NBUF 16 x 128 x 4 B buffers
     uint32_t k;          // chunks staged so far
     int et;              // epilogue thread 0..127 == row of the strip
     int row_bytes;       // bytes of the strip's rows that exist (ragged last strip), multiple of 16
@@ -66,7 +67,8 @@ struct Scatter {
         asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
 };
-constexpr int SCATTER_BYTES = 2 * 16 * 128 * 4;
+constexpr int SCATTER_NBUF = 3;   // staging buffers: NBUF - 1 chunks (8 KB per destination each) in flight towards the peers per CTA
+constexpr int SCATTER_BYTES = SCATTER_NBUF * 16 * 128 * 4;
 
 // 16 final int32 sums of one weight row (tokens t .. t+15) -> fp32 outputs: out[(t+i) * ldo + n] = (float) x * s[t+i]
 // (* w_scale as a second rounding when `ws`).  nv = number of valid tokens among the 16 (>= 16: all); nvalid = this
@@ -106,12 +108,13 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         const int ncopies = 16 * n_dst, stride = ncopies >= 128 ? 1 : 128 / ncopies;
         const int cidx = sc->et / stride;
         const bool issuer = (sc->et % stride == 0) && cidx < ncopies;
-        const uint32_t buf = sc->stage + (sc->k & 1u) * (16 * 512);
+        const uint32_t buf = sc->stage + (sc->k % SCATTER_NBUF) * (16 * 512);
 #pragma unroll
         for (int i = 0; i < 16; i++)
             asm volatile("st.shared.f32 [%0], %1;" ::"r"(buf + i * 512 + sc->et * 4), "f"(f[i]) : "memory");
         ptx::fence_proxy_async();
-        if (issuer) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");   // chunk k - 1 has left its buffer
+        // chunk k - (NBUF - 1) has left its buffer, which the NEXT chunk will write
+        if (issuer) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(SCATTER_NBUF - 2) : "memory");
         ptx::bar_sync(1, 128);
         if (issuer) {
             const int i = cidx & 15, d = cidx >> 4;

@@ -732,6 +732,11 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     const int budget = (NT > 128 && kn.tc_smem_kb == 200 ? 204 : kn.tc_smem_kb) * 1024;
     p.stage_bytes = SPS * (NT / 2 * 128 + SUB_W_BYTES);  // multiple of 1024
     int ns = (budget - 1024) / p.stage_bytes;
+    {   // the staged drain's buffers share the 227 KB with the ring (and ~3 KB of static shared memory)
+        constexpr int scatter = (OUT == 3 || OUT == 4) ? epi::SCATTER_BYTES : 0;
+        const int fit = (224 * 1024 - 1024 - scatter) / p.stage_bytes;
+        if (ns > fit) ns = fit;
+    }
     if (ns > MAX_STAGES) ns = MAX_STAGES;
     int forced = kn.tc_stages;
     // the decode warps fetch the first stage of the next A block before they hand over the current one: the ring must

@@ -65,13 +65,17 @@ __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <
 // counts (profiles/r2_tcp_tiles.txt: it picks the faster tile in 23 of 24 cases, the miss costs 6 %):
 //     tile time = G * unit + tile_overhead;  whole / hybrid schedule as in launch_out (gemm_tc5.cu);  + fixed
 inline double pair_tile_cost(int64_t K, int64_t N, int64_t T, int NT, int gsize, int sm_count) {
-    const double unit = (NT > 128 ? 2000.0 : 1200.0) * (gsize == 640 ? 1.25 : 1.0);
-    const double tile = NT > 128 ? 10000.0 : 3500.0, fixed = NT > 128 ? 5000.0 : 9000.0;
+    // constants in clk, fitted to scripts/time_tcp.py on the lean-loop kernel (profiles/r2_tcp_tiles_lean.txt: the model picks
+    // the faster tile in 24 of 24 measured cases).  Shapes that cannot run the lean role loops (K-groups of 640 k: a full
+    // A block + a 128-k remainder per unit) pay ~2x per unit on the 128-token tile, 1.2x on the 256-token tile.
+    const bool lean = (gsize == 512 && K % 512 == 0);
+    const double unit = (NT > 128 ? 1900.0 : 1300.0) * (lean ? 1.0 : (NT > 128 ? 1.2 : 2.0));
+    const double tile = NT > 128 ? 6000.0 : 0.0, fixed = NT > 128 ? 9000.0 : 6000.0;
     const int64_t G = ceil_div(K, gsize), RP = (ceil_div(N, TILE_ROWS) + 1) / 2, TT = ceil_div(T, NT);
     const int64_t ptiles = RP * TT, npairs = sm_count / 2 > 0 ? sm_count / 2 : 1;
     const int64_t rounds = ceil_div(ptiles, npairs), full = ptiles / npairs, su = (ptiles - full * npairs) * G;
     const double whole = (double) rounds * (G * unit + tile);
-    const double hybrid = (double) full * (G * unit + tile) + (su ? (2.0 * ceil_div(su, npairs) + 3.0) * unit : 0.0);
+    const double hybrid = (double) full * (G * unit + tile) + (su ? (1.3 * ceil_div(su, npairs) + 3.0) * unit : 0.0);
     return (full >= 1 && hybrid < whole ? hybrid : whole) + fixed;
 }
 inline int token_tile_pair(int64_t K, int64_t N, int64_t T, int gsize, int sm_count, int forced) {
