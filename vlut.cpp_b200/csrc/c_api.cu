@@ -479,7 +479,8 @@ static int ensure_q_rm(vlut_ctx *c) {
 }
 
 int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
-    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO, 1);
+    // the weight's row count is unknown here: pick the token tile as for a typical FFN projection
+    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO, 8192);
 }
 
 int vlut_op_supported(int type, int64_t K, int64_t N, int64_t T) {
