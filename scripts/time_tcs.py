@@ -29,7 +29,7 @@ for type_, K, N in shapes:
     hi = 81 if type_ in (api.I2_V, api.I2_V_4, api.I2_V_8) else 243
     ws = [ctx.upload(type_, K, N, torch.randint(0, hi, (nb,), dtype=torch.uint8, device=dev, generator=gen)) for _ in range(n_w)]
     line = []
-    for T in (1, 16, 32, 64):
+    for T in [int(t) for t in os.environ.get("TS", "1,16,32,64").split(",")]:
         xs = [torch.randn((T, K), dtype=torch.float32, device=dev, generator=gen) for _ in range(4)]
         o = torch.empty((T, N), dtype=torch.float32, device=dev)
         ctx.quantize_act(type_, xs[0])

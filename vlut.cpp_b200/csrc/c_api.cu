@@ -55,6 +55,7 @@ void knobs_reload() {
     k.tc_bulk_out = env_int("VLUT_TC_BULK_OUT", 0);
     k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
     k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
+    k.tcs_rows = env_int("VLUT_TCS_ROWS", 0);
     k.tcs_issuers = env_int("VLUT_TCS_ISSUERS", 2) == 1 ? 1 : 2;
     k.tcs_depth = env_int("VLUT_TCS_DEPTH", 3);
     k.tcs_dbg_cta = env_int("VLUT_TCS_DBG_CTA", 0);

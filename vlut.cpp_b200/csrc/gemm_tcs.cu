@@ -65,6 +65,7 @@ struct Params {
     GemmArgs g;
     int KB, G, gsub, RT;
     int S;          // CTAs per strip (cluster size): K-groups split [r*G/S, (r+1)*G/S)
+    int R;          // weight rows per (virtual) strip, <= 128: rows [rt*R, rt*R + R) of the tensor; 128 = the T2 strips themselves
     int NAS, ASB;   // activation ring: NAS stages of ASB 128-k sub-blocks (ASB a power of two >= 4)
     int asb_shift;
     int allow_fast, pdl;
@@ -162,10 +163,14 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         const bool dmark = (d == 0);
         // this thread unpacks its row of the blocks b = ph, ph + 4, ...: 4 x 16 B per block (two 128-k sub-blocks of two
         // 64-k chunks), 32 KB further on each time
-        const uint8_t *wsrc = ten.w + ((int64_t) rt * (2 * p.KB) + 2 * kb_begin) * TILE_BYTES + m * 16;
+        // virtual strips (R < 128 rows, so that e.g. 14336 rows give 144 CTAs on 148 SMs instead of 112): row n of the tensor
+        // sits in T2 strip n / 128 at row n % 128; lanes beyond the strip's R rows (or the padded matrix) fetch nothing
+        const int64_t nrow = (int64_t) rt * p.R + m;
+        const bool wrow = m < p.R && nrow < (int64_t) round_up(ten.N, TILE_ROWS);
+        const uint8_t *wsrc = ten.w + ((int64_t) (nrow >> 7) * (2 * p.KB) + 2 * kb_begin) * TILE_BYTES + (nrow & 127) * 16;
         const uint32_t wdst = wring + dt * 16;
         auto issue = [&](int b, int slot) {   // this thread's 64 bytes of block b -> ring slot; always one commit group
-            if (!ABL(8) && b < nblk) {
+            if (!ABL(8) && b < nblk && wrow) {
                 const uint8_t *src = wsrc + (int64_t) b * W_BLOCK_BYTES;
                 ptx::cp_async16(wdst + (slot * 4 + 0) * (DEC_THREADS * 16), src);
                 ptx::cp_async16(wdst + (slot * 4 + 1) * (DEC_THREADS * 16), src + TILE_BYTES);
@@ -441,7 +446,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
             if (ew == 0) mark(10);
             const int m = ew * 32 + lane;
             const int et = threadIdx.x;  // 0..127
-            const int64_t n = (int64_t) rt * TILE_ROWS + m;
+            const int64_t n = (m < p.R) ? (int64_t) rt * p.R + m : (int64_t) 1 << 40;   // rows beyond the virtual strip: never valid
             const int64_t t0 = (int64_t) tt * NT;
             const int32_t *pre = p.g.act.gpre + (t0 + et) * (p.G + 1);
             float *const out0 = (OUT == 0) ? ten.out : p.g.outs[0];
@@ -539,7 +544,7 @@ __global__ void __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Par
         ptx::cluster_sync();
         if (warp < 4) {
             const int m = warp * 32 + lane;
-            const int64_t n = (int64_t) rt * TILE_ROWS + m;
+            const int64_t n = (m < p.R) ? (int64_t) rt * p.R + m : (int64_t) 1 << 40;   // rows beyond the virtual strip: never valid
             const int64_t t0 = (int64_t) tt * NT;
             float *const out0 = (OUT == 0) ? ten.out : p.g.outs[0];
             const int c_lo = (rank * NT) / S, c_hi = ((rank + 1) * NT) / S;
@@ -632,26 +637,50 @@ static cudaError_t launch_one(Params &p, cudaStream_t s) {
     return p.g.multicast ? launch_out<NT, 2, DT>(p, s) : launch_out<NT, 1, DT>(p, s);
 }
 
-// CTAs per strip.  More CTAs = more weight bytes in flight and shorter per-CTA chains; a split strip pays one cluster
-// barrier and a distributed-shared-memory reduction.  Whole K-groups per CTA, at most 8 (portable cluster size), one CTA
-// per SM.
-static int pick_split(const Params &p) {
-    const int forced = knobs().tcs_split;
+// CTAs per strip (S) and rows per strip (R).  Whole K-groups per CTA, at most 8 (portable cluster size), one CTA per SM.
+// Measured grid (scripts/grid_tcs.sh, profiles/r2_tcs_split_rows.txt), in units of one 512-k K-group of streaming
+// (~0.30 us): a launch costs ~6 units whatever it does, a split strip another ~8 + 0.7 S (cluster launch, cluster
+// barrier, distributed-shared-memory reduction) -- so S > 1 only pays for long K (14336 -> 4096: S = 4, 10.3 -> 7.2 us);
+// round 1's model charged 0.6 units for a split and picked S = 2..4 for 4096 -> 4096 (5.3 us; S = 1: 4.2 us), 3200 -> 8640
+// (6.5 us; 4.0 us) and 2048 -> 8192 (5.9 us; 3.1 us).  R < 128 ("virtual strips": rows [rt R, rt R + R) of the tensor, so
+// that e.g. 14336 rows give 144 CTAs on 148 SMs instead of 112) measured 0.3-0.5 us SLOWER at every shape although each
+// CTA streams less: kept behind VLUT_TCS_ROWS, not selected.
+// Sets p.S, p.R, p.RT and the first (virtual) strip of every tensor of the batch.
+static void pick_split_rows(Params &p, int token_tiles) {
+    const Knobs &kn = knobs();
     const int smax = p.G < 8 ? p.G : 8;
-    if (forced > 0) return forced < smax ? forced : smax;
     const int slots = p.g.sm_count;
-    int best = 1;
+    auto strips_of = [&](int R) {
+        int64_t n = 0;
+        for (int i = 0; i < p.g.n_tens; i++) n += ceil_div(p.g.tens[i].N, R);
+        return n;
+    };
+    int bestS = 1, bestR = TILE_ROWS;
     double best_cost = 1e30;
     for (int s = 1; s <= smax; s++) {
-        const int64_t ctas = (int64_t) p.RT * s;
-        if (ctas > slots && s > 1) break;
-        const int max_groups = (p.G + s - 1) / s;
-        const int waves = (int) ((ctas + slots - 1) / slots);
-        // time ~ fixed start/drain cost (about 3 K-groups' worth) + the longest per-CTA chain + a cost per split
-        const double cost = (double) max_groups * waves + 3.0 + 0.6 * (s > 1) + 0.05 * s;
-        if (cost < best_cost - 1e-9) { best_cost = cost; best = s; }
+        if (kn.tcs_split > 0 && s != (kn.tcs_split < smax ? kn.tcs_split : smax)) continue;
+        if (kn.tcs_split <= 0 && (s & (s - 1)) != 0) continue;   // clusters of 1, 2, 4, 8 (S = 6 on 24 strips measured 2x slower than S = 8 on 16)
+        for (int R = TILE_ROWS; R >= 64; R -= 4) {
+            if (kn.tcs_rows > 0 ? R != kn.tcs_rows : R != TILE_ROWS) continue;
+            const int64_t ctas = strips_of(R) * s * token_tiles;
+            if (ctas > slots && s > 1 && kn.tcs_split <= 0) continue;
+            const int max_groups = (p.G + s - 1) / s;
+            const int waves = (int) ((ctas + slots - 1) / slots);
+            // units of one 512-k group of streaming (~0.30 us); an I1 group is 640 k
+            const double cost = (double) max_groups * (p.gsub / 4.0) * waves * ((double) R / TILE_ROWS) + 6.0 +
+                                (s > 1 ? 8.0 + 0.7 * s : 0.0);
+            if (cost < best_cost - 1e-9) { best_cost = cost; bestS = s; bestR = R; }
+        }
     }
-    return best;
+    p.S = bestS;
+    p.R = bestR;
+    int strips = 0;
+    for (int i = 0; i < p.g.n_tens; i++) {
+        p.g.tens[i].strip0 = strips;
+        strips += (int) ceil_div(p.g.tens[i].N, p.R);
+    }
+    p.g.tens[p.g.n_tens].strip0 = strips;   // sentinel
+    p.RT = strips;
 }
 
 }  // namespace tcs
@@ -670,10 +699,9 @@ cudaError_t launch_gemm_tcs(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.gsub = g.act.gsize / 128;
     p.G = g.act.G;
     const Knobs &kn = knobs();
-    p.RT = g.tens[g.n_tens].strip0;   // strips of all the tensors of the batch
     p.allow_fast = kn.tc_fast;
     p.pdl = kn.pdl;
-    p.S = tcs::pick_split(p);
+    tcs::pick_split_rows(p, (int) (g.act.Tpad / NT));   // p.S, p.R, p.RT, virtual strips of the batch
     p.issuers = kn.tcs_issuers;
     p.pre = kn.tcs_pre >= 0 ? kn.tcs_pre : 8;   // default: the whole ring up front (staggering measured slower: 6.0 vs 5.5 us)
     p.dbg = kn.tc_debug ? debug_buffer(s, 0) : nullptr;

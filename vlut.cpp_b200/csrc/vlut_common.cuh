@@ -205,6 +205,7 @@ struct Knobs {
     int tc_lean;                   // VLUT_TC_LEAN        0: the generic (unit-walking) decode loop even for uniform shapes (comparison, tests)
     int tc_astages;                // VLUT_TC_ASTAGES     2: two A stages of 512 k, 4: four of 256 k; default per token tile
     int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask, tcs_pre;   // VLUT_TCS_*
+    int tcs_rows;                  // VLUT_TCS_ROWS       force the rows per (virtual) strip of the small-T kernel (64..128, multiple of 4; 128 = off)
     int quant_kernel, quant_threads, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
     int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
     int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
