@@ -62,7 +62,13 @@ struct Scatter {
     uint32_t k;          // chunks staged so far
     int et;              // epilogue thread 0..127 == row of the strip
     int row_bytes;       // bytes of the strip's rows that exist (ragged last strip), multiple of 16
-    __device__ __forceinline__ void init(uint32_t stage_smem, int et_) { stage = stage_smem; k = 0; et = et_; row_bytes = 512; }
+    // OUT == 4 (local output through a tensor map): one 2-D TMA store per 16-token chunk, issued by thread 0; the hardware
+    // clips rows / tokens beyond the matrix
+    const void *tmap;    // CUtensorMap of the output [T][ldo] (box 128 rows x 16 tokens), in kernel parameter space
+    int n0, tok;         // first row of the strip; token of the next chunk (set per tile, advanced per chunk)
+    __device__ __forceinline__ void init(uint32_t stage_smem, int et_) {
+        stage = stage_smem; k = 0; et = et_; row_bytes = 512; tmap = nullptr; n0 = 0; tok = 0;
+    }
     __device__ __forceinline__ void finish() const {   // every copy of this thread has been written out
         asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
     }
@@ -97,12 +103,28 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         for (int i = 0; i < 16; i++) f[i] *= w_scale;
     }
     constexpr int SO = (OUT == 4) ? 0 : OUT;   // the direct stores of the staged flavours' slow paths
-    if ((OUT == 3 || OUT == 4) && sc != nullptr) {
+    if (OUT == 4 && sc != nullptr) {
+        // local output, staged: 16 st.shared per thread (immediate offsets, no address arithmetic), one named barrier and ONE
+        // tensor store per chunk.  (The direct drain spends ~115 instructions per thread and chunk, 48 of them address adds and
+        // STG; sixteen 512-byte bulk copies per chunk instead of the tensor store measured slower than the direct stores.)
+        const uint32_t buf = sc->stage + (sc->k % SCATTER_NBUF) * (16 * 512);
+#pragma unroll
+        for (int i = 0; i < 16; i++)
+            asm volatile("st.shared.f32 [%0], %1;" ::"r"(buf + i * 512 + sc->et * 4), "f"(f[i]) : "memory");
+        ptx::fence_proxy_async();
+        if (sc->et == 0) asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(SCATTER_NBUF - 2) : "memory");
+        ptx::bar_sync(1, 128);
+        if (sc->et == 0) {
+            if (nv > 0) ptx::tma_store_2d(sc->tmap, sc->n0, sc->tok, buf);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+        }
+        sc->tok += 16;
+        sc->k++;
+        return;
+    }
+    if (OUT == 3 && sc != nullptr) {
         // all 128 epilogue threads, same chunk: idx0 = (token of column 0) * ldo + (first row of the strip + et)
-        // OUT == 4: one destination, the local output (the drain through direct stores spent ~270 SASS instructions per 16
-        // columns, most of them 64-bit address arithmetic and token-bound checks for 16 STG: 8300 clk per 128 x 128 tile
-        // against 8192 clk of tensor-pipe time; staged, a thread issues 16 st.shared and 16 threads one 512-byte copy each)
-        const int n_dst = (OUT == 4) ? 1 : n_out;
+        const int n_dst = n_out;
         // 16 * n_dst copies per chunk, issued by threads spread over all four warps: bulk copies issued by one warp
         // serialise (2 destinations from the 32 lanes of warp 0 moved 8 KB per ~1300 clk)
         const int ncopies = 16 * n_dst, stride = ncopies >= 128 ? 1 : 128 / ncopies;
@@ -119,7 +141,7 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         if (issuer) {
             const int i = cidx & 15, d = cidx >> 4;
             if (i < nv) {
-                float *dst = (OUT == 4 ? out0 : outs[d]) + (idx0 - sc->et) + (int64_t) i * ldo;
+                float *dst = outs[d] + (idx0 - sc->et) + (int64_t) i * ldo;
                 asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(buf + i * 512),
                              "r"(sc->row_bytes)
                              : "memory");

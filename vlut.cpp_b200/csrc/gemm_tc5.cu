@@ -16,6 +16,35 @@ bool gemm_tc5_supported(int type, int64_t K, int64_t N, int64_t T) {
     return type_valid(type) && T > 32 && K >= 4 && N >= 1 && ceil_div(K, group_size(type)) <= 64;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (the library links cudart only)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *, const cuuint64_t *,
+                                  const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = (EncodeTiledFn) f;
+    }
+    return fn;
+}
+// out [T][ldo] f32 as a 2-D tensor {N, T}, box {128 rows, 16 tokens}: the staged drain's TMA stores (OUT == 4)
+static bool make_out_map(CUtensorMap *m, float *out, int64_t N, int64_t T, int64_t ldo) {
+    EncodeTiledFn fn = encode_tiled_fn();
+    if (!fn) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t) N, (cuuint64_t) T};
+    const cuuint64_t strides[1] = {(cuuint64_t) ldo * 4};
+    const cuuint32_t box[2] = {128, 16};
+    const cuuint32_t estr[2] = {1, 1};
+    return fn(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, out, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     if (g.act.sw_tile * 2 != g.act.NT) return cudaErrorInvalidValue;  // wants half-height swizzled activation tiles
     tc5::Params p{};
@@ -29,6 +58,7 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.TT = (int) (g.act.Tpad / NT);
     p.U = p.RP * p.TT * p.G;
     const Knobs &kn = knobs();
+    if (p.g.local_bulk && !make_out_map(&p.out_map, g.out, g.N, g.T, g.ldo)) p.g.local_bulk = 0;   // no tensor map: direct stores
     p.allow_fast = kn.tc_fast;
     p.uniform = (kn.tc_lean && p.KB % p.gsub == 0) ? 1 : 0;
     p.pdl = kn.pdl;

@@ -42,6 +42,7 @@ struct Params {
     int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores (exact path), 16 no fast-path drain, 32 no activation copies, 64 no weight copies, 256 no LDS / unpack, 512 no stage ring at all (producers idle, decode does not wait for stages)
     long long *dbg;
     int dbg_skip, dbg_cta;
+    alignas(64) CUtensorMap out_map;   // OUT == 4: the output [T][ldo] f32 as a 2-D tensor, box 128 rows x 16 tokens (TMA stores)
 };
 
 __device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
@@ -588,6 +589,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             if (STAGED) {
                 const int64_t rows = p.g.N - (n - m);   // rows of this strip that exist
                 sct.row_bytes = rows >= TILE_ROWS ? TILE_ROWS * 4 : (rows > 0 ? (int) rows * 4 : 0);
+                sct.tmap = &p.out_map;
+                sct.n0 = (int) (n - m);
+                sct.tok = (int) t0;
             }
             // Split tile: every contributor red.adds its int32 partial into ONE accumulation tile (resolved in L2, fire
             // and forget), indexed by the first pair that owns a unit of the tile (unique among split tiles: a pair that

@@ -79,6 +79,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const void *tmap,
         "l"(tmap), "r"(c0), "r"(c1), "r"(bar)
         : "memory");
 }
+// 2-D tiled tensor copy shared -> global through a CUtensorMap (SASS: UTMASTG), bulk-group completion; elements outside
+// the tensor's bounds are clipped by the hardware
+__device__ __forceinline__ void tma_store_2d(const void *tmap, int32_t c0, int32_t c1, uint32_t src_smem) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(tmap), "r"(c0), "r"(c1),
+                 "r"(src_smem)
+                 : "memory");
+}
 __device__ __forceinline__ void prefetch_tmap(const void *tmap) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(tmap) : "memory");
 }
