@@ -609,3 +609,53 @@ def test_fused_scatter_bulk_copies(ctx, orc, knobs, bulk, T, N, bounds, K, kind,
     for b in bufs:
         assert np.array_equal(bits(b[:T, :N].cpu().numpy()), bits(ref))
         assert (b[T:] == -7.0).all() and (b[:, N:] == -7.0).all()
+
+
+@pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
+@pytest.mark.parametrize("lean,astages,bulk_out,nt", [(1, 2, 0, 128), (0, 2, 0, 128), (1, 3, 0, 128), (1, 4, 0, 128),
+                                                     (1, 2, 1, 128), (0, 4, 1, 128), (1, 4, 0, 256), (0, 2, 1, 256)])
+@pytest.mark.parametrize("T", [65, 130, 300, 700])
+def test_tcp_role_loop_and_drain_variants(ctx, orc, knobs, lean, astages, bulk_out, nt, T, fast):
+    """Every shipped variant of the CTA-pair kernel's role loops and drain: lean loops (uniform shapes) vs the generic
+    unit-walking loops (VLUT_TC_LEAN=0, and always for the I1 types' 640-k groups and K not a multiple of the group size),
+    two / three (single accumulator) / four A stages, both token tiles, direct stores vs the staged drain through one 2-D TMA
+    tensor store per chunk (VLUT_TC_BULK_OUT=1; needs 16-byte aligned rows: N % 4 == 0, the ragged N = 900 shape clips at
+    the tensor bound), fast and exact (per-K-group) drains."""
+    a = api()
+    knobs(VLUT_TC_LEAN=lean, VLUT_TC_ASTAGES=astages, VLUT_TC_BULK_OUT=bulk_out, VLUT_TC_NT=nt, VLUT_TC_FAST=fast)
+    for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I2_V_4, 4096, 900), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 388)]:
+        w = O.make_ternary(N, K, seed=T + astages)
+        x = O.make_acts(T, K, seed=T, kind="uniform" if (T + astages) % 2 else "normal")
+        packed = orc.pack(type_, w)
+        ref = orc.mul_mat(type_, packed, x, N)
+        for rep in range(2):
+            out = run(ctx, type_, packed, x, N, a.ALGO_TCP)
+            bad = bits(out) != bits(ref)
+            assert not bad.any(), f"{O.TYPE_NAMES[type_]} K={K} N={N} rep={rep}: {bad.sum()} of {bad.size} differ"
+
+
+@pytest.mark.parametrize("rows", [128, 112, 100, 64])
+@pytest.mark.parametrize("split", [1, 2])
+@pytest.mark.parametrize("T", [1, 16, 48])
+def test_tcs_virtual_strips(ctx, orc, knobs, rows, split, T):
+    """VLUT_TCS_ROWS: the small-T kernel with fewer than 128 weight rows per CTA (a CTA's rows then straddle two T2 strips,
+    lanes beyond its rows fetch and store nothing), alone and combined with the cluster split; single tensors with ragged N
+    and the batched launch (several tensors in one strip index space)."""
+    a = api()
+    knobs(VLUT_TCS_ROWS=rows, VLUT_TCS_SPLIT=split)
+    for type_, K, N in [(O.I2_V_4, 2048, 1000), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 129)]:
+        w = O.make_ternary(N, K, seed=rows)
+        x = O.make_acts(T, K, seed=T)
+        packed = orc.pack(type_, w)
+        ref = orc.mul_mat(type_, packed, x, N)
+        out = run(ctx, type_, packed, x, N, a.ALGO_TCS)
+        assert np.array_equal(bits(out), bits(ref)), f"{O.TYPE_NAMES[type_]} K={K} N={N}"
+    # batched: three tensors of different heights share the activation
+    K, Ns = 2048, [520, 128, 260]
+    x = O.make_acts(T, K, seed=3)
+    packs = [orc.pack(O.I2_V_4, O.make_ternary(n, K, seed=n)) for n in Ns]
+    ws = [ctx.upload(O.I2_V_4, K, n, p) for n, p in zip(Ns, packs)]
+    outs = ctx.mul_mat_batch(ws, torch.from_numpy(x).cuda())
+    torch.cuda.synchronize()
+    for n, p, o in zip(Ns, packs, outs):
+        assert np.array_equal(bits(o.cpu().numpy()), bits(orc.mul_mat(O.I2_V_4, p, x, n))), f"batched N={n}"
