@@ -228,22 +228,24 @@ __device__ __forceinline__ void fast_chunk(const uint32_t (&v)[16], int c0, cons
 template <int NT, int OUT, int TO_SLOT>
 __device__ __forceinline__ void drain_fast(uint32_t ta, const int32_t *s_gs, const float *s_sc, float w_scale, float *out0,
                                            float *const *outs, int n_out, int64_t idx0, int64_t ldo, int tvalid, bool nvalid,
-                                           int32_t *slot_m, bool vec_ok = false, Scatter *sc = nullptr) {
+                                           int32_t *slot_m, bool vec_ok = false, Scatter *sc = nullptr, int c_begin = 0,
+                                           int c_end = NT) {
+    // [c_begin, c_end): this warp's share of the NT columns (multiples of 32; two epilogue warpgroups split a tile)
     const bool ws = (w_scale != 1.0f);
     uint32_t va[16];
-    ptx::tmem_ld_32x32b_x16(ta, va);
+    ptx::tmem_ld_32x32b_x16(ta + c_begin, va);
     if constexpr (NT == 16) {
         tmem_ld_wait_dep(va);
         fast_chunk<OUT, TO_SLOT>(va, 0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok, sc);
     } else {
         uint32_t vb[16];
 #pragma unroll 1
-        for (int c0 = 0; c0 < NT; c0 += 32) {
+        for (int c0 = c_begin; c0 < c_end; c0 += 32) {
             tmem_ld_wait_dep(va);
             ptx::tmem_ld_32x32b_x16(ta + c0 + 16, vb);
             fast_chunk<OUT, TO_SLOT>(va, c0, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid, slot_m, vec_ok, sc);
             tmem_ld_wait_dep(vb);
-            if (c0 + 32 < NT) ptx::tmem_ld_32x32b_x16(ta + c0 + 32, va);
+            if (c0 + 32 < c_end) ptx::tmem_ld_32x32b_x16(ta + c0 + 32, va);
             fast_chunk<OUT, TO_SLOT>(vb, c0 + 16, s_gs, s_sc, ws, w_scale, out0, outs, n_out, idx0, ldo, tvalid, nvalid,
                                      slot_m, vec_ok, sc);
         }

@@ -26,7 +26,17 @@ namespace vlut {
 
 namespace tc5 {
 
-constexpr int THREADS = 480;
+constexpr int THREADS = 480;          // warps 0-3 epilogue, 4-11 decode, 12 activation producer, 13 MMA issuer, 14 TMEM + weight producer
+#ifndef VLUT_TC_EPI2
+#define VLUT_TC_EPI2 0
+#endif
+// VLUT_TC_EPI2=1 (compile time): a SECOND epilogue warpgroup (warps 15-18) for the direct-store flavour, the two groups
+// splitting every tile's columns.  Motivation: the drain of a tile takes a warp ~8200 clk inside the main loop (as long as
+// the tile's MMAs) and ~3000 clk alone.  Measured (bit-exact, 631 tests): 608 threads cap the kernel at 96 registers and
+// add four more warps to the schedulers the decode warps run on -- T = 512 25.6 -> 26.3 us, the 256-token tile at
+// T = 1024 49.2 -> 63.4 us.  Off.
+__host__ __device__ constexpr int epi_groups(int out) { return (VLUT_TC_EPI2 && out == 0) ? 2 : 1; }
+__host__ __device__ constexpr int threads_for(int out) { return THREADS + (epi_groups(out) - 1) * 128; }
 constexpr int MAX_NA = 4;          // A stages in TMEM (ring)
 constexpr int MAX_STAGES = 12;
 constexpr int SUB_W_BYTES = 4096;
@@ -108,7 +118,9 @@ struct Ring {
 // 512 k in flight; (2, 4): four of 256 k -- the in-kernel timeline (profiles/r2_timeline_tcp.txt) showed the issuer waiting
 // ~700 clk per 512-k block for the decode -> st -> wait::st -> remote-arrive chain with only two stages to hide it behind.
 template <int NT, int SPS, int OUT, int SPA, int NA>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(const __grid_constant__ Params p) {
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1) kernel(const __grid_constant__ Params p) {
+    constexpr int EG = epi_groups(OUT);              // epilogue warpgroups
+    constexpr int ET = 128 * EG;                     // epilogue threads (named barrier 1)
     constexpr int A_COLS = SPA * 32;                 // TMEM columns of one A stage
     static_assert(NA <= MAX_NA, "A ring");
     static_assert(SPA % SPS == 0, "an A stage is a whole number of shared-memory stages");
@@ -154,7 +166,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         }
         for (int d = 0; d < 2; d++) {
             ptx::mbar_init(ptx::smem_u32(&s_accfull[d]), 1);
-            ptx::mbar_init(ptx::smem_u32(&s_accempty[d]), 8);   // used in the leader: epilogue warps of both CTAs
+            ptx::mbar_init(ptx::smem_u32(&s_accempty[d]), 8 * EG);   // used in the leader: epilogue warps of both CTAs
         }
         ptx::fence_barrier_init();
     }
@@ -559,12 +571,17 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
         }
         }   // generic decode loop
         if (q == 0 && lane == 0) tflush(2, h * 3);
-    } else if (warp < 4) {
+    } else if (warp < 4 || (EG == 2 && warp >= 15)) {
         // ===================== epilogue: this CTA's 128 rows x NT tokens =====================
+        // EG warpgroups; group eg drains the columns [eg NT / EG, (eg + 1) NT / EG) of every accumulator.  A warp reads the
+        // TMEM lane quadrant warp % 4.
         ev_role = 3;
-        const int ew = warp;
+        const int eg = (warp < 4) ? 0 : 1;
+        const int ew = warp & 3;
         const int m = ew * 32 + lane;
-        const int et = threadIdx.x;  // 0..127
+        const int et = eg * 128 + m;  // 0 .. ET - 1
+        constexpr int CW = NT / EG;   // columns per group
+        const int cbeg = eg * CW, cend = cbeg + CW;
         if (p.pdl) ptx::pdl_wait();  // reads predecessor outputs; owns all global writes of this kernel
         // staged scatter (OUT == 3): the buffers sit behind the stage ring
         epi::Scatter sct;
@@ -604,7 +621,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                 const int b_first = (int) (((x + 1) * npairs - 1) / SU);
                 slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * NT);
             }
-            for (int i = et; i < NT; i += 128) s_sc[i] = __ldg(p.g.act.scales + t0 + i);
+            for (int i = et; i < NT; i += ET) s_sc[i] = __ldg(p.g.act.scales + t0 + i);
 
             auto emit = [&](int c0, const int32_t (&vals)[16]) {
                 if (complete) {
@@ -627,10 +644,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
             for (int u = ra; u <= rb; u++, w.next()) {
                 if (fast && u != rb) continue;  // fast path: a single drain at the end of the run
                 const uint32_t ab = ndrain % NACC;
-                for (int i = et; i < NT; i += 128)
+                for (int i = et; i < NT; i += ET)
                     s_gs[i] = __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + w.g + 1) -
                               __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + (fast ? g_begin : w.g));
-                ptx::bar_sync(1, 128);
+                ptx::bar_sync(1, ET);
                 twait(ptx::smem_u32(&s_accfull[ab]), (ndrain / NACC) & 1, 0);
                 mark(0);
                 ptx::tc_fence_after();
@@ -643,14 +660,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                         // timing ablation: the accumulator is handed back undrained
                     } else if (complete)
                         epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
-                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0, scp);
+                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0, scp, cbeg, cend);
                     else
                         epi::drain_fast<NT, OUT, 2>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
-                                                       p.g.ldo, tvalid, n < p.g.N, slot + m);
+                                                       p.g.ldo, tvalid, n < p.g.N, slot + m, false, nullptr, cbeg, cend);
                 } else {
                     // exact path: int16 wrap per K-group, running totals in the scratch tile
 #pragma unroll 1
-                    for (int c0 = 0; c0 < NT; c0 += 16) {
+                    for (int c0 = cbeg; c0 < cend; c0 += 16) {
                         uint32_t v[16];
                         ptx::tmem_ld_32x32b_x16(ta + c0, v);
                         ptx::tmem_ld_wait();
@@ -658,13 +675,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
 #pragma unroll
                         for (int i = 0; i < 16; i++) {
                             const int32_t x = (int32_t) v[i] - s_gs[c0 + i];
-                            vals[i] = (u == ra) ? wrap16(x) : tots[(c0 + i) * 128 + et] + wrap16(x);
+                            vals[i] = (u == ra) ? wrap16(x) : tots[(c0 + i) * 128 + m] + wrap16(x);
                         }
                         if (u == rb) {
                             emit(c0, vals);
                         } else {
 #pragma unroll
-                            for (int i = 0; i < 16; i++) tots[(c0 + i) * 128 + et] = vals[i];
+                            for (int i = 0; i < 16; i++) tots[(c0 + i) * 128 + m] = vals[i];
                         }
                     }
                 }
@@ -673,27 +690,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                 if (lane == 0) ptx::mbar_arrive_cluster(ab ? accempty_leader1 : accempty_leader0);
                 mark(7);
                 ++ndrain;
-                ptx::bar_sync(1, 128);  // s_gs is rewritten by the next drain
+                ptx::bar_sync(1, ET);  // s_gs is rewritten by the next drain
             }
 
             if (!complete) {
                 // split tile (stream-K): partial parked above; the last CTA to arrive sums all slots and finishes
                 mark(10);
                 __threadfence();
-                ptx::bar_sync(1, 128);
+                ptx::bar_sync(1, ET);
                 int32_t *const counter = p.g.counters + tile * 2 + rank;
                 if (et == 0) {
                     const int ndone = g_end - g_begin + 1;
                     const int old = atomicAdd(counter, ndone);
                     s_last = (old + ndone == p.G);
                 }
-                ptx::bar_sync(1, 128);
+                ptx::bar_sync(1, ET);
                 mark(11);
                 if (s_last) {
                     __threadfence();
-                    constexpr int CB = (NT >= 64) ? 4 : NT / 16;  // 16-column chunks per round trip
+                    constexpr int CB = (CW >= 64) ? 4 : CW / 16;  // 16-column chunks per round trip
 #pragma unroll 1
-                    for (int c0 = 0; c0 < NT; c0 += 16 * CB) {
+                    for (int c0 = cbeg; c0 < cend; c0 += 16 * CB) {
                         int32_t a[CB][16];
 #pragma unroll
                         for (int j = 0; j < CB; j++)
@@ -713,7 +730,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(THREADS, 1) kernel(c
                     mark(12);
                 }
             }
-            ptx::bar_sync(1, 128);  // s_sc / s_last are reused by the next run
+            ptx::bar_sync(1, ET);  // s_sc / s_last are reused by the next run
         }
         if (et == 0) tflush(3, 0);
         if (STAGED) sct.finish();   // every bulk copy of this thread has been written out before the CTA may exit
@@ -756,7 +773,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     cudaError_t e = ensure_dyn_smem(kern, smem, p.g.device, smem_set);
     if (e != cudaSuccess) return e;
     cudaLaunchConfig_t cfg{};
-    cfg.blockDim = dim3(THREADS);
+    cfg.blockDim = dim3(threads_for(OUT));
     cfg.dynamicSmemBytes = smem;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
