@@ -612,18 +612,24 @@ def test_fused_scatter_bulk_copies(ctx, orc, knobs, bulk, T, N, bounds, K, kind,
 
 
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
+@pytest.mark.parametrize("flat", [1, 0], ids=["flat-walk-allowed", "k-group-units"])
 @pytest.mark.parametrize("lean,astages,bulk_out,nt", [(1, 2, 0, 128), (0, 2, 0, 128), (1, 3, 0, 128), (1, 4, 0, 128),
                                                      (1, 2, 1, 128), (0, 4, 1, 128), (1, 4, 0, 256), (0, 2, 1, 256)])
 @pytest.mark.parametrize("T", [65, 130, 300, 700])
-def test_tcp_role_loop_and_drain_variants(ctx, orc, knobs, lean, astages, bulk_out, nt, T, fast):
+def test_tcp_role_loop_and_drain_variants(ctx, orc, knobs, lean, astages, bulk_out, nt, T, fast, flat):
     """Every shipped variant of the CTA-pair kernel's role loops and drain: lean loops (uniform shapes) vs the generic
     unit-walking loops (VLUT_TC_LEAN=0, and always for the I1 types' 640-k groups and K not a multiple of the group size),
     two / three (single accumulator) / four A stages, both token tiles, direct stores vs the staged drain through one 2-D TMA
     tensor store per chunk (VLUT_TC_BULK_OUT=1; needs 16-byte aligned rows: N % 4 == 0, the ragged N = 900 shape clips at
-    the tensor bound), fast and exact (per-K-group) drains."""
+    the tensor bound), fast and exact (per-K-group) drains, and the flat walk (K in uniform A blocks across the K-group
+    boundaries when the quantise kernel reports that no token tile can wrap: normal activations take it, uniform ones
+    do not) for the shapes whose groups do not fit the lean loops -- 640-k groups with a short last block (K = 3200), with
+    whole blocks (K = 8640 -> 8704), K not a multiple of the group size (K = 1040)."""
     a = api()
-    knobs(VLUT_TC_LEAN=lean, VLUT_TC_ASTAGES=astages, VLUT_TC_BULK_OUT=bulk_out, VLUT_TC_NT=nt, VLUT_TC_FAST=fast)
-    for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I2_V_4, 4096, 900), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 388)]:
+    knobs(VLUT_TC_LEAN=lean, VLUT_TC_ASTAGES=astages, VLUT_TC_BULK_OUT=bulk_out, VLUT_TC_NT=nt, VLUT_TC_FAST=fast,
+          VLUT_TC_FLAT=flat)
+    for type_, K, N in [(O.I2_V_4, 2048, 1024), (O.I2_V_4, 4096, 900), (O.I1_V_2, 3200, 520), (O.I2_V, 1040, 388),
+                        (O.I1_V_2, 8640, 260)]:
         w = O.make_ternary(N, K, seed=T + astages)
         x = O.make_acts(T, K, seed=T, kind="uniform" if (T + astages) % 2 else "normal")
         packed = orc.pack(type_, w)

@@ -52,6 +52,7 @@ void knobs_reload() {
     k.tc_nt = env_int("VLUT_TC_NT", 0);
     k.tc_astages = env_int("VLUT_TC_ASTAGES", 0);
     k.tc_lean = env_int("VLUT_TC_LEAN", 1);
+    k.tc_flat = env_int("VLUT_TC_FLAT", 1);
     k.tc_bulk_out = env_int("VLUT_TC_BULK_OUT", 0);
     k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
     k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
@@ -480,8 +481,9 @@ static int ensure_q_rm(vlut_ctx *c) {
 }
 
 int vlut_quantize_act(vlut_ctx *c, int type, const float *x_dev, int64_t ldx, int64_t K, int64_t T) {
-    // the weight's row count is unknown here: pick the token tile as for a typical FFN projection
-    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO, 8192);
+    // the weight's row count is unknown here: the cost model then picks the 128-token tile for the CTA-pair kernel (the
+    // faster one for most shapes; vlut_mul_mat / vlut_mul_mat_batch quantise with the real row count)
+    return quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_AUTO, 1);
 }
 
 int vlut_op_supported(int type, int64_t K, int64_t N, int64_t T) {

@@ -48,6 +48,12 @@ struct Params {
     int allow_fast, pdl;
     int split_last;  // experiment: walk the whole tiles before the split units
     int uniform;  // every K-group unit has gsub sub-blocks (KB % gsub == 0): the decode warps run their lean loop
+    // FLAT walk (shapes whose K-groups do not fit the lean loops: 640-k groups, K not a multiple of the group size).  On the
+    // fast path (no int16 wrap possible) K-group boundaries mean nothing: the whole K extent accumulates anyway.  When the
+    // quantise kernel reports that NO token tile of this call is unsafe, every role walks K in uniform A blocks instead:
+    // unit = one A block of SPA sub-blocks (the last one of a tile may be shorter), Gf units per tile.
+    int flat_ok, Gf, Uf, wholef;
+    int uniform_knob;   // VLUT_TC_LEAN
     int whole;  // 1: whole output tiles only (no fix-up); 0: stream-K over (tile, K-group) units; 2: hybrid (whole tiles + split remainder)
     int abl;  // timing ablations (VLUT_TC_ABL, results become wrong): 1 no tcgen05.st, 2 no MMA, 4 no wait::st, 8 no output stores (exact path), 16 no fast-path drain, 32 no activation copies, 64 no weight copies, 256 no LDS / unpack, 512 no stage ring at all (producers idle, decode does not wait for stages)
     long long *dbg;
@@ -78,8 +84,8 @@ struct Ranges {
 struct Walk {
     int u, u1, n0, n1, G, TT, gsub, KB;
     int tile, g, rp, tt, kb0, nsub;
-    __device__ __forceinline__ void init(const Params &p, const Ranges &r) {
-        G = p.G; TT = p.TT; gsub = p.gsub; KB = p.KB;
+    __device__ __forceinline__ void init(const Params &p, const Ranges &r, int G_, int gsub_) {
+        G = G_; TT = p.TT; gsub = gsub_; KB = p.KB;
         int f0 = r.b0, f1 = r.b1, s0 = r.a0, s1 = r.a1;
         if (p.split_last) { f0 = r.a0; f1 = r.a1; s0 = r.b0; s1 = r.b1; }
         if (f0 < f1) { u = f0; u1 = f1; n0 = s0; n1 = s1; }
@@ -184,26 +190,37 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
     constexpr bool STAGED = (OUT == 3 || OUT == 4);   // tiles leave through shared memory + bulk async copies
     constexpr int SO = (OUT == 4) ? 0 : OUT;          // flavour of the direct stores (exact path)
 
+    // walk shape: the K-group units of the op, or (flat) one A block per unit when no tile of this call can wrap
+    int shG = p.G, shgsub = p.gsub, shU = p.U, shwhole = p.whole;
+    bool flat = false;
+    if (p.flat_ok) {
+        if (p.pdl) ptx::pdl_wait();   // every role, the weight producer included: the flag is the quantise kernel's output
+        flat = p.allow_fast && (__ldg(p.g.act.tile_unsafe + (p.g.act.Tpad >> 4)) != p.g.act.epoch);
+        if (flat) { shG = p.Gf; shgsub = SPA; shU = p.Uf; shwhole = p.wholef; }
+    }
     const int ntiles = p.RP * p.TT;
     // p.whole: 1 = whole tiles only (uneven tile counts per pair), 0 = stream-K (every unit is a split unit),
     // 2 = hybrid: floor(ntiles / npairs) whole tiles per pair, the units of the remaining tiles split evenly over all pairs
-    const int full = (p.whole == 2) ? ntiles / npairs : 0;
-    const int sbase = npairs * full * p.G;   // first split unit
-    const int SU = p.U - sbase;              // split units
+    const int full = (shwhole == 2) ? ntiles / npairs : 0;
+    const int sbase = npairs * full * shG;   // first split unit
+    const int SU = shU - sbase;              // split units
     Ranges rg;
-    if (p.whole == 1) {
-        rg.a0 = (int) (((int64_t) pair * ntiles) / npairs) * p.G;
-        rg.a1 = (int) (((int64_t) (pair + 1) * ntiles) / npairs) * p.G;
+    if (shwhole == 1) {
+        rg.a0 = (int) (((int64_t) pair * ntiles) / npairs) * shG;
+        rg.a1 = (int) (((int64_t) (pair + 1) * ntiles) / npairs) * shG;
         rg.b0 = rg.b1 = 0;
     } else {
-        rg.a0 = pair * full * p.G;
-        rg.a1 = (pair + 1) * full * p.G;
+        rg.a0 = pair * full * shG;
+        rg.a1 = (pair + 1) * full * shG;
         rg.b0 = sbase + (int) (((int64_t) pair * SU) / npairs);
         rg.b1 = sbase + (int) (((int64_t) (pair + 1) * SU) / npairs);
     }
     // lean role loops (issuer, decode): every K-group unit has p.gsub sub-blocks and every A block is full, and no ablation
     // asks for the generic loops
-    const bool lean = p.uniform && (p.gsub % SPA == 0) && !(p.abl & (256 | 512));
+    // (flat: one block per unit, the last unit of a tile possibly short -- handled by the lean loops when a block is one
+    // shared-memory stage)
+    const bool lean = (flat ? (SPS == SPA && p.uniform_knob) : (p.uniform && (p.gsub % SPA == 0))) && !(p.abl & (256 | 512));
+    const int tail_na = p.KB - (shG - 1) * shgsub - (shgsub / SPA - 1) * SPA;   // sub-blocks of a tile's LAST A block (lean shapes)
     auto tile_fast = [&](int tt) -> bool { return p.allow_fast && (__ldg(p.g.act.tile_unsafe + tt) != p.g.act.epoch); };
     // optional timeline of CTA 0: (cycles since start, kind) per role, skipping the first `dbg_skip` events
     const bool dbg_on = p.dbg != nullptr && (int) blockIdx.x == p.dbg_cta && lane == 0;
@@ -250,7 +267,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         const bool is_w = (warp == 14);
         const uint64_t pol = is_w ? ptx::policy_evict_first() : ptx::policy_evict_last();
         Walk w;
-        w.init(p, rg);
+        w.init(p, rg, shG, shgsub);
         Ring st;
         st.init(S);
         // weights are static: with PDL their stream starts while the predecessor (quantise) kernel is still running;
@@ -300,7 +317,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             constexpr uint32_t DESC_HI = (uint32_t) ((1024 >> 4) | (1u << 14) | (2u << 29));   // SBO 1024 B, version 1, SWIZZLE_128B
             constexpr uint32_t DESC_LBO = 1u << 16;
             Walk w;
-            w.init(p, rg);
+            w.init(p, rg, shG, shgsub);
             int st_i = 0, ar_i = 0;
             uint32_t ar_ph = 0;
             const uint32_t empty0 = ptx::smem_u32(&s_empty[0]), afull0 = ptx::smem_u32(&s_afull[0]);
@@ -314,13 +331,15 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             const bool no_mma = (p.abl & 2) != 0;
             if (lean) {
                 // ---- lean loop: every A block is full; the unit walk happens once per TILE RUN, not per block ----
-                const uint32_t nbpu = (uint32_t) (p.gsub / SPA);   // A blocks per K-group unit
+                const uint32_t nbpu = (uint32_t) (shgsub / SPA);   // A blocks per unit
                 while (w.valid()) {
                     const int nu = w.run_last() - w.u + 1;         // units of this tile run
                     const bool fast_run = tile_fast(w.tt);
                     // fast path: one accumulation segment (a single drain) per run; exact path: one per unit
                     const int nseg = fast_run ? 1 : nu;
                     const uint32_t seg_blocks = (fast_run ? (uint32_t) nu : 1u) * nbpu;
+                    // blocks of this run until (and including) the tile's last block, the only one that can be short
+                    uint32_t to_tail = (uint32_t) (shG - w.g) * nbpu;
                     for (int seg = 0; seg < nseg; seg++) {
                         const uint32_t ab = ndrain % NACC;
                         ptx::mbar_wait(ptx::smem_u32(&s_accempty[ab]), ((ndrain / NACC) & 1) ^ 1);
@@ -331,6 +350,23 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                             ptx::mbar_wait(afull0 + 8u * (uint32_t) ar_i, ar_ph);
                             ptx::tc_fence_after();
                             const uint32_t a_tmem = tmem_base + A_COL0 + (uint32_t) ar_i * A_COLS;
+                            if (--to_tail == 0 && tail_na != SPA) {
+                                // the tile's short last block (flat walk; SPS == SPA: one stage): tail_na sub-blocks
+                                if (!no_mma) {
+                                    for (int sb = 0; sb < tail_na; sb++) {
+#pragma unroll
+                                        for (int ks = 0; ks < 4; ks++) {
+                                            const uint64_t b_desc = ((uint64_t) DESC_HI << 32) |
+                                                                    (uint64_t) (DESC_LBO | (stage_lo + (uint32_t) (sb * (ACT_BYTES >> 4) + ks * 2)));
+                                            ptx::umma_i8_ts_pair(d_tmem, a_tmem + sb * 32 + ks * 8, b_desc, idesc,
+                                                                 (sb == 0 && ks == 0) ? acc : 1u);
+                                        }
+                                    }
+                                }
+                                ptx::umma_commit_pair(aempty0 + 8u * (uint32_t) ar_i, 3);
+                                ptx::umma_commit_pair(empty0 + 8u * (uint32_t) st_i, 3);
+                                if (++st_i == S) { st_i = 0; stage_lo = stage_lo0; } else { stage_lo += stage_step; }
+                            } else {
 #pragma unroll
                             for (int s0 = 0; s0 < SPA; s0 += SPS) {
                                 if (!no_mma) {
@@ -349,6 +385,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                                 if (s0 + SPS >= SPA) ptx::umma_commit_pair(aempty0 + 8u * (uint32_t) ar_i, 3);
                                 ptx::umma_commit_pair(empty0 + 8u * (uint32_t) st_i, 3);
                                 if (++st_i == S) { st_i = 0; stage_lo = stage_lo0; } else { stage_lo += stage_step; }
+                            }
                             }
                             acc = 1u;
                             if (++ar_i == NA) { ar_i = 0; ar_ph ^= 1u; }
@@ -452,7 +489,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         const uint32_t taddr_base = tmem_base + ((uint32_t) (q * 32) << 16) + A_COL0 + h * CPH * 16;
         const bool do_st = !(p.abl & 1), do_wait = !(p.abl & 4);
         Walk w;
-        w.init(p, rg);
+        w.init(p, rg, shG, shgsub);
         Ring st, ar;
         st.init(S);
         ar.init(NA);
@@ -488,10 +525,18 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         if (lean) {
             // ---- lean loop: decode needs neither tiles nor units, only the number of (full) A blocks of this pair ----
             constexpr int SB = SPA / SPS;                        // shared-memory stages per A block
-            const uint32_t NB = (uint32_t) ((rg.a1 - rg.a0) + (rg.b1 - rg.b0)) * (uint32_t) (p.gsub / SPA);
+            const uint32_t nbpu = (uint32_t) (shgsub / SPA);     // A blocks per unit
+            const uint32_t NB = (uint32_t) ((rg.a1 - rg.a0) + (rg.b1 - rg.b0)) * nbpu;
+            // which blocks are a tile's short last block (flat walk only, SB == 1): blocks until the next tile end, per range
+            const bool has_tail = (tail_na != SPA);
+            const int r0b = p.split_last ? rg.a0 : rg.b0, r0e = p.split_last ? rg.a1 : rg.b1;   // first range walked
+            const int r1b = p.split_last ? rg.b0 : rg.a0;                                        // second range
+            const uint32_t nb_first = (uint32_t) (r0e - r0b) * nbpu;
+            auto blocks_to_tail = [&](int u) { return (uint32_t) (shG - (u % shG)) * nbpu; };
             const uint32_t full0 = ptx::smem_u32(&s_full[0]), empty0 = ptx::smem_u32(&s_empty[0]);
             const uint32_t aempty0 = ptx::smem_u32(&s_aempty[0]);
             uint32_t st_i = 0, st_ph = 0, ar_i = 0, ar_ph = 0;
+            // (a short block's missing chunks are loaded and unpacked as whatever the stage holds, and never stored)
             auto fetch_unpack_lean = [&]() {
                 ptx::mbar_wait(full0 + 8u * st_i, st_ph);
                 const uint32_t w_s = w_s0 + st_i * stage_bytes;
@@ -516,7 +561,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             };
             uint32_t more = NB * SB;                             // stages not fetched yet
             if (more) { --more; fetch_unpack_lean(); }
+            uint32_t to_tail = NB ? blocks_to_tail(nb_first ? r0b : r1b) : 0;
             for (uint32_t blk = 0; blk < NB; blk++) {
+                if (blk == nb_first && nb_first) to_tail = blocks_to_tail(r1b);   // on to the second range
+                const bool short_blk = (--to_tail == 0) && has_tail;
+                if (to_tail == 0) to_tail = (uint32_t) shG * nbpu;
                 ptx::mbar_wait(aempty0 + 8u * ar_i, ar_ph ^ 1u);
                 ptx::tc_fence_after();
                 const uint32_t taddr0 = taddr_base + ar_i * A_COLS;
@@ -524,7 +573,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                 for (int sg = 0; sg < SB; sg++) {
                     if (do_st) {
 #pragma unroll
-                        for (int c = 0; c < CPH; c++) ptx::tmem_st_32x32b_x16(taddr0 + sg * SPS * 32 + c * 16, r[c]);
+                        for (int c = 0; c < CPH; c++)
+                            if (!short_blk || h * CPH + c < 2 * tail_na) ptx::tmem_st_32x32b_x16(taddr0 + sg * SPS * 32 + c * 16, r[c]);
                     }
                     if (sg == SB - 1) {
                         if (do_wait) ptx::tmem_st_wait();
@@ -593,13 +643,13 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         // exact-path running totals: this CTA's scratch tile in the (L2-resident) workspace
         int32_t *const tots = p.g.part + ((int64_t) gridDim.x * 2 + blockIdx.x) * (NT * 128);
         Walk w;
-        w.init(p, rg);
+        w.init(p, rg, shG, shgsub);
         while (w.valid()) {
             // ---- one tile run: units [ra, rb] of one output tile ----
             const int ra = w.u, rb = w.run_last();
             const int g_begin = w.g, g_end = w.g + (rb - ra);
             const bool fast = tile_fast(w.tt);
-            const bool complete = (g_begin == 0) && (g_end == p.G - 1);
+            const bool complete = (g_begin == 0) && (g_end == shG - 1);
             const int tile = w.tile;
             const int64_t n = ((int64_t) 2 * w.rp + rank) * TILE_ROWS + m;
             const int64_t t0 = (int64_t) w.tt * NT;
@@ -617,7 +667,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             // walk contributors x NT/16 dependent L2 round trips of ~2000 clk each under the main loop's traffic.)
             int32_t *slot = nullptr;
             if (!complete) {
-                const long long x = (long long) tile * p.G - sbase;
+                const long long x = (long long) tile * shG - sbase;
                 const int b_first = (int) (((x + 1) * npairs - 1) / SU);
                 slot = p.g.acc + (int64_t) (2 * b_first + rank) * (128 * NT);
             }
@@ -644,6 +694,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             for (int u = ra; u <= rb; u++, w.next()) {
                 if (fast && u != rb) continue;  // fast path: a single drain at the end of the run
                 const uint32_t ab = ndrain % NACC;
+                if (flat) {
+                    // the +1 code-offset correction is linear in K: the run that holds the tile's first block subtracts all
+                    // of it (the K-group prefix sums do not line up with the A blocks), the other runs nothing
+                    for (int i = et; i < NT; i += ET)
+                        s_gs[i] = (g_begin == 0) ? __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + p.G) -
+                                                       __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1))
+                                                 : 0;
+                } else
                 for (int i = et; i < NT; i += ET)
                     s_gs[i] = __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + w.g + 1) -
                               __ldg(p.g.act.gpre + (t0 + i) * (p.G + 1) + (fast ? g_begin : w.g));
@@ -702,7 +760,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                 if (et == 0) {
                     const int ndone = g_end - g_begin + 1;
                     const int old = atomicAdd(counter, ndone);
-                    s_last = (old + ndone == p.G);
+                    s_last = (old + ndone == shG);
                 }
                 ptx::bar_sync(1, ET);
                 mark(11);
@@ -804,20 +862,33 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     const int ptiles = p.RP * p.TT;
     constexpr int FIXUP_UNITS = 10, HYBRID_UNITS = 3;
     const int rounds = (ptiles + npairs - 1) / npairs;
-    const int full = ptiles / npairs, su = (ptiles - full * npairs) * p.G;
-    const int cost_whole = rounds * p.G;
-    const int cost_hybrid = full * p.G + (su ? 2 * ((su + npairs - 1) / npairs) + HYBRID_UNITS : 0);  // split units cost ~2x (measured)
-    const int cost_sk = (p.U + npairs - 1) / npairs + FIXUP_UNITS;
-    p.whole = 1;
-    if (full >= 1 && cost_hybrid < cost_whole && cost_hybrid <= cost_sk) p.whole = 2;
-    else if (cost_sk < cost_whole) p.whole = 0;
     const int forced_grid = kn.tc_grid;  // tests: force a grid (and with it the split paths)
-    if (forced_grid > 0) p.whole = 0;
-    if (kn.tc_whole >= 0) p.whole = kn.tc_whole;
+    auto policy = [&](int G, int U, int gsub) {    // G units per tile, U in all, gsub 128-k sub-blocks per unit
+        // costs in 512-k units of pair time (the fix-up constants were measured with 512-k K-groups)
+        const double scale = gsub / 4.0;
+        const int full = ptiles / npairs, su = (ptiles - full * npairs) * G;
+        const double cost_whole = rounds * G * scale;
+        const double cost_hybrid = full * G * scale + (su ? 2 * ((su + npairs - 1) / npairs) * scale + HYBRID_UNITS : 0);  // split units cost ~2x (measured)
+        const double cost_sk = ((U + npairs - 1) / npairs) * scale + FIXUP_UNITS;
+        int whole = 1;
+        if (full >= 1 && cost_hybrid < cost_whole && cost_hybrid <= cost_sk) whole = 2;
+        else if (cost_sk < cost_whole) whole = 0;
+        if (forced_grid > 0) whole = 0;
+        if (kn.tc_whole >= 0) whole = kn.tc_whole;
+        return whole;
+    };
+    // flat walk (see Params): for shapes the lean loops cannot take as they are, when a block is one shared-memory stage
+    p.uniform_knob = kn.tc_lean;
+    p.flat_ok = (kn.tc_flat && kn.tc_lean && p.allow_fast && SPS == SPA && !(p.uniform && p.gsub % SPA == 0)) ? 1 : 0;
+    p.Gf = (p.KB + SPA - 1) / SPA;
+    p.Uf = p.RP * p.TT * p.Gf;
+    p.whole = policy(p.G, p.U, p.gsub);
+    p.wholef = policy(p.Gf, p.Uf, SPA);
     p.split_last = kn.tc_split_last;
     if (forced_grid > 0) npairs = forced_grid / 2;
-    else if (p.whole == 1) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
+    else if (p.whole == 1 && !p.flat_ok) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;
+    if (p.flat_ok && npairs > p.Uf) npairs = p.Uf;
     if (2 * npairs > sm_count) npairs = sm_count / 2;  // one accumulation tile per CTA of a resident grid (GemmArgs.acc)
     if (npairs < 1) npairs = 1;
     cfg.gridDim = dim3((unsigned) (2 * npairs));

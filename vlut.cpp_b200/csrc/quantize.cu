@@ -116,7 +116,7 @@ __global__ void __launch_bounds__(QT) quantize_kernel(const float *__restrict__ 
         pre[a.G] = run;
         a.nowrap[t] = safe;
         // a token tile takes the single-drain path unless one of its tokens stamps it with this call's epoch
-        if (!safe) a.tile_unsafe[t / a.NT] = a.epoch;
+        if (!safe) { a.tile_unsafe[t / a.NT] = a.epoch; a.tile_unsafe[a.Tpad / 16] = a.epoch; }   // [Tpad / 16]: "some tile is unsafe"
     }
 }
 
@@ -230,7 +230,7 @@ __global__ void __launch_bounds__(NTH) quantize_reg_kernel(const float *__restri
             pre[a.G] = carry;
             a.nowrap[t] = safe ? 1 : 0;
             // a token tile takes the single-drain path unless one of its tokens stamps it with this call's epoch
-            if (!safe) a.tile_unsafe[t / a.NT] = a.epoch;
+            if (!safe) { a.tile_unsafe[t / a.NT] = a.epoch; a.tile_unsafe[a.Tpad / 16] = a.epoch; }   // [Tpad / 16]: "some tile is unsafe"
         }
     }
 }

@@ -65,13 +65,14 @@ __host__ __device__ inline int token_tile(int64_t T) { return T <= 16 ? 16 : T <
 // counts (profiles/r2_tcp_tiles.txt: it picks the faster tile in 23 of 24 cases, the miss costs 6 %):
 //     tile time = G * unit + tile_overhead;  whole / hybrid schedule as in launch_out (gemm_tc5.cu);  + fixed
 inline double pair_tile_cost(int64_t K, int64_t N, int64_t T, int NT, int gsize, int sm_count) {
-    // constants in clk, fitted to scripts/time_tcp.py on the lean-loop kernel (profiles/r2_tcp_tiles_lean.txt: the model picks
-    // the faster tile in 24 of 24 measured cases).  Shapes that cannot run the lean role loops (K-groups of 640 k: a full
-    // A block + a 128-k remainder per unit) pay ~2x per unit on the 128-token tile, 1.2x on the 256-token tile.
-    const bool lean = (gsize == 512 && K % 512 == 0);
-    const double unit = (NT > 128 ? 1900.0 : 1300.0) * (lean ? 1.0 : (NT > 128 ? 1.2 : 2.0));
+    // constants in clk per 512 k of a tile, fitted to scripts/time_tcp.py on the lean-loop kernel (profiles/r2_tcp_tiles_lean.txt:
+    // the model picks the faster tile in 24 of 24 measured cases).  Shapes whose K-groups do not fit the lean loops (640-k
+    // groups, K not a multiple of the group size) walk K in uniform blocks on the fast path ("flat", gemm_tc5.cuh): the
+    // same constants apply to ceil(K / 512) blocks.
+    const double unit = NT > 128 ? 1900.0 : 1300.0;
     const double tile = NT > 128 ? 6000.0 : 0.0, fixed = NT > 128 ? 9000.0 : 6000.0;
-    const int64_t G = ceil_div(K, gsize), RP = (ceil_div(N, TILE_ROWS) + 1) / 2, TT = ceil_div(T, NT);
+    (void) gsize;
+    const int64_t G = ceil_div(K, 512), RP = (ceil_div(N, TILE_ROWS) + 1) / 2, TT = ceil_div(T, NT);
     const int64_t ptiles = RP * TT, npairs = sm_count / 2 > 0 ? sm_count / 2 : 1;
     const int64_t rounds = ceil_div(ptiles, npairs), full = ptiles / npairs, su = (ptiles - full * npairs) * G;
     const double whole = (double) rounds * (G * unit + tile);
@@ -96,7 +97,7 @@ inline int token_tile_pair(int64_t K, int64_t N, int64_t T, int gsize, int sm_co
 //                             correction of groups [a, b] is gpre[b+1] - gpre[a]  (undoes the +1 of the u8 codes)
 // nowrap int32 [Tpad]         1 if for every group of token t sum_k |q| <= 32767, i.e. no int16 wrap is possible
 //                             whatever the weights are (full-K accumulation is then exact)
-// tile_unsafe u32 [Tpad/NT]   = `epoch` of this quantisation iff some token of the tile can wrap (any unsafe token's CTA
+// tile_unsafe u32 [Tpad/16+1] [tt] = `epoch` of this quantisation iff some token of tile tt can wrap; [Tpad/16] = `epoch` iff any tile can (any unsafe token's CTA
 //                             stores the epoch: no reduction, no atomics); epoch = per-context call counter, never 0
 struct ActView {
     int8_t *q_rm;
@@ -202,6 +203,7 @@ struct Knobs {
     int tc_grid, tc_whole, tc_split_last;   // VLUT_TC_GRID, VLUT_TC_WHOLE, VLUT_TC_SPLIT_LAST (tests: force the split paths)
     int tc_abl, tc_debug, tc_debug_skip;    // VLUT_TC_ABL, VLUT_TC_DEBUG, VLUT_TC_DEBUG_SKIP
     int tc_nt;                     // VLUT_TC_NT          force the TCP token tile (128 / 256)
+    int tc_flat;                   // VLUT_TC_FLAT        0: never walk K in uniform A blocks across the K-group boundaries (comparison, tests)
     int tc_lean;                   // VLUT_TC_LEAN        0: the generic (unit-walking) decode loop even for uniform shapes (comparison, tests)
     int tc_astages;                // VLUT_TC_ASTAGES     2: two A stages of 512 k, 4: four of 256 k; default per token tile
     int tcs_nas, tcs_split, tcs_issuers, tcs_depth, tcs_dbg_cta, tcs_dbg_mask, tcs_pre;   // VLUT_TCS_*
