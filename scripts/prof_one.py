@@ -5,7 +5,7 @@ import vlut_b200
 from vlut_b200 import api
 T = int(sys.argv[1]) if len(sys.argv) > 1 else 16
 iters = int(sys.argv[2]) if len(sys.argv) > 2 else 6
-K, N = 4096, 14336
+K, N = [int(v) for v in os.environ.get("VLUT_SHAPE", "4096,14336").split(",")]
 type_ = api.TYPE_BY_NAME[os.environ.get("VLUT_TYPE", "I2_V_4")]
 ctx = api.Context(0)
 g = torch.Generator(device="cuda"); g.manual_seed(1)

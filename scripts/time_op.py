@@ -21,9 +21,9 @@ def timed(fn, iters=60):
         e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
         best = min(best, e0.elapsed_time(e1) / iters * 1e3)
     return best
-type_, K, N = 42, 4096, 14336
+type_, K, N = [int(v) for v in os.environ.get("SHAPE", "42,4096,14336").split(",")]
 nb = api.nbytes(type_, K, N)
-ws = [ctx.upload(type_, K, N, torch.randint(0, 81, (nb,), dtype=torch.uint8, device=dev, generator=gen)) for _ in range(12)]
+ws = [ctx.upload(type_, K, N, torch.randint(0, 81 if type_ in (40, 42, 43) else 243, (nb,), dtype=torch.uint8, device=dev, generator=gen)) for _ in range(12)]
 line = []
 for T in [int(t) for t in (sys.argv[1] if len(sys.argv) > 1 else "16,128,512,2048").split(",")]:
     xs = [torch.randn((T, K), dtype=torch.float32, device=dev, generator=gen) for _ in range(4)]

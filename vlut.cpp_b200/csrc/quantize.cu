@@ -317,9 +317,15 @@ template <int NTH>
 static cudaError_t launch_reg_n(int words, const float *x, int64_t ldx, int64_t K, int64_t T, const ActView &a, cudaStream_t s,
                                 bool pdl, int early, int want_rm) {
     const int ch = (words + NTH - 1) / NTH;   // 16-byte words per thread
+    // exact word counts up to 8 per thread: every word held costs 4 registers of a row that lives in registers between the
+    // two passes, and the registers decide how many rows an SM has in flight (K = 8640 on 512 threads: 5 words, not 8)
     if (ch <= 1) return launch_reg<NTH, 1>(x, ldx, K, T, a, s, pdl, early, want_rm);
     if (ch <= 2) return launch_reg<NTH, 2>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 3) return launch_reg<NTH, 3>(x, ldx, K, T, a, s, pdl, early, want_rm);
     if (ch <= 4) return launch_reg<NTH, 4>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 5) return launch_reg<NTH, 5>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 6) return launch_reg<NTH, 6>(x, ldx, K, T, a, s, pdl, early, want_rm);
+    if (ch <= 7) return launch_reg<NTH, 7>(x, ldx, K, T, a, s, pdl, early, want_rm);
     if (ch <= 8) return launch_reg<NTH, 8>(x, ldx, K, T, a, s, pdl, early, want_rm);
     if (ch <= 16) return launch_reg<NTH, 16>(x, ldx, K, T, a, s, pdl, early, want_rm);
     return cudaErrorInvalidValue;
