@@ -18,6 +18,7 @@
 // the even CTA ("leader") owns afull[] (16 arrivals: 8 decode warps of each CTA -- a decode warp has waited for its CTA's
 // stage, so A-ready implies that CTA's half of the activations has landed) and accempty[] (8 arrivals: 4 epilogue warps of
 // each CTA).  The leader's commits are multicast to both CTAs.
+#include <type_traits>
 #include "epilogue.cuh"
 #include "ptx.cuh"
 #include "vlut_common.cuh"
@@ -329,7 +330,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             int run_tile = -1;
             bool fast = false, open = false;
             const bool no_mma = (p.abl & 2) != 0;
-            if (lean) {
+            // (one body, compiled twice: the flat walk's short-block bookkeeping must not cost the K-group walk anything --
+            //  a few instructions per block in this loop are ~2 % of the kernel)
+            auto lean_issue = [&](auto flat_c) {
+                constexpr bool FLAT = decltype(flat_c)::value;
                 // ---- lean loop: every A block is full; the unit walk happens once per TILE RUN, not per block ----
                 const uint32_t nbpu = (uint32_t) (shgsub / SPA);   // A blocks per unit
                 while (w.valid()) {
@@ -339,7 +343,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     const int nseg = fast_run ? 1 : nu;
                     const uint32_t seg_blocks = (fast_run ? (uint32_t) nu : 1u) * nbpu;
                     // blocks of this run until (and including) the tile's last block, the only one that can be short
-                    uint32_t to_tail = (uint32_t) (shG - w.g) * nbpu;
+                    [[maybe_unused]] uint32_t to_tail = (uint32_t) (shG - w.g) * nbpu;
                     for (int seg = 0; seg < nseg; seg++) {
                         const uint32_t ab = ndrain % NACC;
                         ptx::mbar_wait(ptx::smem_u32(&s_accempty[ab]), ((ndrain / NACC) & 1) ^ 1);
@@ -350,7 +354,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                             ptx::mbar_wait(afull0 + 8u * (uint32_t) ar_i, ar_ph);
                             ptx::tc_fence_after();
                             const uint32_t a_tmem = tmem_base + A_COL0 + (uint32_t) ar_i * A_COLS;
-                            if (--to_tail == 0 && tail_na != SPA) {
+                            bool short_blk = false;
+                            if constexpr (FLAT) short_blk = (--to_tail == 0 && tail_na != SPA);
+                            if (FLAT && short_blk) {
                                 // the tile's short last block (flat walk; SPS == SPA: one stage): tail_na sub-blocks
                                 if (!no_mma) {
                                     for (int sb = 0; sb < tail_na; sb++) {
@@ -395,6 +401,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     }
                     for (int i = 0; i < nu; i++) w.next();
                 }
+            };
+            if (lean) {
+                if (flat) lean_issue(std::true_type{}); else lean_issue(std::false_type{});
             } else
             for (; w.valid(); w.next()) {
                 if (w.tile != run_tile) {
@@ -522,7 +531,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                 epi::reg_fence(r[c]);   // unpacked HERE, not sunk below the A-free wait
             }
         };
-        if (lean) {
+        auto lean_decode = [&](auto flat_c) {
+            constexpr bool FLAT = decltype(flat_c)::value;
             // ---- lean loop: decode needs neither tiles nor units, only the number of (full) A blocks of this pair ----
             constexpr int SB = SPA / SPS;                        // shared-memory stages per A block
             const uint32_t nbpu = (uint32_t) (shgsub / SPA);     // A blocks per unit
@@ -561,11 +571,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             };
             uint32_t more = NB * SB;                             // stages not fetched yet
             if (more) { --more; fetch_unpack_lean(); }
-            uint32_t to_tail = NB ? blocks_to_tail(nb_first ? r0b : r1b) : 0;
+            [[maybe_unused]] uint32_t to_tail = NB ? blocks_to_tail(nb_first ? r0b : r1b) : 0;
             for (uint32_t blk = 0; blk < NB; blk++) {
-                if (blk == nb_first && nb_first) to_tail = blocks_to_tail(r1b);   // on to the second range
-                const bool short_blk = (--to_tail == 0) && has_tail;
-                if (to_tail == 0) to_tail = (uint32_t) shG * nbpu;
+                bool short_blk = false;
+                if constexpr (FLAT) {
+                    if (blk == nb_first && nb_first) to_tail = blocks_to_tail(r1b);   // on to the second range
+                    short_blk = (--to_tail == 0) && has_tail;
+                    if (to_tail == 0) to_tail = (uint32_t) shG * nbpu;
+                }
                 ptx::mbar_wait(aempty0 + 8u * ar_i, ar_ph ^ 1u);
                 ptx::tc_fence_after();
                 const uint32_t taddr0 = taddr_base + ar_i * A_COLS;
@@ -574,7 +587,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     if (do_st) {
 #pragma unroll
                         for (int c = 0; c < CPH; c++)
-                            if (!short_blk || h * CPH + c < 2 * tail_na) ptx::tmem_st_32x32b_x16(taddr0 + sg * SPS * 32 + c * 16, r[c]);
+                            if (!FLAT || !short_blk || h * CPH + c < 2 * tail_na) ptx::tmem_st_32x32b_x16(taddr0 + sg * SPS * 32 + c * 16, r[c]);
                     }
                     if (sg == SB - 1) {
                         if (do_wait) ptx::tmem_st_wait();
@@ -586,6 +599,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     if (more) { --more; fetch_unpack_lean(); }
                 }
             }
+        };
+        if (lean) {
+            if (flat) lean_decode(std::true_type{}); else lean_decode(std::false_type{});
         } else {
         if (w.valid()) fetch_unpack();
         while (w.valid()) {
