@@ -378,6 +378,9 @@ def main() -> None:
             gather_mode = "fused-multimem-v4" if use_mc else ("fused-p2p-v4" if os.environ.get("VLUT_SCATTER_BULK") == "0" else "fused-p2p-bulk")
             if os.environ.get("VLUT_SCATTER_VEC") == "0":
                 gather_mode = gather_mode.replace("-v4", "-scalar").replace("-bulk", "-scalar")
+            if os.environ.get("VLUT_BENCH_PUSH", "0") == "1" and not use_mc:
+                gather_mode = "push-copy-kernel"
+
         except Exception as e:  # noqa: BLE001
             if rank == 0:
                 print(f"[bench] symmetric memory unavailable ({e}); using the NCCL all-gather", file=sys.stderr)
@@ -387,7 +390,14 @@ def main() -> None:
         gather_buf = torch.empty((world * T, N), dtype=torch.float32, device=dev)
         local_out = [torch.empty((T, N), dtype=torch.float32, device=dev) for _ in range(n_x)]
 
+    # VLUT_BENCH_PUSH=1: the GEMM stores its slice locally and stamps its tiles; a copy kernel resident beside it forwards
+    # them to the peers (vlut_mul_mat_scatter_push) -- the transfer no longer holds the GEMM's accumulators
+    use_push = world > 1 and os.environ.get("VLUT_BENCH_PUSH", "0") == "1"
+
     def fused_scatter(h, w, x, n_tot, col0):
+        if use_push and not use_mc:
+            ctx.mul_mat_scatter_push(w, x, peers=[int(p) for p in h.buffer_ptrs], self_index=rank, ldo=n_tot, col0=col0)
+            return
         ctx.mul_mat_scatter(w, x, peers=[int(p) for p in h.buffer_ptrs],
                             multicast_ptr=int(getattr(h, "multicast_ptr", 0) or 0) if use_mc else 0, ldo=n_tot, col0=col0)
 

@@ -135,6 +135,14 @@ int vlut_scale_rows(vlut_ctx *ctx, const float *x_dev, int64_t ldx, float *out_d
 int vlut_mul_mat_scatter(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                          int64_t ldx, float *const *outs_dev, int n_out, int multicast, int64_t ldo, float w_scale,
                          int algo);
+/* The same op with the all-gather DECOUPLED from the GEMM's accumulators: the GEMM stores this rank's slice into its OWN
+ * buffer (outs_dev[self]) and stamps every finished tile; a small copy kernel on a second stream, resident beside the
+ * GEMM on every SM, forwards each stamped tile to the other ranks' buffers while the GEMM goes on.  Same arguments as
+ * vlut_mul_mat_scatter without multicast; `self` = index of this rank's buffer in outs_dev.  Falls back to the fused
+ * scatter where the CTA-pair kernel is not the one that runs (T <= 64) or the buffers are not 16-byte aligned. */
+int vlut_mul_mat_scatter_push(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev,
+                              const float *x_dev, int64_t ldx, float *const *outs_dev, int n_out, int self, int64_t ldo,
+                              float w_scale);
 /* The cross-rank barrier that publishes a fused all-gather.  flags_dev[i] = rank i's flag array as seen from this device:
  * >= 16 uint32, peer-visible (a symmetric-memory signal pad or a vlut_group allocation), zero-initialised.  Rank `rank`
  * advances its epoch (kept in word [8] of its own array, so the call is CUDA-graph capturable), stores it into slot [rank]

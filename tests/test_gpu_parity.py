@@ -665,3 +665,30 @@ def test_tcs_virtual_strips(ctx, orc, knobs, rows, split, T):
     torch.cuda.synchronize()
     for n, p, o in zip(Ns, packs, outs):
         assert np.array_equal(bits(o.cpu().numpy()), bits(orc.mul_mat(O.I2_V_4, p, x, n))), f"batched N={n}"
+
+
+@pytest.mark.parametrize("T,kind", [(40, "normal"), (130, "normal"), (300, "uniform"), (520, "normal")])
+@pytest.mark.parametrize("type_,K,N,bounds", [(O.I2_V_4, 2048, 640, [0, 384, 640]), (O.I1_V_2, 3200, 900, [0, 512, 900]),
+                                              (O.I2_V_4, 4096, 1800, [0, 640, 1280, 1800])])
+def test_scatter_push_single_gpu_emulation(ctx, orc, type_, K, N, bounds, T, kind):
+    """vlut_mul_mat_scatter_push (local GEMM that stamps its tiles + the copy kernel on a second stream that forwards them),
+    the 'ranks' emulated as shards and result buffers on ONE GPU: every shard's call writes its column slice into its own
+    buffer and the copy kernel forwards it to the others.  T <= 64 takes the documented fall-back (fused scatter); uniform
+    activations the exact path; split tiles (hybrid) stamp from the last arriver; twice, so that the epoch-stamped tile
+    flags of the first call are stale for the second."""
+    a = api()
+    w = O.make_ternary(N, K, seed=5)
+    x = O.make_acts(T, K, seed=6, kind=kind)
+    packed = orc.pack(type_, w)
+    ref = orc.mul_mat(type_, packed, x, N)
+    xd = torch.from_numpy(x).cuda()
+    G = len(bounds) - 1
+    for rep in range(2):
+        bufs = [torch.zeros((T, N), device="cuda") for _ in range(G)]
+        for g in range(G):
+            r0, rows = bounds[g], bounds[g + 1] - bounds[g]
+            Wg = ctx.upload(type_, K, rows, a.shard_rows(type_, K, N, r0, rows, packed))
+            ctx.mul_mat_scatter_push(Wg, xd, peers=[b.data_ptr() for b in bufs], self_index=g, ldo=N, col0=r0)
+        torch.cuda.synchronize()
+        for i, b in enumerate(bufs):
+            assert np.array_equal(bits(b.cpu().numpy()), bits(ref)), f"rep {rep} buffer {i}"

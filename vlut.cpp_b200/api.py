@@ -209,6 +209,16 @@ class Context:
                                               len(ptrs), 1 if multicast_ptr else 0, ldo, w_scale, algo),
               "vlut_mul_mat_scatter")
 
+    def mul_mat_scatter_push(self, w: Weight, x: torch.Tensor, peers: list[int], self_index: int, ldo: int, col0: int,
+                             w_scale: float = 1.0) -> None:
+        """vlut_mul_mat_scatter_push: local GEMM + a concurrent copy kernel that forwards finished tiles to the peers."""
+        assert x.is_cuda and x.dtype == torch.float32 and x.dim() == 2 and x.stride(1) == 1 and x.shape[1] == w.K
+        T = x.shape[0]
+        ptrs = [p + 4 * col0 for p in peers]
+        arr = (C.c_void_p * len(ptrs))(*ptrs)
+        check(_lib.lib().vlut_mul_mat_scatter_push(self._h, w.type, w.K, w.N, T, w.t2.data_ptr(), x.data_ptr(), x.stride(0),
+                                                   arr, len(ptrs), self_index, ldo, w_scale), "vlut_mul_mat_scatter_push")
+
     def barrier(self, flag_ptrs: list[int], rank: int) -> None:
         """vlut_barrier: publish a fused all-gather across ranks (flag_ptrs[i] = rank i's peer-visible flag array)."""
         arr = (C.c_void_p * len(flag_ptrs))(*flag_ptrs)

@@ -121,7 +121,10 @@ struct vlut_ctx {
     int sm_count = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
-    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_unsafe, part, counters, acc, stage_x, stage_out, stage_w;
+    DevBuf q_rm, q_sw, scales, gpre, nowrap, tile_unsafe, part, counters, acc, stage_x, stage_out, stage_w, tile_done;
+    uint32_t *push_flags = nullptr;   // set around a push-mode GEMM launch (vlut_mul_mat_scatter_push)
+    cudaStream_t push_stream = nullptr;
+    cudaEvent_t push_fork = nullptr, push_join = nullptr;
     ActView act{};
     int64_t act_K = 0, act_T = 0;
     int act_type = 0;
@@ -581,6 +584,8 @@ static int gemm_impl(vlut_ctx *c, int64_t K, int64_t T, const GemmCall *calls, i
     g.w = g.tens[0].w;
     g.out = g.tens[0].out;
     g.ldo = g.tens[0].ldo;
+    g.tile_done = c->push_flags;
+    g.tile_epoch = c->act.epoch;
     g.local_bulk = (g.n_out == 0 && knobs().tc_bulk_out && g.ldo % 4 == 0 && calls[0].N % 4 == 0 &&
                     !(reinterpret_cast<uintptr_t>(g.out) & 15)) ? 1 : 0;
     g.N = g.tens[0].N;
@@ -784,6 +789,48 @@ int vlut_mul_mat_scatter(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T,
     if (rc) return rc;
     const GemmCall q{type, N, t2_dev, nullptr, ldo, w_scale};
     return gemm_impl(c, K, T, &q, 1, outs_dev, n_out, multicast, algo);
+}
+
+int vlut_mul_mat_scatter_push(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
+                              int64_t ldx, float *const *outs_dev, int n_out, int self, int64_t ldo, float w_scale) {
+    if (!c || !outs_dev || n_out < 2 || n_out > 8 || self < 0 || self >= n_out) return VLUT_ERR_INVALID;
+    // the copy kernel moves 16-byte words of rows that start 16-byte aligned; the CTA-pair kernel stamps the tiles
+    bool ok = (ldo % 4 == 0) && (N % 4 == 0) && vlut_pick_algo(type, K, N, T) == VLUT_ALGO_TCP && knobs().algo == 0;
+    for (int i = 0; i < n_out; i++) ok = ok && !(reinterpret_cast<uintptr_t>(outs_dev[i]) & 15);
+    if (!ok) return vlut_mul_mat_scatter(c, type, K, N, T, t2_dev, x_dev, ldx, outs_dev, n_out, 0, ldo, w_scale, VLUT_ALGO_AUTO);
+    int rc = quantize_impl(c, type, x_dev, ldx, K, T, VLUT_ALGO_TCP, N);
+    if (rc) return rc;
+    CK(cudaSetDevice(c->device));
+    if (!c->push_stream) {
+        CK(cudaStreamCreateWithFlags(&c->push_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&c->push_fork, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&c->push_join, cudaEventDisableTiming));
+    }
+    const int NT = c->act.NT, TT = (int) (c->act.Tpad / NT);
+    const int RP = (int) ((ceil_div(N, TILE_ROWS) + 1) / 2), ntiles = RP * TT;
+    bool grew = false;
+    if (c->tile_done.reserve((size_t) ntiles * 2 * sizeof(uint32_t), &grew) != cudaSuccess) return VLUT_ERR_NOMEM;
+    if (grew) CK(cudaMemsetAsync(c->tile_done.p, 0, c->tile_done.cap, c->stream));
+    // fork: the copy kernel starts with the GEMM (both behind the quantise kernel)
+    CK(cudaEventRecord(c->push_fork, c->stream));
+    CK(cudaStreamWaitEvent(c->push_stream, c->push_fork, 0));
+    c->push_flags = (uint32_t *) c->tile_done.p;
+    const GemmCall q{type, N, t2_dev, outs_dev[self], ldo, w_scale};
+    rc = gemm_impl(c, K, T, &q, 1, nullptr, 0, 0, VLUT_ALGO_TCP);
+    c->push_flags = nullptr;
+    if (rc) return rc;
+    float *dst[7];
+    int nd = 0;
+    for (int i = 0; i < n_out; i++)
+        if (i != self) dst[nd++] = outs_dev[i];
+    cudaError_t e = vlut::launch_push(outs_dev[self], dst, nd, ldo, N, T, NT, TT, ntiles, (const uint32_t *) c->tile_done.p,
+                                      c->act.epoch, c->sm_count, c->push_stream);
+    if (e != cudaSuccess) return cuda_fail(e, "push launch");
+    c->launches++;
+    CK(cudaEventRecord(c->push_join, c->push_stream));
+    CK(cudaStreamWaitEvent(c->stream, c->push_join, 0));
+    c->inflight_unknown = true;
+    return VLUT_OK;
 }
 
 int vlut_barrier(vlut_ctx *c, void *const *flags_dev, int n_ranks, int rank) {

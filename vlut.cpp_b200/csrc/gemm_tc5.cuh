@@ -804,7 +804,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     mark(12);
                 }
             }
+            // push mode: this CTA's block of the tile is in the local result buffer -> stamp it for the copy kernel
+            const bool stamp = p.g.tile_done != nullptr && (complete || s_last);
+            if (stamp) __threadfence();
             ptx::bar_sync(1, ET);  // s_sc / s_last are reused by the next run
+            if (stamp && et == 0)
+                asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.g.tile_done + tile * 2 + rank), "r"(p.g.tile_epoch) : "memory");
         }
         if (et == 0) tflush(3, 0);
         if (STAGED) sct.finish();   // every bulk copy of this thread has been written out before the CTA may exit

@@ -148,6 +148,8 @@ struct GemmArgs {
     int vec_ok;         // scatter destinations are 16-byte aligned with ldo % 4 == 0: four rows per lane per store
     int bulk_ok;        // ... and N % 4 == 0, peer pointers: the CTA-pair kernel stages tiles in shared memory and scatters
                         // them with bulk async copies (epilogue.cuh, Scatter)
+    uint32_t *tile_done;   // push mode (push.cu): [tiles][2] stamped with tile_epoch when a CTA's 128 x NT block of a tile is in `out`
+    uint32_t tile_epoch;
     int local_bulk;     // n_out == 0 and `out` allows the staged drain (16-byte aligned, ldo % 4 == 0, N % 4 == 0): OUT = 4
     int64_t ldo;
     int64_t K, N, T, Npad;
@@ -233,6 +235,8 @@ long long *debug_buffer(cudaStream_t s, int skip);   // c_api.cu: zeroed buffer 
 cudaError_t measure_int8_peak(int sm_count, cudaStream_t s, int iters, double *tops, double *clk_per_mma);  // peak.cu
 
 cudaError_t launch_barrier(uint32_t *const *flags, int n, int rank, cudaStream_t s);   // barrier.cu
+cudaError_t launch_push(const float *src, float *const *dst, int n_dst, int64_t ldo, int64_t N, int64_t T, int NT, int TT,
+                        int ntiles, const uint32_t *tile_done, uint32_t epoch, int sm_count, cudaStream_t s);   // push.cu
 // launchers (one per .cu)
 cudaError_t launch_repack(int type, int64_t K, int64_t N, const uint8_t *gguf, uint8_t *t2, cudaStream_t s);
 cudaError_t launch_unpack_t2(int64_t K, int64_t N, const uint8_t *t2, int8_t *w, cudaStream_t s);

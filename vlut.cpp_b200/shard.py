@@ -140,7 +140,12 @@ class RowShardedWeight:
         # VLUT_SHARD_MULTICAST=1: NVSwitch multicast stores (multimem.st) instead
         mc = int(getattr(hdl, "multicast_ptr", 0) or 0) if os.environ.get("VLUT_SHARD_MULTICAST", "0") == "1" else 0
         peers = [int(p) for p in hdl.buffer_ptrs]
-        self.ctx.mul_mat_scatter(self.local, x, peers=peers, multicast_ptr=mc, ldo=self.N, col0=self.row0,
-                                 w_scale=w_scale)
+        if os.environ.get("VLUT_SHARD_PUSH", "0") == "1" and not mc:
+            # local GEMM + the concurrent copy kernel (push.cu); falls back to the fused scatter for T <= 64
+            self.ctx.mul_mat_scatter_push(self.local, x, peers=peers, self_index=self.rank, ldo=self.N, col0=self.row0,
+                                          w_scale=w_scale)
+        else:
+            self.ctx.mul_mat_scatter(self.local, x, peers=peers, multicast_ptr=mc, ldo=self.N, col0=self.row0,
+                                     w_scale=w_scale)
         self.ctx.barrier(self.flag_ptrs(hdl), self.rank)  # every rank's stores have landed everywhere
         return buf
