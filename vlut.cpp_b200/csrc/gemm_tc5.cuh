@@ -881,7 +881,6 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     //   stream-K (0) ceil(U / npairs) + 10             every pair ends on a split tile: the fix-up is exposed at the tail
     //                                                  (measured T=512: 39.6 us vs 33.9 us whole on 56 of the 74 pairs)
     const int ptiles = p.RP * p.TT;
-    constexpr int FIXUP_UNITS = 10, HYBRID_UNITS = 3;
     const int rounds = (ptiles + npairs - 1) / npairs;
     const int forced_grid = kn.tc_grid;  // tests: force a grid (and with it the split paths)
     auto policy = [&](int G, int U, int gsub) {    // G units per tile, U in all, gsub 128-k sub-blocks per unit
@@ -889,8 +888,13 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
         const double scale = gsub / 4.0;
         const int full = ptiles / npairs, su = (ptiles - full * npairs) * G;
         const double cost_whole = rounds * G * scale;
-        const double cost_hybrid = full * G * scale + (su ? 2 * ((su + npairs - 1) / npairs) * scale + HYBRID_UNITS : 0);  // split units cost ~2x (measured)
-        const double cost_sk = ((U + npairs - 1) / npairs) * scale + FIXUP_UNITS;
+        // refitted on the lean-loop kernel (scripts/time_split.py, profiles/r2_tcp_split_policies.txt): a split unit costs
+        // ~1.2 units; the fix-up of a split tile costs ~7 units next to short whole tiles (G = 8) and hides almost
+        // completely under long ones (G = 28); stream-K's exposed fix-up ~16
+        const double tile_units = G * scale;
+        const double hybrid_fix = tile_units > 24.0 ? 2.0 : 10.0 - tile_units / 3.0;
+        const double cost_hybrid = full * tile_units + (su ? 1.2 * ((su + npairs - 1) / npairs) * scale + hybrid_fix : 0);
+        const double cost_sk = ((U + npairs - 1) / npairs) * scale + 16.0;
         int whole = 1;
         if (full >= 1 && cost_hybrid < cost_whole && cost_hybrid <= cost_sk) whole = 2;
         else if (cost_sk < cost_whole) whole = 0;
