@@ -892,7 +892,8 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
         // ~1.2 units; the fix-up of a split tile costs ~7 units next to short whole tiles (G = 8) and hides almost
         // completely under long ones (G = 28); stream-K's exposed fix-up ~16
         const double tile_units = G * scale;
-        const double hybrid_fix = tile_units > 24.0 ? 2.0 : 10.0 - tile_units / 3.0;
+        // (... and a little better the more whole tiles follow it: with three or more, hybrid wins the ties -- all SMs busy)
+        const double hybrid_fix = (tile_units > 24.0 ? 2.0 : 10.0 - tile_units / 3.0) * (full >= 3 ? 0.85 : 1.0);
         const double cost_hybrid = full * tile_units + (su ? 1.2 * ((su + npairs - 1) / npairs) * scale + hybrid_fix : 0);
         const double cost_sk = ((U + npairs - 1) / npairs) * scale + 16.0;
         int whole = 1;
