@@ -520,6 +520,52 @@ def main() -> None:
                      "int8_peak_measured_tops": int8_peak_tops, "int8_peak_2x_bf16_tops": int8_peak_2xbf16,
                      "algorithmic_bytes": main_shape.alg_bytes(T), "algorithmic_ops": 2 * K * N * T})
 
+    # ---- the SM clock INSIDE the dominant kernel ---------------------------------------------------------------
+    # nvidia-smi samples every 200 ms and cannot see a 26 us kernel; under sustained load this GEMM drives the B200 into its
+    # 1000 W power cap (sw_power_cap) and the SM clock drops below the 1965 MHz the peak is quoted at.  The kernel's debug
+    # counters (VLUT_TC_DEBUG=1, OUTSIDE every timed region) give the MMA issuer's life in SM cycles (clock64) and in wall
+    # time (globaltimer): their ratio is the clock the kernel really ran at, and ideal MMA cycles / life is the tensor-pipe
+    # utilisation in the pipe's own clock.
+    def in_kernel_clock():
+        if not (world == 1 and gemm_algo == "tcp" and not args.no_cpu):
+            return
+        try:
+            import numpy as np
+            from vlut_b200 import _lib
+            os.environ["VLUT_TC_DEBUG"] = "1"
+            api.reload_env()
+            ctx.quantize_act(type_, xs[0])
+
+            def read():
+                torch.cuda.synchronize()
+                buf = np.zeros(256 * 4 * 8 + 4 * 24 * 2, dtype=np.int64)
+                _lib.lib().vlut_debug_tc_counters(buf.ctypes.data, buf.size)
+                c = buf[:8192].reshape(256, 4, 8)
+                used = c[:, 1, 7] > 0
+                life, ns = float(c[used, 1, 7].mean()), float(c[used, 1, 5].mean())
+                mma_clk = (-(-N // 256)) * (-(-T // 128)) * (K // 32) * 64.0 / max(int(used.sum()), 1)
+                return {"sm_mhz": round(life / ns * 1e3, 1), "issuer_life_clk": round(life), "issuer_life_us": round(ns / 1e3, 2),
+                        "ideal_mma_clk_per_pair": round(mma_clk), "tensor_pipe_frac_in_sm_clocks": round(mma_clk / life, 4)}
+
+            time.sleep(0.5)   # let the chip cool off the sweep
+            for i in range(50):
+                ctx.gemm(weights[i % n_w], T, out=outs[0], algo=api.ALGO_TCP)
+            burst = read()
+            t_end = time.time() + 1.0
+            while time.time() < t_end:
+                for i in range(100):
+                    ctx.gemm(weights[i % n_w], T, out=outs[0], algo=api.ALGO_TCP)
+                torch.cuda.synchronize()
+            roofline["in_kernel"] = {"burst_50_launches": burst, "after_1s_of_load": read(),
+                                     "note": "SM cycles (clock64) over wall time (globaltimer) of the MMA issuer's life, kernel's debug "
+                                             "counters, outside every timed region: the clock the kernel really runs at (the peak is "
+                                             "quoted at sm_max_mhz) and the tensor-pipe utilisation in the pipe's own clock"}
+        except Exception as e:  # noqa: BLE001
+            roofline["in_kernel"] = {"error": str(e)}
+        finally:
+            os.environ.pop("VLUT_TC_DEBUG", None)
+            api.reload_env()
+
     sweep, configs, batches = [], [], []
     if not args.no_sweep and world == 1:
         for t in SWEEP_T:
@@ -702,6 +748,8 @@ def main() -> None:
                              f"build {ref.isa}", "ms_per_op": t_acc / reps * 1e3}
         except Exception as e:  # noqa: BLE001
             cpu = {"value": None, "unit": "Tint-op/s", "cores": 0, "kind": "reference", "sample": f"failed: {e}"}
+
+    in_kernel_clock()   # last: it heats the chip into its power cap
 
     if rank == 0:
         ws_mb = (n_w * api.repacked_nbytes(type_, K, N) + n_x * 4 * T * (K + n_total)) / 1e6

@@ -227,6 +227,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
     const bool dbg_on = p.dbg != nullptr && (int) blockIdx.x == p.dbg_cta && lane == 0;
     const long long t_start = dbg_on ? clock64() : 0;
     const long long t_start0 = p.dbg != nullptr ? clock64() : 0;
+    long long t_ns0 = 0;   // wall clock (globaltimer, ns) next to the SM clock: their ratio is the SM frequency under load
+    if (p.dbg != nullptr) asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_ns0));
     int n_ev = 0, ev_role = 0;
     auto mark = [&](int kind) {
         if (dbg_on && ev_role < 4) {
@@ -257,7 +259,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         if (cnt_on && blockIdx.x < 256) {
             long long *o = p.dbg + ((int) blockIdx.x * 4 + role) * 8;
             o[k0] = tw[0]; o[k0 + 1] = tw[1]; o[k0 + 2] = tw[2];
-            if (k0 == 0) { o[7] = clock64() - t_start0; o[6] = tw[3]; }
+            if (k0 == 0) {
+                long long t_ns1;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_ns1));
+                o[7] = clock64() - t_start0; o[6] = tw[3]; o[5] = t_ns1 - t_ns0;
+            }
         }
     };
     if (warp == 12 || warp == 14) {
@@ -642,10 +648,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         // EG warpgroups; group eg drains the columns [eg NT / EG, (eg + 1) NT / EG) of every accumulator.  A warp reads the
         // TMEM lane quadrant warp % 4.
         ev_role = 3;
-        const int eg = (warp < 4) ? 0 : 1;
-        const int ew = warp & 3;
+        const int eg = (EG == 1 || warp < 4) ? 0 : 1;   // (a compile-time 0 with one group: the column loops keep constant bounds)
+        const int ew = (EG == 1) ? warp : (warp & 3);   // (one group: exactly the round-1 expressions -- with `warp & 3` and
+                                                       //  et = eg * 128 + m the 256-token kernels spilled 320 bytes and their
+                                                       //  split-tile fix-up took 30 us longer)
         const int m = ew * 32 + lane;
-        const int et = eg * 128 + m;  // 0 .. ET - 1
+        const int et = (EG == 1) ? (int) threadIdx.x : eg * 128 + m;  // 0 .. ET - 1
         constexpr int CW = NT / EG;   // columns per group
         const int cbeg = eg * CW, cend = cbeg + CW;
         if (p.pdl) ptx::pdl_wait();  // reads predecessor outputs; owns all global writes of this kernel
