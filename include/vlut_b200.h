@@ -120,6 +120,23 @@ int vlut_gemm(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const vo
 /* the whole op on device buffers = GGML_OP_MUL_MAT(vlut weight, f32) of ggml-cpu.c:1372-1421 */
 int vlut_mul_mat(vlut_ctx *ctx, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev, const float *x_dev,
                  int64_t ldx, float *out_dev, int64_t ldo, float w_scale, int algo);
+/* The whole op for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Needs no vlut_ctx and calls no cudaMalloc / cudaFree / allocating library routine: the quantised activations -- the scratch
+ * every other entry point keeps in the context workspace -- live in one file-scope __device__ array of
+ * VLUT_NO_ALLOC_MAX_SCRATCH_BYTES that every GPU loading the library holds until the process exits (no_alloc.cu).
+ *   limit:   round_up(4 T, 256) + T * round_up(K, 128) <= VLUT_NO_ALLOC_MAX_SCRATCH_BYTES (e.g. 1023 tokens of K = 4096, 292 of
+ *            K = 14336) and T <= 65535; beyond it the call returns VLUT_ERR_UNSUPPORTED and says so in `err`.
+ *   sharing: every call uses the same array (which keeps the last call's contents; the kernels rewrite every byte they read).
+ *            Calls that overlap on the GPU -- different streams -- RACE; calls on one stream are ordered by it.
+ * device: CUDA ordinal the buffers live on; stream: cudaStream_t (NULL = default stream); t2_dev: weights repacked by
+ * vlut_repack_weights / vlut_upload_weights; x_dev f32 [T][ldx]; out_dev f32 [T][ldo].  err (optional): receives a
+ * NUL-terminated message when the result is not VLUT_OK.  Results are bit-identical to vlut_mul_mat's; the kernels are the
+ * plain CUDA-core anchor (VLUT_ALGO_SIMPLE class), not the tcgen05 path. */
+#define VLUT_NO_ALLOC_MAX_SCRATCH_BYTES ((size_t) 4 << 20)
+int vlut_mul_mat_no_alloc(int device, void *stream, int type, int64_t K, int64_t N, int64_t T, const void *t2_dev,
+                          const float *x_dev, int64_t ldx, float *out_dev, int64_t ldo, float w_scale, char *err,
+                          size_t err_len);
 /* out[t][n] = x[t][n] * scale on device buffers (in place allowed): GGML_OP_MUL by a one-element f32 tensor -- the
  * `.scale` of a ternary weight (src/models/bitnet.cpp:33-34, src/llama-graph.cpp:780-783; CPU:
  * ggml_compute_forward_mul, ggml/src/ggml-cpu/binary-ops.cpp:152) -- for the cases where the plugin cannot fold it

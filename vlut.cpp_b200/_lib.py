@@ -49,6 +49,7 @@ _SIGNATURES = {
     "vlut_mul_mat": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, cint]),
     "vlut_mul_mat_scatter": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, cint, cint, i64, f32, cint]),
     "vlut_mul_mat_scatter_push": (cint, [vp, cint, i64, i64, i64, vp, vp, i64, vp, cint, cint, i64, f32]),
+    "vlut_mul_mat_no_alloc": (cint, [cint, vp, cint, i64, i64, i64, vp, vp, i64, vp, i64, f32, C.c_char_p, C.c_size_t]),
     "vlut_group_create": (cint, [cint, vp, C.POINTER(vp)]),
     "vlut_group_destroy": (None, [vp]),
     "vlut_group_size": (cint, [vp]),

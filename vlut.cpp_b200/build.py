@@ -16,7 +16,7 @@ OUT = CSRC / "build"
 LIB = OUT / "libvlut_b200.so"
 GGML_PLUGIN = OUT / "libggml-vlut-b200.so"
 
-CU_SOURCES = ["c_api.cu", "repack.cu", "quantize.cu", "gemm_simple.cu", "gemm_tc5.cu", "gemm_tc5_nt64.cu", "gemm_tc5_nt128.cu", "gemm_tc5_nt128b.cu", "gemm_tc5_nt128c.cu", "gemm_tc5_nt256.cu", "gemm_tc5_nt256b.cu", "gemm_tcs.cu", "gemm_gemv.cu", "gemm_lut.cu", "peak.cu", "barrier.cu", "push.cu", "group.cu"]
+CU_SOURCES = ["c_api.cu", "repack.cu", "quantize.cu", "gemm_simple.cu", "gemm_tc5.cu", "gemm_tc5_nt64.cu", "gemm_tc5_nt128.cu", "gemm_tc5_nt128b.cu", "gemm_tc5_nt128c.cu", "gemm_tc5_nt256.cu", "gemm_tc5_nt256b.cu", "gemm_tcs.cu", "gemm_gemv.cu", "gemm_lut.cu", "peak.cu", "barrier.cu", "push.cu", "group.cu", "no_alloc.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
 
 
