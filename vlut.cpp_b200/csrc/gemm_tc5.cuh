@@ -48,6 +48,7 @@ struct Params {
     int nstages, stage_bytes;
     int allow_fast, pdl;
     int split_last;  // experiment: walk the whole tiles before the split units
+    int coop_fix;    // hybrid: the contributors of a split tile share its fix-up (VLUT_TC_COOP, default 1)
     int uniform;  // every K-group unit has gsub sub-blocks (KB % gsub == 0): the decode warps run their lean loop
     // FLAT walk (shapes whose K-groups do not fit the lean loops: 640-k groups, K not a multiple of the group size).  On the
     // fast path (no int16 wrap possible) K-group boundaries mean nothing: the whole K extent accumulates anyway.  When the
@@ -666,6 +667,10 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         const uint32_t accempty_leader1 = ptx::mapa(ptx::smem_u32(&s_accempty[1]), 0);
         // exact-path running totals: this CTA's scratch tile in the (L2-resident) workspace
         int32_t *const tots = p.g.part + ((int64_t) gridDim.x * 2 + blockIdx.x) * (NT * 128);
+        // shared fix-up of split tiles (below): only when every pair owns at most ONE split unit -- all contributors of a tile
+        // then arrive together, at the start of the kernel, and nobody's wait can hold up a run that another tile waits for
+        // (with longer split ranges pair b's second run feeds the tile pair b + 1 waits on: a chain over all pairs)
+        const bool coop = (shwhole == 2) && !p.split_last && p.coop_fix && SU < npairs;
         Walk w;
         w.init(p, rg, shG, shgsub);
         while (w.valid()) {
@@ -776,13 +781,61 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             }
 
             if (!complete) {
-                // split tile (stream-K): partial parked above; the last CTA to arrive sums all slots and finishes
+                // Split tile: partial parked above.  Who turns the accumulated tile into output?
+                //  * stream-K: the last CTA to arrive reads the sum back and finishes the tile (nobody ever waits);
+                //  * hybrid with at most one split unit per pair (split units are walked FIRST, so a tile's contributors arrive
+                //    together): every contributor waits until all units are in and finishes ITS share of the 16-column chunks.
+                //    The fix-up is ~6000 clk on one SM (64 KB read back over two L2 round trips, 64 KB of zeros and 64 KB of
+                //    output through ~29 B/clk of store bandwidth, scripts/ubench/red_rate.cu) and made its CTA the kernel's
+                //    straggler (scripts/role_life_spread.py: 44.6k clk against a mean of 36.7k at T = 512); shared by n
+                //    contributors it is one round trip and 128/n KB of stores each.  All CTAs of the grid are resident
+                //    (launch_out clamps the grid to the occupancy), so the wait cannot deadlock; it traps after ~1 s.
                 mark(10);
                 __threadfence();
                 ptx::bar_sync(1, ET);
                 int32_t *const counter = p.g.counters + tile * 2 + rank;
+                const int ndone = g_end - g_begin + 1;
+                if (coop) {
+                    // fewer split units than pairs: every unit of the tile has its own pair, contributor g finishes the
+                    // chunks g, g + G, ...
+                    if (et == 0) {
+                        atomicAdd(counter, ndone);
+                        const long long w0 = clock64();
+                        int seen;
+                        do {
+                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+                            if ((seen & 0xffff) >= shG) break;
+                            __nanosleep(40);
+                            if (clock64() - w0 > (1ll << 31)) __trap();
+                        } while (true);
+                    }
+                    ptx::bar_sync(1, ET);
+                    mark(11);
+                    __threadfence();
+#pragma unroll 1
+                    for (int c0 = cbeg + 16 * g_begin; c0 < cend; c0 += 16 * shG) {
+                        int32_t a[16];
+#pragma unroll
+                        for (int i = 0; i < 16; i++) a[i] = __ldcg(slot + (c0 + i) * 128 + m);
+#pragma unroll
+                        for (int i = 0; i < 16; i++) __stcg(slot + (c0 + i) * 128 + m, 0);
+                        epi::store16<OUT>(a, s_sc + c0, p.g.w_scale != 1.0f, p.g.w_scale, out0, p.g.outs, p.g.n_out,
+                                          (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0), n < p.g.N,
+                                          p.g.vec_ok != 0, scp);
+                    }
+                    // count the finished shares in the counter's upper half; the last one resets it (and, in push mode,
+                    // stamps the tile)
+                    __threadfence();
+                    ptx::bar_sync(1, ET);
+                    if (et == 0) {
+                        const int old = atomicAdd(counter, 1 << 16);
+                        s_last = ((old >> 16) + 1 == shG);
+                        if (s_last) *counter = 0;
+                    }
+                    ptx::bar_sync(1, ET);
+                    mark(12);
+                } else {
                 if (et == 0) {
-                    const int ndone = g_end - g_begin + 1;
                     const int old = atomicAdd(counter, ndone);
                     s_last = (old + ndone == shG);
                 }
@@ -810,6 +863,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     }
                     if (et == 0) *counter = 0;
                     mark(12);
+                }
                 }
             }
             // push mode: this CTA's block of the tile is in the local result buffer -> stamp it for the copy kernel
@@ -919,6 +973,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     p.whole = policy(p.G, p.U, p.gsub);
     p.wholef = policy(p.Gf, p.Uf, SPA);
     p.split_last = kn.tc_split_last;
+    p.coop_fix = kn.tc_coop;
     if (forced_grid > 0) npairs = forced_grid / 2;
     else if (p.whole == 1 && !p.flat_ok) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;
