@@ -10,6 +10,8 @@ dev = torch.device("cuda", 0)
 stream = torch.cuda.Stream(device=dev); torch.cuda.set_stream(stream)
 gen = torch.Generator(device=dev); gen.manual_seed(7)
 KNOB = os.environ.get("AB_KNOB", "VLUT_TC_COOP")
+VALS = [int(v) for v in os.environ.get("AB_VALS", "0,1").split(",")]   # e.g. AB_KNOB=VLUT_TC_NT AB_VALS=128,256
+if os.environ.get("AB_TS"): pass
 def capture(fn, iters=20):
     for i in range(3): fn(i)
     torch.cuda.synchronize()
@@ -23,25 +25,26 @@ def replay(g, iters=20):
     e0.record(); g.replay(); e1.record(); torch.cuda.synchronize()
     return e0.elapsed_time(e1) / iters * 1e3
 shapes = [("I2_V_4", 4096, 14336), ("I2_V_4", 14336, 4096), ("I2_V_4", 4096, 4096), ("I1_V_2", 3200, 8640), ("I1_V_2", 8640, 3200)]
-Ts = (384, 512, 640, 768, 1024, 1536, 2048)
-ctx = api.Context(dev, stream=stream)
+Ts = tuple(int(t) for t in os.environ.get("AB_TS", "384,512,640,768,1024,1536,2048").split(","))
+ctxs = {v: api.Context(dev, stream=stream) for v in VALS}   # one activation workspace per setting (the layout depends on the tile)
+ctx = ctxs[VALS[0]]
 for tn, K, N in shapes:
     type_ = api.TYPE_BY_NAME[tn]
     nb = api.nbytes(type_, K, N)
     ws = [ctx.upload(type_, K, N, torch.randint(0, 81, (nb,), dtype=torch.uint8, device=dev, generator=gen)) for _ in range(12)]
-    rows = {0: f"{tn} {K}->{N} {KNOB}=0", 1: f"{tn} {K}->{N} {KNOB}=1"}
+    rows = {v: f"{tn} {K}->{N} {KNOB}={v}" for v in VALS}
     for T in Ts:
         x = torch.randn((T, K), device=dev, generator=gen)
         o = torch.empty((T, N), device=dev)
-        ctx.quantize_act(type_, x)
         gs = {}
-        for v in (0, 1):
+        for v in VALS:
             os.environ[KNOB] = str(v)
             api.reload_env()
-            gs[v] = capture(lambda i: ctx.gemm(ws[i % 12], T, out=o, algo=api.ALGO_TCP))
-        ts = {0: [], 1: []}
+            ctxs[v].quantize_act(type_, x)
+            gs[v] = capture(lambda i: ctxs[v].gemm(ws[i % 12], T, out=o, algo=api.ALGO_TCP))
+        ts = {v: [] for v in VALS}
         for _ in range(9):
-            for v in (0, 1): ts[v].append(replay(gs[v]))
-        for v in (0, 1): rows[v] += f" {T}:{sorted(ts[v])[4]:5.1f}"
-    print(rows[0]); print(rows[1], flush=True)
+            for v in VALS: ts[v].append(replay(gs[v]))
+        for v in VALS: rows[v] += f" {T}:{sorted(ts[v])[4]:5.1f}"
+    for v in VALS: print(rows[v], flush=True)
     del ws; torch.cuda.empty_cache()
