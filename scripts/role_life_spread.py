@@ -33,3 +33,9 @@ for T in (128, 512, 1024):
         print("  fastest:", ", ".join(f"{pairs[i]}: {ep[i]} {'S' if has_split[pairs[i]] else '-'}" for i in order[-6:]))
         sp = np.array(has_split)
         print(f"  mean epilogue life: pairs with a split unit {ep[sp[pairs]].mean():.0f}, without {ep[~sp[pairs]].mean():.0f}")
+        isl = c[lead, 1, 7]
+        print(f"  mean issuer life: pairs with a split unit {isl[sp[pairs]].mean():.0f}, without {isl[~sp[pairs]].mean():.0f}")
+        for role, name in ((3, "epilogue"), (2, "decode"), (0, "producer")):
+            w = c[lead, role, :]
+            print(f"  {name} wait counters [0..2], [6] (mean clk): split " + " ".join(f"{w[sp[pairs], k].mean():.0f}" for k in (0, 1, 2, 6)) +
+                  "   no split " + " ".join(f"{w[~sp[pairs], k].mean():.0f}" for k in (0, 1, 2, 6)))

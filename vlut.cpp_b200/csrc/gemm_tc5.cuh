@@ -671,6 +671,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         // then arrive together, at the start of the kernel, and nobody's wait can hold up a run that another tile waits for
         // (with longer split ranges pair b's second run feeds the tile pair b + 1 waits on: a chain over all pairs)
         const bool coop = (shwhole == 2) && !p.split_last && p.coop_fix && SU < npairs;
+        int pend_old = -1;   // thread 0: the counter of this pair's split tile before its share was counted (coop)
         Walk w;
         w.init(p, rg, shG, shgsub);
         while (w.valid()) {
@@ -797,21 +798,27 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                 const int ndone = g_end - g_begin + 1;
                 if (coop) {
                     // fewer split units than pairs: every unit of the tile has its own pair, contributor g finishes the
-                    // chunks g, g + G, ...
+                    // chunks g, g + G, ...  Every step below that waits for an L2 round trip (~1000-1500 clk under load) is
+                    // on this pair's critical path, so there are as few as the protocol allows: fence (the partials have
+                    // landed) -> add the unit count -> poll -> load the share.  The zeros and the output are fire and forget,
+                    // and the count of finished shares (upper half of the counter; whoever completes it resets the counter) is
+                    // only looked at when the kernel ends (pend_old): nothing orders it against the output stores -- the
+                    // accumulation tile and the counter are next read by another launch.
                     if (et == 0) {
-                        atomicAdd(counter, ndone);
-                        const long long w0 = clock64();
-                        int seen;
-                        do {
-                            asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
-                            if ((seen & 0xffff) >= shG) break;
-                            __nanosleep(40);
-                            if (clock64() - w0 > (1ll << 31)) __trap();
-                        } while (true);
+                        const int old = atomicAdd(counter, ndone);
+                        if (((old + ndone) & 0xffff) < shG) {
+                            const long long w0 = clock64();
+                            int seen;
+                            do {
+                                __nanosleep(20);
+                                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
+                                if (clock64() - w0 > (1ll << 31)) __trap();
+                            } while ((seen & 0xffff) < shG);
+                        }
+                        __threadfence();   // acquire side for the whole epilogue (the bar.sync below carries it to the others)
                     }
                     ptx::bar_sync(1, ET);
                     mark(11);
-                    __threadfence();
 #pragma unroll 1
                     for (int c0 = cbeg + 16 * g_begin; c0 < cend; c0 += 16 * shG) {
                         int32_t a[16];
@@ -823,16 +830,19 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                                           (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0), n < p.g.N,
                                           p.g.vec_ok != 0, scp);
                     }
-                    // count the finished shares in the counter's upper half; the last one resets it (and, in push mode,
-                    // stamps the tile)
-                    __threadfence();
-                    ptx::bar_sync(1, ET);
-                    if (et == 0) {
-                        const int old = atomicAdd(counter, 1 << 16);
-                        s_last = ((old >> 16) + 1 == shG);
-                        if (s_last) *counter = 0;
+                    if (p.g.tile_done != nullptr) {
+                        // push mode: the last finisher stamps the tile, so the shares must be visible before they are counted
+                        __threadfence();
+                        ptx::bar_sync(1, ET);
+                        if (et == 0) {
+                            const int old = atomicAdd(counter, 1 << 16);
+                            s_last = ((old >> 16) + 1 == shG);
+                            if (s_last) *counter = 0;
+                        }
+                        ptx::bar_sync(1, ET);
+                    } else if (et == 0) {
+                        pend_old = atomicAdd(counter, 1 << 16);   // not waited for here
                     }
-                    ptx::bar_sync(1, ET);
                     mark(12);
                 } else {
                 if (et == 0) {
@@ -873,6 +883,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             if (stamp && et == 0)
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.g.tile_done + tile * 2 + rank), "r"(p.g.tile_epoch) : "memory");
         }
+        if (et == 0 && pend_old >= 0 && (pend_old >> 16) + 1 == shG)   // last finisher of the split tile: leave its counter at zero
+            p.g.counters[(rg.b0 / shG) * 2 + rank] = 0;
         if (et == 0) tflush(3, 0);
         if (STAGED) sct.finish();   // every bulk copy of this thread has been written out before the CTA may exit
     }
