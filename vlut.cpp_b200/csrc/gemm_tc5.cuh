@@ -747,8 +747,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     if (p.abl & 16) {
                         // timing ablation: the accumulator is handed back undrained
                     } else if (complete)
-                        epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
-                                                        p.g.ldo, tvalid, n < p.g.N, nullptr, p.g.vec_ok != 0, scp, cbeg, cend);
+                        epi::drain_fast<NT, OUT, 0>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0, p.g.ldo, tvalid,
+                                                    n < p.g.N && !(p.abl & 8) /* timing ablation: a drain without its stores */,
+                                                    nullptr, p.g.vec_ok != 0, scp, cbeg, cend);
                     else
                         epi::drain_fast<NT, OUT, 2>(ta, s_gs, s_sc, p.g.w_scale, out0, p.g.outs, p.g.n_out, idx0,
                                                        p.g.ldo, tvalid, n < p.g.N, slot + m, false, nullptr, cbeg, cend);
