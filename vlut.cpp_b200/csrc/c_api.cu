@@ -55,6 +55,7 @@ void knobs_reload() {
     k.tc_lean = env_int("VLUT_TC_LEAN", 1);
     k.tc_flat = env_int("VLUT_TC_FLAT", 1);
     k.tc_bulk_out = env_int("VLUT_TC_BULK_OUT", 0);
+    k.tc_vec_out = env_int("VLUT_TC_VEC_OUT", 0);
     k.tcs_nas = env_int("VLUT_TCS_NAS", 0);
     k.tcs_split = env_int("VLUT_TCS_SPLIT", 0);
     k.tcs_rows = env_int("VLUT_TCS_ROWS", 0);

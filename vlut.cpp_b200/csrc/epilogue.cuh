@@ -151,7 +151,7 @@ __device__ __forceinline__ void store16(const int32_t (&x)[16], const float *sc_
         sc->k++;
         return;
     }
-    if (SO != 0 && vec_ok) {
+    if (vec_ok) {   // (local output only with VLUT_TC_VEC_OUT=1: measured slower there than the 4-byte stores)
         const int lane = threadIdx.x & 31, j = lane & 3;
         // which rows of this lane's group of four exist (ragged tail of the matrix)
         const unsigned gm = (__ballot_sync(0xffffffffu, nvalid) >> (lane & ~3)) & 0xfu;

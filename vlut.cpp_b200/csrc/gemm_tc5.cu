@@ -59,6 +59,8 @@ cudaError_t launch_gemm_tc5(const GemmArgs &g, cudaStream_t s, int *launches) {
     p.U = p.RP * p.TT * p.G;
     const Knobs &kn = knobs();
     if (p.g.local_bulk && !make_out_map(&p.out_map, g.out, g.N, g.T, g.ldo)) p.g.local_bulk = 0;   // no tensor map: direct stores
+    // local output: 16-byte stores (four rows of a token per lane after a 4 x 4 transpose inside the warp) when the rows allow it
+    if (g.n_out == 0) p.g.vec_ok = (kn.tc_vec_out && g.ldo % 4 == 0 && (reinterpret_cast<uintptr_t>(g.out) & 15) == 0) ? 1 : 0;
     p.allow_fast = kn.tc_fast;
     p.uniform = (kn.tc_lean && p.KB % p.gsub == 0) ? 1 : 0;
     p.pdl = kn.pdl;

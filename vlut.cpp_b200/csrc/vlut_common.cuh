@@ -214,6 +214,7 @@ struct Knobs {
     int quant_kernel, quant_threads, quant_pdl, quant_early, quant_tpc;   // VLUT_QUANT_*
     int gemv_split, gemv_max_t;    // VLUT_GEMV_SPLIT, VLUT_GEMV_MAX_T
     int scatter_vec;               // VLUT_SCATTER_VEC    0: scalar 4-byte scatter stores (comparison)
+    int tc_vec_out;                // VLUT_TC_VEC_OUT     1: CTA-pair kernel, single-GPU output: 16-byte stores after a 4 x 4 lane transpose (measured 8-25 % SLOWER than the 4-byte stores, profiles/r2_tcp_drain_ablation.txt; default 0)
     int tc_bulk_out;               // VLUT_TC_BULK_OUT    1: the CTA-pair kernel drains single-GPU outputs through shared memory + one 2-D TMA tensor store per 16-token chunk (measured: T = 512 27.4 vs 25.6 us direct, equal at T = 2048; sixteen 512-byte bulk copies per chunk: 31-42 us)
     int scatter_bulk;              // VLUT_SCATTER_BULK   0: no staged bulk-copy scatter in the CTA-pair kernel (comparison)
 };
