@@ -670,7 +670,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
         // shared fix-up of split tiles (below): only when every pair owns at most ONE split unit -- all contributors of a tile
         // then arrive together, at the start of the kernel, and nobody's wait can hold up a run that another tile waits for
         // (with longer split ranges pair b's second run feeds the tile pair b + 1 waits on: a chain over all pairs)
-        const bool coop = (shwhole == 2) && !p.split_last && p.coop_fix && SU < npairs;
+        // (not in push mode: its copy kernel shares the SMs and waits for this kernel's stamps -- nothing here may wait on a CTA
+        // that might not be resident yet)
+        const bool coop = (shwhole == 2) && !p.split_last && p.coop_fix && SU < npairs && p.g.tile_done == nullptr;
         int pend_old = -1;   // thread 0: the counter of this pair's split tile before its share was counted (coop)
         Walk w;
         w.init(p, rg, shG, shgsub);
@@ -831,19 +833,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                                           (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0), n < p.g.N,
                                           p.g.vec_ok != 0, scp);
                     }
-                    if (p.g.tile_done != nullptr) {
-                        // push mode: the last finisher stamps the tile, so the shares must be visible before they are counted
-                        __threadfence();
-                        ptx::bar_sync(1, ET);
-                        if (et == 0) {
-                            const int old = atomicAdd(counter, 1 << 16);
-                            s_last = ((old >> 16) + 1 == shG);
-                            if (s_last) *counter = 0;
-                        }
-                        ptx::bar_sync(1, ET);
-                    } else if (et == 0) {
-                        pend_old = atomicAdd(counter, 1 << 16);   // not waited for here
-                    }
+                    if (et == 0) pend_old = atomicAdd(counter, 1 << 16);   // not waited for here
                     mark(12);
                 } else {
                 if (et == 0) {
