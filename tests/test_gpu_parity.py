@@ -371,19 +371,22 @@ def test_tcp_hybrid_whole_plus_split_tiles(ctx, orc, knobs, grid, T, fast, nt):
             assert np.array_equal(bits(out), bits(ref)), f"{O.TYPE_NAMES[type_]} K={K} N={N} rep={rep}"
 
 
-@pytest.mark.parametrize("coop", [1, 0], ids=["shared-fixup", "last-arriver-fixup"])
+@pytest.mark.parametrize("coop", [(1, 400000), (1, 1), (1, 3000), (0, 0)],
+                         ids=["shared-fixup", "shared-fixup-everybody-gives-up", "shared-fixup-some-give-up", "last-arriver-fixup"])
 @pytest.mark.parametrize("fast", [1, 0], ids=["fastpath-allowed", "per-group-drain"])
 @pytest.mark.parametrize("grid", [12, 22, 148])
 @pytest.mark.parametrize("T", [130, 300, 600])
 def test_tcp_hybrid_shared_fixup(ctx, orc, knobs, grid, T, fast, coop):
     """Hybrid split with at most one split unit per pair (fewer split units than pairs): VLUT_TC_COOP=1 lets every contributor
-    of a split tile wait for the others and finish its own 16-column chunks; 0 is the last-arriver fix-up.  More contributors
+    of a split tile wait for the others and finish its own 16-column chunks; 0 is the last-arriver fix-up.  The wait is bounded
+    (VLUT_TC_COOP_TIMEOUT clk): with 1 clk every waiter gives up at once and the last arriver finishes the tile alone, with
+    3000 clk some do and some do not.  More contributors
     than chunks (I1 flat walk: 25 blocks, 8 chunks), fewer (K = 1024: 2 units), ragged N and T, exact and fast path, twice in
     a row (the counters and accumulation tiles must come back clean)."""
     a = api()
-    knobs(VLUT_TC_GRID=grid, VLUT_TC_WHOLE=2, VLUT_TC_FAST=fast, VLUT_TC_COOP=coop)
+    knobs(VLUT_TC_GRID=grid, VLUT_TC_WHOLE=2, VLUT_TC_FAST=fast, VLUT_TC_COOP=coop[0], VLUT_TC_COOP_TIMEOUT=coop[1])
     for type_, K, N in [(O.I2_V_4, 1024, 700), (O.I1_V_2, 3200, 520), (O.I2_V_4, 4096, 1300), (O.I1_V, 1300, 260)]:
-        w = O.make_ternary(N, K, seed=grid + coop)
+        w = O.make_ternary(N, K, seed=grid + coop[0])
         x = O.make_acts(T, K, seed=T, kind="uniform" if (grid + T) % 4 == 0 else "normal")
         packed = orc.pack(type_, w)
         ref = orc.mul_mat(type_, packed, x, N)

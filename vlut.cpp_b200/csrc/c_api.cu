@@ -47,6 +47,7 @@ void knobs_reload() {
     k.tc_whole = env_int("VLUT_TC_WHOLE", -1);
     k.tc_split_last = env_int("VLUT_TC_SPLIT_LAST", 0);
     k.tc_coop = env_int("VLUT_TC_COOP", 1);
+    k.tc_coop_timeout = env_int("VLUT_TC_COOP_TIMEOUT", 400000);
     k.tc_abl = env_int("VLUT_TC_ABL", 0);
     k.tc_debug = env_int("VLUT_TC_DEBUG", 0);
     k.tc_debug_skip = env_int("VLUT_TC_DEBUG_SKIP", 0);

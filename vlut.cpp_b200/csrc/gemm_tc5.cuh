@@ -49,6 +49,7 @@ struct Params {
     int allow_fast, pdl;
     int split_last;  // experiment: walk the whole tiles before the split units
     int coop_fix;    // hybrid: the contributors of a split tile share its fix-up (VLUT_TC_COOP, default 1)
+    int coop_timeout;   // ... and wait at most this many clk for each other (VLUT_TC_COOP_TIMEOUT)
     int uniform;  // every K-group unit has gsub sub-blocks (KB % gsub == 0): the decode warps run their lean loop
     // FLAT walk (shapes whose K-groups do not fit the lean loops: 640-k groups, K not a multiple of the group size).  On the
     // fast path (no int16 wrap possible) K-group boundaries mean nothing: the whole K extent accumulates anyway.  When the
@@ -792,8 +793,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                 //    The fix-up is ~6000 clk on one SM (64 KB read back over two L2 round trips, 64 KB of zeros and 64 KB of
                 //    output through ~29 B/clk of store bandwidth, scripts/ubench/red_rate.cu) and made its CTA the kernel's
                 //    straggler (scripts/role_life_spread.py: 44.6k clk against a mean of 36.7k at T = 512); shared by n
-                //    contributors it is one round trip and 128/n KB of stores each.  All CTAs of the grid are resident
-                //    (launch_out clamps the grid to the occupancy), so the wait cannot deadlock; it traps after ~1 s.
+                //    contributors it is one round trip and 128/n KB of stores each.  The wait is bounded (below).
                 mark(10);
                 __threadfence();
                 ptx::bar_sync(1, ET);
@@ -807,23 +807,44 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                     // and the count of finished shares (upper half of the counter; whoever completes it resets the counter) is
                     // only looked at when the kernel ends (pend_old): nothing orders it against the output stores -- the
                     // accumulation tile and the counter are next read by another launch.
+                    // The wait needs every contributor to be running.  That holds for a grid that owns the GPU (launch_out clamps
+                    // it to the occupancy), but a kernel of another stream or process may hold the SMs this grid's last CTAs are
+                    // waiting for, and wait in the same way for its own -- so the wait is bounded (p.coop_timeout clk): a
+                    // contributor that runs out of patience sets ABANDON (only while the tile is still incomplete: CAS) and
+                    // leaves, everybody who sees the flag leaves too, and the last arriver -- which finds the flag in the value
+                    // its own arrival returns -- finishes the whole tile as in the stream-K protocol.  The flag cannot change
+                    // once the tile is complete, so all contributors agree on who stores what.
+                    constexpr int ABANDON = 1 << 30;
                     if (et == 0) {
-                        const int old = atomicAdd(counter, ndone);
-                        if (((old + ndone) & 0xffff) < shG) {
+                        int mode = 1;   // 1: my share, 2: the whole tile, 0: nothing
+                        int v = atomicAdd(counter, ndone) + ndone;
+                        if ((v & 0xffff) >= shG) {
+                            if (v & ABANDON) mode = 2;
+                        } else if (v & ABANDON) {
+                            mode = 0;
+                        } else {
                             const long long w0 = clock64();
-                            int seen;
-                            do {
+                            for (;;) {
                                 __nanosleep(20);
-                                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(counter) : "memory");
-                                if (clock64() - w0 > (1ll << 31)) __trap();
-                            } while ((seen & 0xffff) < shG);
+                                asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(counter) : "memory");
+                                if (v & ABANDON) { mode = 0; break; }
+                                if ((v & 0xffff) >= shG) break;
+                                if (clock64() - w0 > (long long) p.coop_timeout && atomicCAS(counter, v, v | ABANDON) == v) {
+                                    mode = 0;
+                                    break;
+                                }
+                            }
                         }
                         __threadfence();   // acquire side for the whole epilogue (the bar.sync below carries it to the others)
+                        s_last = mode;
                     }
                     ptx::bar_sync(1, ET);
                     mark(11);
+                    const int mode = s_last;
+                    const int cs = (mode == 1) ? cbeg + 16 * g_begin : (mode == 2 ? cbeg : cend);
+                    const int cstep = (mode == 1) ? 16 * shG : 16;
 #pragma unroll 1
-                    for (int c0 = cbeg + 16 * g_begin; c0 < cend; c0 += 16 * shG) {
+                    for (int c0 = cs; c0 < cend; c0 += cstep) {
                         int32_t a[16];
 #pragma unroll
                         for (int i = 0; i < 16; i++) a[i] = __ldcg(slot + (c0 + i) * 128 + m);
@@ -833,6 +854,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
                                           (t0 + c0) * p.g.ldo + n, p.g.ldo, (int) min((int64_t) 16, p.g.T - t0 - c0), n < p.g.N,
                                           p.g.vec_ok != 0, scp);
                     }
+                    // every contributor counts itself out exactly once (bits 16..29); the last one leaves the counter at zero
                     if (et == 0) pend_old = atomicAdd(counter, 1 << 16);   // not waited for here
                     mark(12);
                 } else {
@@ -874,7 +896,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(threads_for(OUT), 1)
             if (stamp && et == 0)
                 asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.g.tile_done + tile * 2 + rank), "r"(p.g.tile_epoch) : "memory");
         }
-        if (et == 0 && pend_old >= 0 && (pend_old >> 16) + 1 == shG)   // last finisher of the split tile: leave its counter at zero
+        if (et == 0 && pend_old >= 0 && ((pend_old >> 16) & 0x3fff) + 1 == shG)   // last contributor out: leave the counter at zero
             p.g.counters[(rg.b0 / shG) * 2 + rank] = 0;
         if (et == 0) tflush(3, 0);
         if (STAGED) sct.finish();   // every bulk copy of this thread has been written out before the CTA may exit
@@ -977,6 +999,7 @@ static cudaError_t launch_out(Params &p, int sm_count, cudaStream_t s) {
     p.wholef = policy(p.Gf, p.Uf, SPA);
     p.split_last = kn.tc_split_last;
     p.coop_fix = kn.tc_coop;
+    p.coop_timeout = kn.tc_coop_timeout;
     if (forced_grid > 0) npairs = forced_grid / 2;
     else if (p.whole == 1 && !p.flat_ok) npairs = (ptiles + rounds - 1) / rounds;  // the fewest pairs that finish in the same number of rounds
     if (npairs > p.U) npairs = p.U;

@@ -202,6 +202,7 @@ struct Knobs {
     int pdl;                       // VLUT_PDL            programmatic dependent launch (default 1)
     int tc_fast;                   // VLUT_TC_FAST        0 forces the exact (per-K-group drain) path
     int tc_smem_kb, tc_stages;     // VLUT_TC_SMEM_KB, VLUT_TC_STAGES
+    int tc_coop_timeout;                    // VLUT_TC_COOP_TIMEOUT: clk a contributor waits for the others before the tile falls back to the last-arriver fix-up (default 400000)
     int tc_coop;                            // VLUT_TC_COOP: contributors of a hybrid split tile share its fix-up (default 1)
     int tc_grid, tc_whole, tc_split_last;   // VLUT_TC_GRID, VLUT_TC_WHOLE, VLUT_TC_SPLIT_LAST (tests: force the split paths)
     int tc_abl, tc_debug, tc_debug_skip;    // VLUT_TC_ABL, VLUT_TC_DEBUG, VLUT_TC_DEBUG_SKIP
