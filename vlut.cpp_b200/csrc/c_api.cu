@@ -919,7 +919,16 @@ int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, co
     // long pole (4TN bytes against 4TK in), so the op costs ~ D2H(out) + one chunk of H2D + one chunk of compute.
     if (!c->h2d_stream) CK(cudaStreamCreateWithFlags(&c->h2d_stream, cudaStreamNonBlocking));
     if (!c->d2h_stream) CK(cudaStreamCreateWithFlags(&c->d2h_stream, cudaStreamNonBlocking));
-    const int64_t nchunk = (T + chunk - 1) / chunk;
+    // chunk boundaries: the result copy is the long pole and cannot start before the first chunk has been copied in and
+    // multiplied, so the first chunk is a quarter of the others (32 + 96 + 128 + 128 + ... tokens)
+    std::vector<int64_t> cut;
+    cut.push_back(0);
+    if (chunk >= 8 && T > chunk) {
+        cut.push_back(chunk / 4);
+        cut.push_back(chunk);
+    }
+    while (cut.back() < T) cut.push_back(std::min(T, cut.back() + chunk));
+    const int64_t nchunk = (int64_t) cut.size() - 1;
     while ((int64_t) c->ev_in.size() < nchunk) {
         cudaEvent_t a, b;
         CK(cudaEventCreateWithFlags(&a, cudaEventDisableTiming));
@@ -931,13 +940,13 @@ int vlut_mul_mat_host(vlut_ctx *c, int type, int64_t K, int64_t N, int64_t T, co
     CK(cudaEventRecord(c->ev_done[0], c->stream));
     CK(cudaStreamWaitEvent(c->h2d_stream, c->ev_done[0], 0));
     for (int64_t i = 0; i < nchunk; i++) {
-        const int64_t t0 = i * chunk, tn = std::min(chunk, T - t0);
+        const int64_t t0 = cut[i], tn = cut[i + 1] - cut[i];
         CK(copy_rows(sx + t0 * K, (size_t) K * 4, x_host + t0 * ldx, (size_t) ldx * 4, (size_t) K * 4, (size_t) tn,
                              cudaMemcpyHostToDevice, c->h2d_stream));
         CK(cudaEventRecord(c->ev_in[i], c->h2d_stream));
     }
     for (int64_t i = 0; i < nchunk; i++) {
-        const int64_t t0 = i * chunk, tn = std::min(chunk, T - t0);
+        const int64_t t0 = cut[i], tn = cut[i + 1] - cut[i];
         CK(cudaStreamWaitEvent(c->stream, c->ev_in[i], 0));
         rc = vlut_mul_mat(c, type, K, N, tn, t2_dev, sx + t0 * K, K, so + t0 * N, N, w_scale, algo);
         if (rc) {
